@@ -1,0 +1,151 @@
+/*
+ * qflex_b200.h -- C ABI of the B200 contraction engine (libqflex_b200.so).
+ *
+ * The reference (ngnrsaa/qflex) has no FFI/plugin seam; its numeric hot path is
+ * the C++ call boundary listed below.  This header is the thin C-ABI layer the
+ * new host code (qflex_b200/csrc/host) calls instead; each entry point cites the
+ * reference interface it replaces (paths relative to the reference repo).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++/torch types cross this boundary;
+ *   - every function returns 0 on success and a non-zero status on failure; the
+ *     message is available from qfx_last_error() (thread-local).  The host layer
+ *     turns it back into the reference's `throw std::string` convention
+ *     (src/errors.h:7-9);
+ *   - a tensor is a span of complex64 (2 floats, re then im) inside ONE device
+ *     arena per context; positions are element offsets into that arena.  Device
+ *     pointers never escape;
+ *   - every tensor dimension is a power of two (true for every tensor qFlex
+ *     builds: bond dims are 2^#cz or 4^#fsim, src/read_circuit.cpp:146-165), so
+ *     a tensor is addressed by the BITS of its linear index.  Bit 0 is the
+ *     fastest-varying (row-major, last index fastest, as src/tensor.h:34-60);
+ *   - calls are asynchronous on the context's stream; qfx_sync() /
+ *     qfx_download() / qfx_amps_download() synchronise.
+ */
+#ifndef QFLEX_B200_H_
+#define QFLEX_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QFX_MAX_BITS 40
+#define QFX_OK 0
+#define QFX_ERR_CUDA 1
+#define QFX_ERR_ARG 2
+#define QFX_ERR_OOM 3
+
+typedef struct qfx_ctx qfx_ctx;
+
+/* Thread-local message of the last failing call (never NULL). */
+const char* qfx_last_error(void);
+
+/* Number of visible CUDA devices (fails loudly when there is no GPU/driver:
+ * there is no CPU fallback anywhere in this library). */
+int qfx_device_count(int* n_out);
+
+/* One context = one GPU + one stream + one arena + one amplitude table.
+ * Replaces the process-global state of the reference (global::*, _REORDER_MAPS,
+ * src/tensor.cpp:83) with an explicit handle. */
+int qfx_create(int device, qfx_ctx** ctx_out);
+int qfx_destroy(qfx_ctx* ctx);
+int qfx_sync(qfx_ctx* ctx);
+
+/* Arena of n_elems complex64.  Replaces the scratch arena that
+ * ContractionData::Initialize sizes and allocates
+ * (src/contraction_utils.cpp:117-218) and scratch_2D
+ * (src/evaluate_circuit.cpp:207).  Re-reserving a larger size reallocates and
+ * discards the contents. */
+int qfx_arena_reserve(qfx_ctx* ctx, uint64_t n_elems);
+int qfx_arena_size(qfx_ctx* ctx, uint64_t* n_elems_out);
+
+/* Host <-> arena.  Replaces Tensor(indices, dims, data) construction and
+ * Tensor::data() reads (src/tensor.h:62-118). */
+int qfx_upload(qfx_ctx* ctx, uint64_t off, const float* host_re_im,
+               uint64_t n_elems);
+int qfx_download(qfx_ctx* ctx, uint64_t off, float* host_re_im,
+                 uint64_t n_elems);
+
+/* Flat device copy.  Replaces Tensor::operator= / _copy
+ * (src/tensor.cpp:107-139,197-213) as used for patch seeding and
+ * merge-into-empty (src/contraction_utils.cpp:238,323). */
+int qfx_copy(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
+             uint64_t n_elems);
+
+/* Pairwise contraction C[l,r] = sum_c A[l,c] * B[c,r] with all three operands
+ * addressed through per-bit position tables, so the two Tensor::reorder passes
+ * of the reference are folded into the operand gathers.
+ * Replaces qflex::multiply (src/tensor.cpp:1045-1194) = A.reorder + B.reorder
+ * (src/tensor.cpp:866-911) + cblas_cgemm / cgemv / cdotu
+ * (src/tensor.cpp:960-1042).
+ *
+ *   m (m_bits bits) enumerates the free indices of A, n the free indices of B,
+ *   k the contracted indices.  For bit i of m: it is bit a_m[i] of A's linear
+ *   offset and bit c_m[i] of C's.  Likewise b_n/c_n for n and a_k/b_k for k.
+ *   All listed positions inside one operand must be distinct and together cover
+ *   0..bits-1 of that operand.  Operands must not overlap C.
+ */
+typedef struct qfx_contract_desc {
+  uint64_t off_a, off_b, off_c; /* element offsets into the arena */
+  int32_t m_bits, n_bits, k_bits;
+  int8_t a_m[QFX_MAX_BITS], c_m[QFX_MAX_BITS];
+  int8_t b_n[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
+  int8_t a_k[QFX_MAX_BITS], b_k[QFX_MAX_BITS];
+  int32_t precision; /* QFX_PREC_* */
+} qfx_contract_desc;
+
+#define QFX_PREC_AUTO 0 /* class by arithmetic intensity */
+#define QFX_PREC_FFMA 1 /* fp32 FFMA everywhere */
+#define QFX_PREC_BF16X3 2 /* tcgen05 split-bf16 emulation of fp32 where legal */
+
+int qfx_contract(qfx_ctx* ctx, const qfx_contract_desc* desc);
+
+/* Final scalar contraction (m_bits = n_bits = 0) accumulated in complex128 into
+ * amplitude slot `slot`.  Replaces _multiply_vv + `(*amplitudes_)[output_index]
+ * += *output->data()` (src/tensor.cpp:1027-1042,
+ * src/contraction_utils.cpp:348-352). */
+int qfx_dot_accumulate(qfx_ctx* ctx, const qfx_contract_desc* desc,
+                       uint64_t slot);
+/* amps[slot] += (complex128) arena[off]  (final tensor already a scalar). */
+int qfx_scalar_accumulate(qfx_ctx* ctx, uint64_t off, uint64_t slot);
+
+/* Amplitude table (complex128), replaces std::vector<std::complex<double>>
+ * amplitudes (src/evaluate_circuit.cpp:226). */
+int qfx_amps_reserve(qfx_ctx* ctx, uint64_t n_amps); /* also zeroes */
+int qfx_amps_download(qfx_ctx* ctx, double* host_re_im, uint64_t n_amps);
+
+/* Index permutation = bit permutation of the linear offset:
+ * dst[sigma(i)] = src[i] where bit b of i becomes bit dst_pos[b] of sigma(i).
+ * One pass (read once, write once).  Replaces Tensor::reorder ->
+ * _fast_reorder/_left_reorder/_right_reorder (src/tensor.cpp:494-911).
+ * src and dst spans must not overlap. */
+int qfx_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
+                int32_t n_bits, const int8_t* dst_pos);
+
+/* Timing helpers (CUDA events on the context stream). */
+int qfx_timer_start(qfx_ctx* ctx);
+int qfx_timer_stop_ms(qfx_ctx* ctx, float* ms_out);
+
+/* Per-kernel-family accounting since the last reset: launches, device time is
+ * NOT measured here (see qfx_timer_*); flops/bytes are the algorithmic ones
+ * (8*M*N*K and 8*(MK+KN+MN)). */
+typedef struct qfx_stats {
+  uint64_t launches_total;
+  uint64_t launches_gemm_ffma;
+  uint64_t launches_gemm_tc;
+  uint64_t launches_reduce;
+  uint64_t launches_permute;
+  uint64_t launches_copy;
+  double flops;
+  double bytes;
+} qfx_stats;
+int qfx_stats_get(qfx_ctx* ctx, qfx_stats* out);
+int qfx_stats_reset(qfx_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QFLEX_B200_H_ */

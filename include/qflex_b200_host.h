@@ -1,0 +1,70 @@
+/*
+ * qflex_b200_host.h -- C entry points of libqflex_host.so (the C++ host layer:
+ * parsers, network builder, planner, executor).  These are what a language
+ * binding (ctypes, pybind's qflex.simulate, cgo ...) calls; they wrap
+ * qflex::EvaluateCircuit (reference src/evaluate_circuit.h:81-82) and its
+ * resident variant.  Inputs are the TEXTS of the three qFlex files, exactly what
+ * QflexCircuit/QflexOrdering/QflexGrid::load(std::istream&) consume
+ * (reference src/circuit.h:26-35, src/ordering.h:13-19, src/grid.h:13-20).
+ *
+ * Errors: functions return -1 (or NULL) and copy the reference-style error
+ * string ("ERROR (file: function:line) --> ...") into err.
+ */
+#ifndef QFLEX_B200_HOST_H_
+#define QFLEX_B200_HOST_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QFLEX_B200_N_STATS 16
+/* stats_out layout (doubles):
+ *  [0] seconds_upload   [1] seconds_flatten   [2] seconds_contract (host wall)
+ *  [3] device_ms_contract (CUDA events)       [4] leaves executed on this rank
+ *  [5] kernel launches in the last Contract() [6] algorithmic flops executed
+ *  [7] algorithmic bytes executed             [8] arena bytes
+ *  [9] flops of one pass over the schedule    [10] bytes of one pass
+ *  [11] gemm (FFMA) launches [12] gemm (tensor core) launches
+ *  [13] reduce launches      [14] permute launches   [15] number of amplitudes
+ */
+
+/* One-shot EvaluateCircuit.  states_out receives the output bitstrings joined
+ * by '\n'; amps_out receives 2*n doubles (re, im).  Returns n >= 0 or -1. */
+long qflex_b200_evaluate(const char* circuit_text, const char* ordering_text,
+                         const char* grid_text, const char* initial_state,
+                         const char* final_state, uint64_t memory_limit_bytes,
+                         int device, int rank, int world, int precision,
+                         char* states_out, uint64_t states_cap, double* amps_out,
+                         uint64_t amps_cap_complex, double* stats_out, char* err,
+                         uint64_t err_cap);
+
+/* Resident variant: parse + plan + upload + flatten once ... */
+void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
+                         const char* grid_text, const char* initial_state,
+                         const char* final_state, uint64_t memory_limit_bytes,
+                         int device, int precision, char* err, uint64_t err_cap);
+/* ... then run the contraction schedule any number of times.  Only the slices
+ * dealt to `rank` of `world` are executed; sum the partial amplitudes across
+ * ranks (NCCL all-reduce).  Returns the number of amplitudes or -1. */
+long qflex_b200_contract(void* prepared, int rank, int world, double* amps_out,
+                         uint64_t amps_cap_complex, double* stats_out, char* err,
+                         uint64_t err_cap);
+/* Re-run the host->device upload of the gate tensors and the device-side
+ * flatten (used to time the full host-buffer path). */
+long qflex_b200_reload(void* prepared, char* err, uint64_t err_cap);
+long qflex_b200_states(void* prepared, char* states_out, uint64_t states_cap);
+/* Text dump of the plan, one step per line:
+ * "<phase> <level> <kind> <m_bits> <n_bits> <k_bits> <label>". Returns bytes
+ * needed (including NUL). */
+long qflex_b200_describe(void* prepared, char* out, uint64_t cap);
+void qflex_b200_release(void* prepared);
+
+/* verbosity of the host layer (reference global::verbose, src/global.h:9). */
+void qflex_b200_set_verbose(int level);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QFLEX_B200_HOST_H_ */

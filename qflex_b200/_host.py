@@ -1,0 +1,250 @@
+"""ctypes binding of libqflex_host.so (include/qflex_b200_host.h).
+
+Mirrors the reference's Python entry point ``qflex.simulate(options)``
+(reference src/pybind_main.cpp:27-138): same option keys, same return type
+(list of (bitstring, complex)), errors printed to stderr and an empty list
+returned.  ``HostLibrary.evaluate`` is the raising variant used by tests.
+"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+
+N_STATS = 16
+STAT_NAMES = (
+    "seconds_upload", "seconds_flatten", "seconds_contract", "device_ms_contract",
+    "leaves", "launches", "flops", "bytes", "arena_bytes", "flops_per_pass",
+    "bytes_per_pass", "launches_gemm_ffma", "launches_gemm_tc", "launches_reduce",
+    "launches_permute", "n_amplitudes",
+)
+PRECISIONS = {"auto": 0, "ffma": 1, "bf16x3": 2}
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+DEFAULT_HOST_LIB = os.path.join(_HERE, "libqflex_host.so")
+
+
+class QflexError(RuntimeError):
+    pass
+
+
+def _text(x):
+    """Accepts a filename-less text: str, or an iterable of lines."""
+    if x is None:
+        return b""
+    if isinstance(x, bytes):
+        return x
+    if isinstance(x, str):
+        return x.encode()
+    return "\n".join(str(l).rstrip("\n") for l in x).encode()
+
+
+def _memory_bytes(m):
+    if m is None:
+        return 1 << 30
+    if isinstance(m, int):
+        if m <= 0:
+            raise QflexError("'memory_limit' must be positive.")
+        return m
+    s = "".join(str(m).split()).upper()
+    num = ""
+    while s and s[0].isdigit():
+        num, s = num + s[0], s[1:]
+    scale = {"GB": 1 << 30, "MB": 1 << 20, "KB": 1 << 10, "B": 1, "": 1}
+    if s not in scale:
+        raise QflexError("Suffix %s not recognized." % s)
+    return int(num) * scale[s]
+
+
+class Prepared:
+    """A circuit resident on one GPU: contract() can be called repeatedly."""
+
+    def __init__(self, lib, handle):
+        self._lib = lib
+        self._h = handle
+        n = lib._c.qflex_b200_states(handle, None, 0)
+        buf = ctypes.create_string_buffer(n)
+        lib._c.qflex_b200_states(handle, buf, n)
+        self.states = buf.value.decode().split("\n")
+        self.stats = {}
+
+    def contract(self, rank=0, world=1):
+        n = len(self.states)
+        amps = np.zeros(2 * n, dtype=np.float64)
+        stats = np.zeros(N_STATS, dtype=np.float64)
+        err = ctypes.create_string_buffer(1 << 16)
+        rc = self._lib._c.qflex_b200_contract(
+            self._h, rank, world, amps.ctypes.data_as(ctypes.c_void_p), n,
+            stats.ctypes.data_as(ctypes.c_void_p), err, len(err))
+        if rc < 0:
+            raise QflexError(err.value.decode())
+        self.stats = dict(zip(STAT_NAMES, stats.tolist()))
+        return amps.view(np.complex128)
+
+    def reload(self):
+        err = ctypes.create_string_buffer(1 << 16)
+        if self._lib._c.qflex_b200_reload(self._h, err, len(err)) < 0:
+            raise QflexError(err.value.decode())
+
+    def describe(self):
+        n = self._lib._c.qflex_b200_describe(self._h, None, 0)
+        buf = ctypes.create_string_buffer(n)
+        self._lib._c.qflex_b200_describe(self._h, buf, n)
+        rows = []
+        for line in buf.value.decode().splitlines():
+            phase, level, kind, m, n_, k, label = line.split(" ", 6)
+            rows.append(dict(phase=phase, level=int(level), kind=kind, m_bits=int(m),
+                             n_bits=int(n_), k_bits=int(k), label=label))
+        return rows
+
+    def close(self):
+        if self._h:
+            self._lib._c.qflex_b200_release(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class HostLibrary:
+    def __init__(self, path=DEFAULT_HOST_LIB):
+        if not os.path.exists(path):
+            raise QflexError(
+                "%s not found: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (there is no Python/CPU fallback)" % path)
+        self.path = path
+        c = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        c.qflex_b200_evaluate.restype = ctypes.c_long
+        c.qflex_b200_evaluate.argtypes = [
+            ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
+            ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+            ctypes.c_int, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p,
+            ctypes.c_uint64, ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_prepare.restype = ctypes.c_void_p
+        c.qflex_b200_prepare.argtypes = [
+            ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
+            ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int,
+            ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_contract.restype = ctypes.c_long
+        c.qflex_b200_contract.argtypes = [
+            ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+            ctypes.c_uint64, ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_reload.restype = ctypes.c_long
+        c.qflex_b200_reload.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_states.restype = ctypes.c_long
+        c.qflex_b200_states.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_describe.restype = ctypes.c_long
+        c.qflex_b200_describe.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_release.restype = None
+        c.qflex_b200_release.argtypes = [ctypes.c_void_p]
+        c.qflex_b200_set_verbose.restype = None
+        c.qflex_b200_set_verbose.argtypes = [ctypes.c_int]
+        self._c = c
+
+    def set_verbose(self, level):
+        self._c.qflex_b200_set_verbose(int(level))
+
+    def prepare(self, circuit, ordering, grid, initial_state="", final_state="",
+                memory_limit=None, device=0, precision="auto"):
+        err = ctypes.create_string_buffer(1 << 16)
+        h = self._c.qflex_b200_prepare(
+            _text(circuit), _text(ordering), _text(grid), _text(initial_state),
+            _text(final_state), _memory_bytes(memory_limit), device,
+            PRECISIONS[precision], err, len(err))
+        if not h:
+            raise QflexError(err.value.decode())
+        return Prepared(self, h)
+
+    def evaluate(self, circuit, ordering, grid, initial_state="", final_state="",
+                 memory_limit=None, device=0, rank=0, world=1, precision="auto",
+                 max_amplitudes=1 << 20):
+        """EvaluateCircuit: returns ([(bitstring, complex)], stats dict)."""
+        cap = max_amplitudes
+        amps = np.zeros(2 * cap, dtype=np.float64)
+        stats = np.zeros(N_STATS, dtype=np.float64)
+        states = ctypes.create_string_buffer(cap * 128 if cap < 4096 else cap * 64)
+        err = ctypes.create_string_buffer(1 << 16)
+        n = self._c.qflex_b200_evaluate(
+            _text(circuit), _text(ordering), _text(grid), _text(initial_state),
+            _text(final_state), _memory_bytes(memory_limit), device, rank, world,
+            PRECISIONS[precision], states, len(states),
+            amps.ctypes.data_as(ctypes.c_void_p), cap,
+            stats.ctypes.data_as(ctypes.c_void_p), err, len(err))
+        if n < 0:
+            raise QflexError(err.value.decode())
+        names = states.value.decode().split("\n")
+        vals = amps[: 2 * n].view(np.complex128)
+        return list(zip(names, [complex(v) for v in vals])), dict(zip(STAT_NAMES, stats.tolist()))
+
+
+def _load_option(options, key):
+    """options[key] = iterable of lines, or options[key + '_filename'] = path
+    (reference LoadData, src/pybind_main.cpp:27-42)."""
+    if key in options:
+        v = options[key]
+        if isinstance(v, (str, bytes)) or not hasattr(v, "__iter__"):
+            raise QflexError("'%s' must be a list of strings." % key)
+        return _text(v)
+    fkey = key + "_filename"
+    if fkey in options:
+        if not isinstance(options[fkey], str):
+            raise QflexError("'%s_filename' must be a string." % key)
+        try:
+            with open(options[fkey], "rb") as f:
+                return f.read()
+        except OSError:
+            raise QflexError("Cannot open %s file %s." % (key, options[fkey]))
+    return b""
+
+
+def _load_state(options, key):
+    if key + "_states" in options:
+        v = options[key + "_states"]
+        v = [v] if isinstance(v, str) else list(v)
+        if not all(isinstance(x, str) for x in v):
+            raise QflexError("states must be strings.")
+        return v
+    if key + "_state" in options:
+        if not isinstance(options[key + "_state"], str):
+            raise QflexError("states must be strings.")
+        return [options[key + "_state"]]
+    return [""]
+
+
+def simulate(options, lib=None):
+    """qflex.simulate(options) on the B200 engine.
+
+    Keys (as in the reference): circuit / circuit_filename, ordering /
+    ordering_filename, grid / grid_filename, initial_state(s), final_state(s),
+    memory_limit.  Additive keys: device, rank, world, precision.
+    Errors are printed to stderr and [] is returned (src/pybind_main.cpp:127-137).
+    """
+    try:
+        lib = lib or default_library()
+        initial = _load_state(options, "initial")
+        final = _load_state(options, "final")
+        if len(initial) != 1 or len(final) != 1:
+            raise QflexError("Not yet supported")
+        result, _ = lib.evaluate(
+            _load_option(options, "circuit"), _load_option(options, "ordering"),
+            _load_option(options, "grid"), initial[0], final[0],
+            memory_limit=options.get("memory_limit"), device=options.get("device", 0),
+            rank=options.get("rank", 0), world=options.get("world", 1),
+            precision=options.get("precision", "auto"))
+        return result
+    except QflexError as e:
+        print(e, file=sys.stderr)
+        return []
+
+
+_default = None
+
+
+def default_library():
+    global _default
+    if _default is None:
+        _default = HostLibrary()
+    return _default

@@ -1,0 +1,251 @@
+// C ABI of libqflex_b200.so: context, arena, transfers, amplitude table.
+// See include/qflex_b200.h for the reference interfaces each entry replaces.
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "qfx_internal.h"
+
+namespace {
+thread_local std::string g_last_error = "";
+}
+
+void qfx_set_error(const std::string& msg) { g_last_error = msg; }
+
+int qfx_fail_cuda(cudaError_t e, const char* what) {
+  g_last_error = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
+  return QFX_ERR_CUDA;
+}
+
+int qfx_ensure_ws(qfx_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->ws_bytes) return QFX_OK;
+  // The workspace may still be in use by earlier launches on the stream.
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->ws) QFX_CUDA(cudaFree(ctx->ws));
+  ctx->ws = nullptr;
+  ctx->ws_bytes = 0;
+  size_t want = bytes < (1u << 20) ? (1u << 20) : bytes;
+  cudaError_t e = cudaMalloc(&ctx->ws, want);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    qfx_set_error("out of device memory allocating the split-K workspace");
+    return QFX_ERR_OOM;
+  }
+  ctx->ws_bytes = want;
+  return QFX_OK;
+}
+
+extern "C" {
+
+const char* qfx_last_error(void) { return g_last_error.c_str(); }
+
+int qfx_device_count(int* n_out) {
+  if (n_out == nullptr) {
+    qfx_set_error("qfx_device_count: null argument");
+    return QFX_ERR_ARG;
+  }
+  int n = 0;
+  QFX_CUDA(cudaGetDeviceCount(&n));
+  *n_out = n;
+  return QFX_OK;
+}
+
+int qfx_create(int device, qfx_ctx** ctx_out) {
+  if (ctx_out == nullptr) {
+    qfx_set_error("qfx_create: null argument");
+    return QFX_ERR_ARG;
+  }
+  *ctx_out = nullptr;
+  int n = 0;
+  QFX_CUDA(cudaGetDeviceCount(&n));
+  if (device < 0 || device >= n) {
+    qfx_set_error("qfx_create: no such CUDA device (this library has no CPU path)");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  QFX_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    qfx_set_error(std::string("qfx_create: device '") + prop.name +
+                  "' is not sm_100-class; this library is built for sm_100a only");
+    return QFX_ERR_ARG;
+  }
+  qfx_ctx* ctx = new (std::nothrow) qfx_ctx();
+  if (ctx == nullptr) {
+    qfx_set_error("qfx_create: host allocation failed");
+    return QFX_ERR_OOM;
+  }
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  QFX_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  QFX_CUDA(cudaEventCreate(&ctx->ev0));
+  QFX_CUDA(cudaEventCreate(&ctx->ev1));
+  *ctx_out = ctx;
+  return QFX_OK;
+}
+
+int qfx_destroy(qfx_ctx* ctx) {
+  if (ctx == nullptr) return QFX_OK;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->arena) cudaFree(ctx->arena);
+  if (ctx->amps) cudaFree(ctx->amps);
+  if (ctx->ws) cudaFree(ctx->ws);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return QFX_OK;
+}
+
+int qfx_sync(qfx_ctx* ctx) {
+  if (ctx == nullptr) {
+    qfx_set_error("qfx_sync: null context");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return QFX_OK;
+}
+
+int qfx_arena_reserve(qfx_ctx* ctx, uint64_t n_elems) {
+  if (ctx == nullptr) {
+    qfx_set_error("qfx_arena_reserve: null context");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaSetDevice(ctx->device));
+  if (n_elems <= ctx->arena_elems) return QFX_OK;
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->arena) QFX_CUDA(cudaFree(ctx->arena));
+  ctx->arena = nullptr;
+  ctx->arena_elems = 0;
+  cudaError_t e = cudaMalloc(&ctx->arena, n_elems * sizeof(float2));
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    char buf[160];
+    snprintf(buf, sizeof(buf),
+             "out of device memory: arena of %.2f GB does not fit this GPU",
+             (double)n_elems * 8.0 / (1024.0 * 1024.0 * 1024.0));
+    qfx_set_error(buf);
+    return QFX_ERR_OOM;
+  }
+  ctx->arena_elems = n_elems;
+  return QFX_OK;
+}
+
+int qfx_arena_size(qfx_ctx* ctx, uint64_t* n_elems_out) {
+  if (ctx == nullptr || n_elems_out == nullptr) {
+    qfx_set_error("qfx_arena_size: null argument");
+    return QFX_ERR_ARG;
+  }
+  *n_elems_out = ctx->arena_elems;
+  return QFX_OK;
+}
+
+int qfx_upload(qfx_ctx* ctx, uint64_t off, const float* host, uint64_t n_elems) {
+  if (ctx == nullptr || host == nullptr || off + n_elems > ctx->arena_elems) {
+    qfx_set_error("qfx_upload: bad argument or span outside the arena");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaMemcpyAsync(ctx->arena + off, host, n_elems * sizeof(float2),
+                           cudaMemcpyHostToDevice, ctx->stream));
+  // pageable host memory: the copy is staged before return, but keep the
+  // contract simple -- the host buffer may be reused once this returns.
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return QFX_OK;
+}
+
+int qfx_download(qfx_ctx* ctx, uint64_t off, float* host, uint64_t n_elems) {
+  if (ctx == nullptr || host == nullptr || off + n_elems > ctx->arena_elems) {
+    qfx_set_error("qfx_download: bad argument or span outside the arena");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaMemcpyAsync(host, ctx->arena + off, n_elems * sizeof(float2),
+                           cudaMemcpyDeviceToHost, ctx->stream));
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return QFX_OK;
+}
+
+int qfx_copy(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off, uint64_t n_elems) {
+  if (ctx == nullptr || src_off + n_elems > ctx->arena_elems ||
+      dst_off + n_elems > ctx->arena_elems) {
+    qfx_set_error("qfx_copy: bad argument or span outside the arena");
+    return QFX_ERR_ARG;
+  }
+  if (n_elems == 0 || src_off == dst_off) return QFX_OK;
+  QFX_CUDA(cudaMemcpyAsync(ctx->arena + dst_off, ctx->arena + src_off,
+                           n_elems * sizeof(float2), cudaMemcpyDeviceToDevice,
+                           ctx->stream));
+  ctx->stats.launches_copy++;
+  return QFX_OK;
+}
+
+int qfx_contract(qfx_ctx* ctx, const qfx_contract_desc* desc) {
+  return qfx_launch_contract(ctx, desc, false, 0);
+}
+
+int qfx_dot_accumulate(qfx_ctx* ctx, const qfx_contract_desc* desc, uint64_t slot) {
+  return qfx_launch_contract(ctx, desc, true, slot);
+}
+
+int qfx_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off, int32_t n_bits,
+                const int8_t* dst_pos) {
+  return qfx_launch_permute(ctx, src_off, dst_off, n_bits, dst_pos);
+}
+
+int qfx_amps_reserve(qfx_ctx* ctx, uint64_t n_amps) {
+  if (ctx == nullptr || n_amps == 0) {
+    qfx_set_error("qfx_amps_reserve: bad argument");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaSetDevice(ctx->device));
+  if (n_amps > ctx->n_amps) {
+    QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->amps) QFX_CUDA(cudaFree(ctx->amps));
+    ctx->amps = nullptr;
+    ctx->n_amps = 0;
+    QFX_CUDA(cudaMalloc(&ctx->amps, n_amps * sizeof(double2)));
+    ctx->n_amps = n_amps;
+  }
+  QFX_CUDA(cudaMemsetAsync(ctx->amps, 0, ctx->n_amps * sizeof(double2), ctx->stream));
+  return QFX_OK;
+}
+
+int qfx_amps_download(qfx_ctx* ctx, double* host, uint64_t n_amps) {
+  if (ctx == nullptr || host == nullptr || n_amps > ctx->n_amps) {
+    qfx_set_error("qfx_amps_download: bad argument");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaMemcpyAsync(host, ctx->amps, n_amps * sizeof(double2),
+                           cudaMemcpyDeviceToHost, ctx->stream));
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return QFX_OK;
+}
+
+int qfx_timer_start(qfx_ctx* ctx) {
+  if (ctx == nullptr) return QFX_ERR_ARG;
+  QFX_CUDA(cudaEventRecord(ctx->ev0, ctx->stream));
+  return QFX_OK;
+}
+
+int qfx_timer_stop_ms(qfx_ctx* ctx, float* ms_out) {
+  if (ctx == nullptr || ms_out == nullptr) return QFX_ERR_ARG;
+  QFX_CUDA(cudaEventRecord(ctx->ev1, ctx->stream));
+  QFX_CUDA(cudaEventSynchronize(ctx->ev1));
+  QFX_CUDA(cudaEventElapsedTime(ms_out, ctx->ev0, ctx->ev1));
+  return QFX_OK;
+}
+
+int qfx_stats_get(qfx_ctx* ctx, qfx_stats* out) {
+  if (ctx == nullptr || out == nullptr) return QFX_ERR_ARG;
+  *out = ctx->stats;
+  return QFX_OK;
+}
+
+int qfx_stats_reset(qfx_ctx* ctx) {
+  if (ctx == nullptr) return QFX_ERR_ARG;
+  ctx->stats = qfx_stats{};
+  return QFX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,747 @@
+// Pairwise tensor contraction kernels (FFMA path) for sm_100a.
+//
+// Replaces qflex::multiply = A.reorder + B.reorder + cblas_cgemm/cgemv/cdotu
+// (reference src/tensor.cpp:1045-1194, 960-1042).  The two reorder passes are
+// folded into the operand gathers: every operand is addressed through per-bit
+// position tables (include/qflex_b200.h), so a contraction reads A and B once
+// from wherever their index bits live and writes C once.
+//
+// Kernels
+//   gemm_gather<...>  shared-memory tiled complex64 GEMM on FFMA, register
+//                     tiles TMxTN per thread, double-buffered smem, 16-byte
+//                     gathered global loads ordered by operand address so that a
+//                     warp touches contiguous runs; optional split-K partials.
+//   splitk_finish     deterministic sum of split-K partials -> C.
+//   dotk / dotk_finish  contractions with <= 64 outputs (cgemv tails, cdotu):
+//                     block-wide reduction over K in fp64, optional accumulation
+//                     into a complex128 amplitude slot
+//                     (reference src/contraction_utils.cpp:352).
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "qfx_internal.h"
+
+namespace {
+
+constexpr int kMaxTileBits = 16;
+
+struct GemmArgs {
+  const float2* A;
+  const float2* B;
+  float2* C;
+  float2* ws;  // split-K partial sums, or nullptr
+  int m_bits, n_bits, k_bits;
+  int tm, tn, tk;  // runtime tile bits (<= template maxima)
+  int ks_bits;     // log2(number of K splits)
+  int8_t a_m[QFX_MAX_BITS], c_m[QFX_MAX_BITS];
+  int8_t b_n[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
+  int8_t a_k[QFX_MAX_BITS], b_k[QFX_MAX_BITS];
+  // tile element enumeration, sorted by operand address bit
+  int8_t ta_addr[kMaxTileBits], ta_smem[kMaxTileBits];
+  int8_t tb_addr[kMaxTileBits], tb_smem[kMaxTileBits];
+  int ta_n, tb_n;
+  int a_vec, b_vec, c_vec;
+};
+
+__device__ __forceinline__ float4 ldg_f4(const float2* p) {
+  return __ldg(reinterpret_cast<const float4*>(p));
+}
+
+template <int TMB, int TNB, int TKB, int TM, int TN, bool FULLK>
+__global__ void __launch_bounds__(((1 << TMB) / TM) * ((1 << TNB) / TN))
+    gemm_gather(const __grid_constant__ GemmArgs g) {
+  constexpr int BM = 1 << TMB, BN = 1 << TNB, BKMAX = 1 << TKB;
+  constexpr int TX = BN / TN, TY = BM / TM, NT = TX * TY;
+  constexpr int PA = (BM * BKMAX / 2 + NT - 1) / NT;
+  constexpr int PB = (BKMAX * BN / 2 + NT - 1) / NT;
+  static_assert(TM % 2 == 0, "TM must be even");
+  static_assert(TN == 1 || TN % 2 == 0, "TN must be 1 or even");
+
+  extern __shared__ __align__(16) float2 smem[];
+  float2* As = smem;                    // [2][BKMAX][BM]
+  float2* Bs = smem + 2 * BKMAX * BM;   // [2][BKMAX][BN]
+
+  const int tid = threadIdx.x;
+  const int tx = tid % TX, ty = tid / TX;
+  const int tk = FULLK ? TKB : g.tk;
+  const int BK = 1 << tk;
+
+  // ---- block decode: n tile fastest (CTAs sharing an A tile are adjacent)
+  unsigned bid = blockIdx.x;
+  const int ntn_bits = g.n_bits - g.tn, ntm_bits = g.m_bits - g.tm;
+  const unsigned ntile = bid & ((1u << ntn_bits) - 1u);
+  bid >>= ntn_bits;
+  const unsigned mtile = bid & ((1u << ntm_bits) - 1u);
+  bid >>= ntm_bits;
+  const unsigned split = bid;
+
+  unsigned long long baseA = 0, baseB = 0, baseC = 0;
+  for (int i = 0; i < ntm_bits; ++i) {
+    unsigned long long b = (mtile >> i) & 1u;
+    baseA |= b << g.a_m[g.tm + i];
+    baseC |= b << g.c_m[g.tm + i];
+  }
+  for (int i = 0; i < ntn_bits; ++i) {
+    unsigned long long b = (ntile >> i) & 1u;
+    baseB |= b << g.b_n[g.tn + i];
+    baseC |= b << g.c_n[g.tn + i];
+  }
+  const float2* __restrict__ Ab = g.A + baseA;
+  const float2* __restrict__ Bb = g.B + baseB;
+
+  // ---- per-thread gather slots (pairs of tile elements)
+  const int EA = 1 << (g.tm + tk), EB = 1 << (tk + g.tn);
+  unsigned gA[PA], gB[PB];
+  int sA[PA], sB[PB];
+  const int ta_n = g.tm + tk, tb_n = tk + g.tn;
+  // When the runtime tk is below TKB the host sorted tables for the runtime
+  // tile, so ta_n/tb_n bits are exactly the populated entries.
+#pragma unroll
+  for (int j = 0; j < PA; ++j) {
+    const unsigned e0 = 2u * (tid + j * NT);
+    unsigned go = 0;
+    int so = 0;
+    for (int i = 1; i < ta_n; ++i) {
+      const unsigned b = (e0 >> i) & 1u;
+      go |= b << g.ta_addr[i];
+      so |= b << g.ta_smem[i];
+    }
+    gA[j] = go;
+    sA[j] = so;
+  }
+#pragma unroll
+  for (int j = 0; j < PB; ++j) {
+    const unsigned e0 = 2u * (tid + j * NT);
+    unsigned go = 0;
+    int so = 0;
+    for (int i = 1; i < tb_n; ++i) {
+      const unsigned b = (e0 >> i) & 1u;
+      go |= b << g.tb_addr[i];
+      so |= b << g.tb_smem[i];
+    }
+    gB[j] = go;
+    sB[j] = so;
+  }
+  const unsigned dA = ta_n > 0 ? (1u << g.ta_addr[0]) : 0u;
+  const unsigned dB = tb_n > 0 ? (1u << g.tb_addr[0]) : 0u;
+  const int sdA = ta_n > 0 ? (1 << g.ta_smem[0]) : 0;
+  const int sdB = tb_n > 0 ? (1 << g.tb_smem[0]) : 0;
+  const bool a_vec = g.a_vec != 0, b_vec = g.b_vec != 0;
+
+  float4 ra[PA], rb[PB];
+  const int khi_bits = g.k_bits - tk;
+
+  auto ldg_tiles = [&](unsigned kc) {
+    unsigned long long kA = 0, kB = 0;
+    for (int i = 0; i < khi_bits; ++i) {
+      unsigned long long b = (kc >> i) & 1u;
+      kA |= b << g.a_k[tk + i];
+      kB |= b << g.b_k[tk + i];
+    }
+    const float2* __restrict__ Ak = Ab + kA;
+    const float2* __restrict__ Bk = Bb + kB;
+#pragma unroll
+    for (int j = 0; j < PA; ++j) {
+      const int e0 = 2 * (tid + j * NT);
+      if (e0 < EA) {
+        if (a_vec) {
+          ra[j] = ldg_f4(Ak + gA[j]);
+        } else {
+          const float2 lo = __ldg(Ak + gA[j]);
+          float2 hi = make_float2(0.f, 0.f);
+          if (e0 + 1 < EA) hi = __ldg(Ak + gA[j] + dA);
+          ra[j] = make_float4(lo.x, lo.y, hi.x, hi.y);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PB; ++j) {
+      const int e0 = 2 * (tid + j * NT);
+      if (e0 < EB) {
+        if (b_vec) {
+          rb[j] = ldg_f4(Bk + gB[j]);
+        } else {
+          const float2 lo = __ldg(Bk + gB[j]);
+          float2 hi = make_float2(0.f, 0.f);
+          if (e0 + 1 < EB) hi = __ldg(Bk + gB[j] + dB);
+          rb[j] = make_float4(lo.x, lo.y, hi.x, hi.y);
+        }
+      }
+    }
+  };
+  auto sts_tiles = [&](int buf) {
+    float2* Ad = As + buf * BKMAX * BM;
+    float2* Bd = Bs + buf * BKMAX * BN;
+#pragma unroll
+    for (int j = 0; j < PA; ++j) {
+      const int e0 = 2 * (tid + j * NT);
+      if (e0 < EA) {
+        Ad[sA[j]] = make_float2(ra[j].x, ra[j].y);
+        if (e0 + 1 < EA) Ad[sA[j] + sdA] = make_float2(ra[j].z, ra[j].w);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PB; ++j) {
+      const int e0 = 2 * (tid + j * NT);
+      if (e0 < EB) {
+        Bd[sB[j]] = make_float2(rb[j].x, rb[j].y);
+        if (e0 + 1 < EB) Bd[sB[j] + sdB] = make_float2(rb[j].z, rb[j].w);
+      }
+    }
+  };
+
+  float2 acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = make_float2(0.f, 0.f);
+
+  const unsigned nch = 1u << (khi_bits - g.ks_bits);
+  const unsigned kc0 = split * nch;
+
+  ldg_tiles(kc0);
+  sts_tiles(0);
+  __syncthreads();
+
+  for (unsigned it = 0; it < nch; ++it) {
+    const int cur = it & 1;
+    const bool more = (it + 1 < nch);
+    if (more) ldg_tiles(kc0 + it + 1);
+
+    const float2* Ac = As + cur * BKMAX * BM;
+    const float2* Bc = Bs + cur * BKMAX * BN;
+    auto kstep = [&](int kk) {
+      float2 a[TM], b[TN];
+      const float2* Ak = Ac + kk * BM;
+      const float2* Bk = Bc + kk * BN;
+#pragma unroll
+      for (int i = 0; i < TM / 2; ++i) {
+        const float4 v =
+            *reinterpret_cast<const float4*>(Ak + (i * TY + ty) * 2);
+        a[2 * i] = make_float2(v.x, v.y);
+        a[2 * i + 1] = make_float2(v.z, v.w);
+      }
+      if constexpr (TN == 1) {
+        b[0] = Bk[tx];
+      } else {
+#pragma unroll
+        for (int j = 0; j < TN / 2; ++j) {
+          const float4 v =
+              *reinterpret_cast<const float4*>(Bk + (j * TX + tx) * 2);
+          b[2 * j] = make_float2(v.x, v.y);
+          b[2 * j + 1] = make_float2(v.z, v.w);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+          acc[i][j].x = fmaf(a[i].x, b[j].x, acc[i][j].x);
+          acc[i][j].x = fmaf(-a[i].y, b[j].y, acc[i][j].x);
+          acc[i][j].y = fmaf(a[i].x, b[j].y, acc[i][j].y);
+          acc[i][j].y = fmaf(a[i].y, b[j].x, acc[i][j].y);
+        }
+    };
+    if constexpr (FULLK) {
+#pragma unroll
+      for (int kk = 0; kk < BKMAX; ++kk) kstep(kk);
+    } else {
+      for (int kk = 0; kk < BK; ++kk) kstep(kk);
+    }
+
+    if (more) sts_tiles(cur ^ 1);
+    __syncthreads();
+  }
+
+  // ---- epilogue
+  const int mvalid = 1 << g.tm, nvalid = 1 << g.tn;
+  if (g.ws == nullptr) {
+    float2* __restrict__ Cb = g.C + baseC;
+    unsigned colOff[TN];
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int nl = (TN == 1) ? tx : (((j >> 1) * TX + tx) * 2 + (j & 1));
+      unsigned o = 0;
+      for (int q = 0; q < g.tn; ++q) o |= ((nl >> q) & 1u) << g.c_n[q];
+      colOff[j] = o;
+    }
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+      const int ml = ((i >> 1) * TY + ty) * 2 + (i & 1);
+      if (ml >= mvalid) continue;
+      unsigned ro = 0;
+      for (int q = 0; q < g.tm; ++q) ro |= ((ml >> q) & 1u) << g.c_m[q];
+      if constexpr (TN == 1) {
+        if (tx < nvalid) Cb[ro + colOff[0]] = acc[i][0];
+      } else {
+#pragma unroll
+        for (int j = 0; j < TN; j += 2) {
+          const int nl = ((j >> 1) * TX + tx) * 2;
+          if (nl >= nvalid) continue;
+          if (g.c_vec) {
+            *reinterpret_cast<float4*>(Cb + ro + colOff[j]) = make_float4(
+                acc[i][j].x, acc[i][j].y, acc[i][j + 1].x, acc[i][j + 1].y);
+          } else {
+            Cb[ro + colOff[j]] = acc[i][j];
+            if (nl + 1 < nvalid) Cb[ro + colOff[j + 1]] = acc[i][j + 1];
+          }
+        }
+      }
+    }
+  } else {
+    // split-K partials: ws[split][m][n] in natural (m,n) numbering
+    float2* __restrict__ W =
+        g.ws + ((unsigned long long)split << (g.m_bits + g.n_bits));
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+      const int ml = ((i >> 1) * TY + ty) * 2 + (i & 1);
+      if (ml >= mvalid) continue;
+      const unsigned long long mg = ((unsigned long long)mtile << g.tm) | ml;
+#pragma unroll
+      for (int j = 0; j < TN; ++j) {
+        const int nl = (TN == 1) ? tx : (((j >> 1) * TX + tx) * 2 + (j & 1));
+        if (nl >= nvalid) continue;
+        const unsigned long long ng = ((unsigned long long)ntile << g.tn) | nl;
+        W[(mg << g.n_bits) | ng] = acc[i][j];
+      }
+    }
+  }
+}
+
+struct FinishArgs {
+  const float2* ws;
+  float2* C;
+  int m_bits, n_bits, splits;
+  int8_t c_m[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
+};
+
+__global__ void splitk_finish(const __grid_constant__ FinishArgs g) {
+  const unsigned long long total = 1ull << (g.m_bits + g.n_bits);
+  for (unsigned long long idx =
+           blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+       idx < total; idx += (unsigned long long)gridDim.x * blockDim.x) {
+    float2 s = make_float2(0.f, 0.f);
+    for (int sp = 0; sp < g.splits; ++sp) {
+      const float2 v = g.ws[((unsigned long long)sp << (g.m_bits + g.n_bits)) + idx];
+      s.x += v.x;
+      s.y += v.y;
+    }
+    const unsigned long long n = idx & ((1ull << g.n_bits) - 1ull);
+    const unsigned long long m = idx >> g.n_bits;
+    unsigned long long o = 0;
+    for (int q = 0; q < g.n_bits; ++q) o |= ((n >> q) & 1ull) << g.c_n[q];
+    for (int q = 0; q < g.m_bits; ++q) o |= ((m >> q) & 1ull) << g.c_m[q];
+    g.C[o] = s;
+  }
+}
+
+// ---------------------------------------------------------------- small outputs
+struct DotArgs {
+  const float2* A;
+  const float2* B;
+  float2* C;      // used when amp == nullptr
+  double2* amp;   // amplitude slot (accumulated) or nullptr
+  double2* ws;    // [outputs][splits] partials (splits > 1)
+  int m_bits, n_bits, k_bits, ks_bits;
+  int8_t a_m[QFX_MAX_BITS], c_m[QFX_MAX_BITS];
+  int8_t b_n[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
+  int8_t a_k[QFX_MAX_BITS], b_k[QFX_MAX_BITS];
+};
+
+constexpr int kDotThreads = 256;
+constexpr int kDotLoBits = 8;
+
+__device__ __forceinline__ unsigned long long dot_out_offset(const DotArgs& g,
+                                                             unsigned out) {
+  const unsigned n = out & ((1u << g.n_bits) - 1u), m = out >> g.n_bits;
+  unsigned long long o = 0;
+  for (int q = 0; q < g.n_bits; ++q) o |= (unsigned long long)((n >> q) & 1u) << g.c_n[q];
+  for (int q = 0; q < g.m_bits; ++q) o |= (unsigned long long)((m >> q) & 1u) << g.c_m[q];
+  return o;
+}
+
+__global__ void __launch_bounds__(kDotThreads)
+    dotk(const __grid_constant__ DotArgs g) {
+  const unsigned out = blockIdx.x, split = blockIdx.y;
+  const unsigned n = out & ((1u << g.n_bits) - 1u), m = out >> g.n_bits;
+  unsigned long long baseA = 0, baseB = 0;
+  for (int q = 0; q < g.m_bits; ++q) baseA |= (unsigned long long)((m >> q) & 1u) << g.a_m[q];
+  for (int q = 0; q < g.n_bits; ++q) baseB |= (unsigned long long)((n >> q) & 1u) << g.b_n[q];
+
+  const int lo_bits = g.k_bits < kDotLoBits ? g.k_bits : kDotLoBits;
+  const unsigned tid = threadIdx.x;
+  unsigned long long loA = 0, loB = 0;
+  for (int q = 0; q < lo_bits; ++q) {
+    unsigned long long b = (tid >> q) & 1u;
+    loA |= b << g.a_k[q];
+    loB |= b << g.b_k[q];
+  }
+  const bool active = tid < (1u << lo_bits);
+  const int hi_bits = g.k_bits - lo_bits;
+  const unsigned nch = 1u << (hi_bits - g.ks_bits);
+  const unsigned c0 = split * nch;
+  const float2* __restrict__ A = g.A + baseA + loA;
+  const float2* __restrict__ B = g.B + baseB + loB;
+
+  double sx = 0.0, sy = 0.0;
+  if (active) {
+    for (unsigned c = c0; c < c0 + nch; ++c) {
+      unsigned long long hA = 0, hB = 0;
+      for (int q = 0; q < hi_bits; ++q) {
+        unsigned long long b = (c >> q) & 1u;
+        hA |= b << g.a_k[lo_bits + q];
+        hB |= b << g.b_k[lo_bits + q];
+      }
+      const float2 a = __ldg(A + hA), b = __ldg(B + hB);
+      sx += (double)a.x * b.x - (double)a.y * b.y;
+      sy += (double)a.x * b.y + (double)a.y * b.x;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sx += __shfl_xor_sync(0xffffffffu, sx, o);
+    sy += __shfl_xor_sync(0xffffffffu, sy, o);
+  }
+  __shared__ double red[2][kDotThreads / 32];
+  if ((tid & 31) == 0) {
+    red[0][tid >> 5] = sx;
+    red[1][tid >> 5] = sy;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double tx_ = 0.0, ty_ = 0.0;
+    for (int w = 0; w < kDotThreads / 32; ++w) {
+      tx_ += red[0][w];
+      ty_ += red[1][w];
+    }
+    if (g.ks_bits > 0) {
+      g.ws[((unsigned long long)out << g.ks_bits) + split] = make_double2(tx_, ty_);
+    } else if (g.amp != nullptr) {
+      g.amp->x += tx_;
+      g.amp->y += ty_;
+    } else {
+      g.C[dot_out_offset(g, out)] = make_float2((float)tx_, (float)ty_);
+    }
+  }
+}
+
+__global__ void dotk_finish(const __grid_constant__ DotArgs g) {
+  const unsigned outs = 1u << (g.m_bits + g.n_bits);
+  const unsigned out = blockIdx.x * blockDim.x + threadIdx.x;
+  if (out >= outs) return;
+  double sx = 0.0, sy = 0.0;
+  const unsigned splits = 1u << g.ks_bits;
+  for (unsigned s = 0; s < splits; ++s) {
+    const double2 v = g.ws[((unsigned long long)out << g.ks_bits) + s];
+    sx += v.x;
+    sy += v.y;
+  }
+  if (g.amp != nullptr) {
+    g.amp->x += sx;
+    g.amp->y += sy;
+  } else {
+    g.C[dot_out_offset(g, out)] = make_float2((float)sx, (float)sy);
+  }
+}
+
+__global__ void scalar_accumulate_kernel(const float2* src, double2* amp) {
+  amp->x += (double)src->x;
+  amp->y += (double)src->y;
+}
+
+// ---------------------------------------------------------------- host side
+template <int TMB, int TNB, int TKB, int TM, int TN>
+int launch_gemm_cfg(qfx_ctx* ctx, GemmArgs& g, unsigned blocks) {
+  constexpr int BM = 1 << TMB, BN = 1 << TNB, BKMAX = 1 << TKB;
+  constexpr int NT = (BM / TM) * (BN / TN);
+  constexpr size_t smem = 2ull * BKMAX * (BM + BN) * sizeof(float2);
+  static bool attr_full = false, attr_part = false;
+  if (g.tk == TKB) {
+    auto kern = gemm_gather<TMB, TNB, TKB, TM, TN, true>;
+    if (!attr_full) {
+      QFX_CUDA(cudaFuncSetAttribute(
+          kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_full = true;
+    }
+    kern<<<blocks, NT, smem, ctx->stream>>>(g);
+  } else {
+    auto kern = gemm_gather<TMB, TNB, TKB, TM, TN, false>;
+    if (!attr_part) {
+      QFX_CUDA(cudaFuncSetAttribute(
+          kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_part = true;
+    }
+    kern<<<blocks, NT, smem, ctx->stream>>>(g);
+  }
+  QFX_CUDA(cudaGetLastError());
+  return QFX_OK;
+}
+
+struct TileBit {
+  int addr, smem;
+};
+
+void build_tile_table(const int8_t* row_addr, int trow, const int8_t* k_addr,
+                      int tk, int k_smem_shift, int8_t* out_addr,
+                      int8_t* out_smem, int* vec) {
+  std::vector<TileBit> bits;
+  for (int q = 0; q < trow; ++q) bits.push_back({row_addr[q], q});
+  for (int q = 0; q < tk; ++q) bits.push_back({k_addr[q], k_smem_shift + q});
+  std::sort(bits.begin(), bits.end(),
+            [](const TileBit& x, const TileBit& y) { return x.addr < y.addr; });
+  for (size_t i = 0; i < bits.size(); ++i) {
+    out_addr[i] = (int8_t)bits[i].addr;
+    out_smem[i] = (int8_t)bits[i].smem;
+  }
+  *vec = (!bits.empty() && bits[0].addr == 0) ? 1 : 0;
+}
+
+// Positions of one operand must be distinct and < 32.  Returns the OR of all
+// position bits (the operand's extent minus one) or ~0 on error.
+uint64_t operand_mask(const int8_t* p1, int n1, const int8_t* p2, int n2) {
+  uint64_t seen = 0;
+  for (int i = 0; i < n1; ++i) {
+    if (p1[i] < 0 || p1[i] >= 32 || (seen >> p1[i]) & 1) return ~0ull;
+    seen |= 1ull << p1[i];
+  }
+  for (int i = 0; i < n2; ++i) {
+    if (p2[i] < 0 || p2[i] >= 32 || (seen >> p2[i]) & 1) return ~0ull;
+    seen |= 1ull << p2[i];
+  }
+  return seen;
+}
+
+}  // namespace
+
+int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
+                        bool accumulate_amp, uint64_t slot) {
+  if (ctx == nullptr || din == nullptr) {
+    qfx_set_error("qfx_contract: null argument");
+    return QFX_ERR_ARG;
+  }
+  qfx_contract_desc d = *din;
+  if (d.m_bits < 0 || d.n_bits < 0 || d.k_bits < 0 ||
+      d.m_bits + d.k_bits > 32 || d.n_bits + d.k_bits > 32 ||
+      d.m_bits + d.n_bits > 32) {
+    qfx_set_error("qfx_contract: operand rank out of range (max 32 bits each)");
+    return QFX_ERR_ARG;
+  }
+  const uint64_t mask_a = operand_mask(d.a_m, d.m_bits, d.a_k, d.k_bits);
+  const uint64_t mask_b = operand_mask(d.b_k, d.k_bits, d.b_n, d.n_bits);
+  const uint64_t mask_c = operand_mask(d.c_m, d.m_bits, d.c_n, d.n_bits);
+  if (mask_a == ~0ull || mask_b == ~0ull || mask_c == ~0ull) {
+    qfx_set_error(
+        "qfx_contract: bit positions of an operand must be distinct and < 32");
+    return QFX_ERR_ARG;
+  }
+  // spans actually touched (positions may have holes: projected/cut bits are
+  // folded into the base offset)
+  const uint64_t sa = mask_a + 1, sb = mask_b + 1, sc = mask_c + 1;
+  if (d.off_a + sa > ctx->arena_elems || d.off_b + sb > ctx->arena_elems ||
+      (!accumulate_amp && d.off_c + sc > ctx->arena_elems)) {
+    qfx_set_error("qfx_contract: operand outside the arena");
+    return QFX_ERR_ARG;
+  }
+  if (!accumulate_amp) {
+    auto overlap = [](uint64_t o1, uint64_t s1, uint64_t o2, uint64_t s2) {
+      return o1 < o2 + s2 && o2 < o1 + s1;
+    };
+    if (overlap(d.off_a, sa, d.off_c, sc) || overlap(d.off_b, sb, d.off_c, sc)) {
+      // reference: "A and C cannot be the same tensor" (src/tensor.cpp:1050-1057)
+      qfx_set_error("qfx_contract: C overlaps an input operand");
+      return QFX_ERR_ARG;
+    }
+  } else {
+    if (d.m_bits != 0 || d.n_bits != 0) {
+      // reference: "Contraction did not complete" (src/contraction_utils.cpp:348)
+      qfx_set_error("qfx_dot_accumulate: result is not a scalar");
+      return QFX_ERR_ARG;
+    }
+    if (slot >= ctx->n_amps) {
+      qfx_set_error("qfx_dot_accumulate: amplitude slot out of range");
+      return QFX_ERR_ARG;
+    }
+  }
+
+  // Larger free side plays "M" (rows); the contraction is symmetric in A/B once
+  // C is addressed through tables.
+  if (d.n_bits > d.m_bits) {
+    std::swap(d.off_a, d.off_b);
+    std::swap(d.m_bits, d.n_bits);
+    for (int i = 0; i < QFX_MAX_BITS; ++i) {
+      std::swap(d.a_m[i], d.b_n[i]);
+      std::swap(d.c_m[i], d.c_n[i]);
+      std::swap(d.a_k[i], d.b_k[i]);
+    }
+  }
+  // K enumeration order is free (it only permutes the summation): put the K
+  // bits that sit lowest in either operand first so that a K chunk covers the
+  // operands' contiguous low address bits.
+  {
+    std::vector<int> idx(d.k_bits);
+    for (int i = 0; i < d.k_bits; ++i) idx[i] = i;
+    std::stable_sort(idx.begin(), idx.end(), [&](int x, int y) {
+      return std::min(d.a_k[x], d.b_k[x]) < std::min(d.a_k[y], d.b_k[y]);
+    });
+    int8_t ak[QFX_MAX_BITS], bk[QFX_MAX_BITS];
+    for (int i = 0; i < d.k_bits; ++i) {
+      ak[i] = d.a_k[idx[i]];
+      bk[i] = d.b_k[idx[i]];
+    }
+    memcpy(d.a_k, ak, d.k_bits);
+    memcpy(d.b_k, bk, d.k_bits);
+  }
+
+  const double M = (double)(1ull << d.m_bits), N = (double)(1ull << d.n_bits),
+               K = (double)(1ull << d.k_bits);
+  ctx->stats.flops += 8.0 * M * N * K;
+  ctx->stats.bytes += 8.0 * (M * K + K * N + M * N);
+
+  const float2* A = ctx->arena + d.off_a;
+  const float2* B = ctx->arena + d.off_b;
+  float2* C = accumulate_amp ? nullptr : ctx->arena + d.off_c;
+
+  // ---------------- tiny outputs: block reduction over K
+  if (d.m_bits + d.n_bits <= 6) {
+    DotArgs g{};
+    g.A = A;
+    g.B = B;
+    g.C = C;
+    g.amp = accumulate_amp ? ctx->amps + slot : nullptr;
+    g.m_bits = d.m_bits;
+    g.n_bits = d.n_bits;
+    g.k_bits = d.k_bits;
+    memcpy(g.a_m, d.a_m, QFX_MAX_BITS);
+    memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
+    memcpy(g.b_n, d.b_n, QFX_MAX_BITS);
+    memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
+    memcpy(g.a_k, d.a_k, QFX_MAX_BITS);
+    memcpy(g.b_k, d.b_k, QFX_MAX_BITS);
+    const int outs_bits = d.m_bits + d.n_bits;
+    const int lo_bits = std::min(d.k_bits, kDotLoBits);
+    const int hi_bits = d.k_bits - lo_bits;
+    // each block should stream at least 16 chunks of 256 elements
+    int ks = 0;
+    while (ks < hi_bits - 4 && ((1 << (outs_bits + ks)) < 4 * ctx->sm_count)) ++ks;
+    g.ks_bits = ks;
+    if (ks > 0) {
+      const size_t need = sizeof(double2) << (outs_bits + ks);
+      int rc = qfx_ensure_ws(ctx, need);
+      if (rc) return rc;
+      g.ws = reinterpret_cast<double2*>(ctx->ws);
+    }
+    dim3 grid(1u << outs_bits, 1u << ks);
+    dotk<<<grid, kDotThreads, 0, ctx->stream>>>(g);
+    QFX_CUDA(cudaGetLastError());
+    ctx->stats.launches_reduce++;
+    ctx->stats.launches_total++;
+    if (ks > 0) {
+      const unsigned outs = 1u << outs_bits;
+      dotk_finish<<<(outs + 63) / 64, 64, 0, ctx->stream>>>(g);
+      QFX_CUDA(cudaGetLastError());
+      ctx->stats.launches_reduce++;
+      ctx->stats.launches_total++;
+    }
+    return QFX_OK;
+  }
+
+  // ---------------- tiled GEMM
+  GemmArgs g{};
+  g.A = A;
+  g.B = B;
+  g.C = C;
+  g.ws = nullptr;
+  g.m_bits = d.m_bits;
+  g.n_bits = d.n_bits;
+  g.k_bits = d.k_bits;
+  memcpy(g.a_m, d.a_m, QFX_MAX_BITS);
+  memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
+  memcpy(g.b_n, d.b_n, QFX_MAX_BITS);
+  memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
+  memcpy(g.a_k, d.a_k, QFX_MAX_BITS);
+  memcpy(g.b_k, d.b_k, QFX_MAX_BITS);
+
+  int TMB, TNB, TKB;
+  const int nb = d.n_bits;
+  if (nb >= 7) { TMB = 7; TNB = 7; TKB = 3; }
+  else if (nb == 6) { TMB = 7; TNB = 6; TKB = 4; }
+  else if (nb == 5) { TMB = 8; TNB = 5; TKB = 3; }
+  else if (nb == 4) { TMB = 8; TNB = 4; TKB = 3; }
+  else if (nb == 3) { TMB = 8; TNB = 3; TKB = 3; }
+  else if (nb == 2) { TMB = 8; TNB = 2; TKB = 3; }
+  else if (nb == 1) { TMB = 8; TNB = 1; TKB = 3; }
+  else { TMB = 9; TNB = 0; TKB = 3; }
+  g.tm = std::min(TMB, d.m_bits);
+  g.tn = std::min(TNB, d.n_bits);
+  g.tk = std::min(TKB, d.k_bits);
+  g.ta_n = g.tm + g.tk;
+  g.tb_n = g.tk + g.tn;
+  build_tile_table(g.a_m, g.tm, g.a_k, g.tk, TMB, g.ta_addr, g.ta_smem, &g.a_vec);
+  build_tile_table(g.b_n, g.tn, g.b_k, g.tk, TNB, g.tb_addr, g.tb_smem, &g.b_vec);
+  g.c_vec = (g.tn >= 1 && g.c_n[0] == 0) ? 1 : 0;
+  // 16-byte accesses need 16-byte aligned bases
+  if (d.off_a & 1) g.a_vec = 0;
+  if (d.off_b & 1) g.b_vec = 0;
+  if (d.off_c & 1) g.c_vec = 0;
+
+  const int tile_bits = (d.m_bits - g.tm) + (d.n_bits - g.tn);
+  const int khi_bits = d.k_bits - g.tk;
+  int ks = 0;
+  // split K when the output tiles cannot fill the GPU
+  while (ks < khi_bits - 2 && (1ll << (tile_bits + ks)) < 2ll * ctx->sm_count &&
+         (sizeof(float2) << (d.m_bits + d.n_bits + ks + 1)) <= (512ull << 20))
+    ++ks;
+  g.ks_bits = ks;
+  if (ks > 0) {
+    const size_t need = sizeof(float2) << (d.m_bits + d.n_bits + ks);
+    int rc = qfx_ensure_ws(ctx, need);
+    if (rc) return rc;
+    g.ws = reinterpret_cast<float2*>(ctx->ws);
+  }
+  const unsigned blocks = 1u << (tile_bits + ks);
+  int rc;
+  if (nb >= 7) rc = launch_gemm_cfg<7, 7, 3, 8, 8>(ctx, g, blocks);
+  else if (nb == 6) rc = launch_gemm_cfg<7, 6, 4, 8, 4>(ctx, g, blocks);
+  else if (nb == 5) rc = launch_gemm_cfg<8, 5, 3, 8, 4>(ctx, g, blocks);
+  else if (nb == 4) rc = launch_gemm_cfg<8, 4, 3, 4, 4>(ctx, g, blocks);
+  else if (nb == 3) rc = launch_gemm_cfg<8, 3, 3, 4, 2>(ctx, g, blocks);
+  else if (nb == 2) rc = launch_gemm_cfg<8, 2, 3, 4, 1>(ctx, g, blocks);
+  else if (nb == 1) rc = launch_gemm_cfg<8, 1, 3, 2, 1>(ctx, g, blocks);
+  else rc = launch_gemm_cfg<9, 0, 3, 2, 1>(ctx, g, blocks);
+  if (rc) return rc;
+  ctx->stats.launches_gemm_ffma++;
+  ctx->stats.launches_total++;
+  if (ks > 0) {
+    FinishArgs f{};
+    f.ws = g.ws;
+    f.C = C;
+    f.m_bits = d.m_bits;
+    f.n_bits = d.n_bits;
+    f.splits = 1 << ks;
+    memcpy(f.c_m, d.c_m, QFX_MAX_BITS);
+    memcpy(f.c_n, d.c_n, QFX_MAX_BITS);
+    const unsigned long long total = 1ull << (d.m_bits + d.n_bits);
+    const unsigned fb = (unsigned)std::min<unsigned long long>((total + 255) / 256,
+                                                               8ull * ctx->sm_count);
+    splitk_finish<<<fb, 256, 0, ctx->stream>>>(f);
+    QFX_CUDA(cudaGetLastError());
+    ctx->stats.launches_reduce++;
+    ctx->stats.launches_total++;
+  }
+  return QFX_OK;
+}
+
+extern "C" int qfx_scalar_accumulate(qfx_ctx* ctx, uint64_t off, uint64_t slot) {
+  if (ctx == nullptr || off >= ctx->arena_elems || slot >= ctx->n_amps) {
+    qfx_set_error("qfx_scalar_accumulate: bad argument");
+    return QFX_ERR_ARG;
+  }
+  scalar_accumulate_kernel<<<1, 1, 0, ctx->stream>>>(ctx->arena + off,
+                                                      ctx->amps + slot);
+  QFX_CUDA(cudaGetLastError());
+  ctx->stats.launches_reduce++;
+  ctx->stats.launches_total++;
+  return QFX_OK;
+}

@@ -1,0 +1,45 @@
+// Internal declarations shared by the translation units of libqflex_b200.so.
+// Nothing here is part of the ABI (see include/qflex_b200.h).
+#ifndef QFX_INTERNAL_H_
+#define QFX_INTERNAL_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "qflex_b200.h"
+
+struct qfx_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  float2* arena = nullptr;
+  uint64_t arena_elems = 0;
+  double2* amps = nullptr;
+  uint64_t n_amps = 0;
+  // split-K / reduction workspace (separate from the arena, grows on demand)
+  void* ws = nullptr;
+  size_t ws_bytes = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  qfx_stats stats{};
+};
+
+void qfx_set_error(const std::string& msg);
+int qfx_fail_cuda(cudaError_t e, const char* what);
+int qfx_ensure_ws(qfx_ctx* ctx, size_t bytes);
+
+#define QFX_CUDA(expr)                                   \
+  do {                                                   \
+    cudaError_t _e = (expr);                             \
+    if (_e != cudaSuccess) return qfx_fail_cuda(_e, #expr); \
+  } while (0)
+
+// contract.cu
+int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* d,
+                        bool accumulate_amp, uint64_t slot);
+// permute.cu
+int qfx_launch_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
+                       int n_bits, const int8_t* dst_pos);
+
+#endif  // QFX_INTERNAL_H_

@@ -1,0 +1,153 @@
+// EvaluateCircuit on the B200 engine.  Control flow follows the reference
+// driver (src/evaluate_circuit.cpp:106-253): ordering -> output states ->
+// network -> flatten -> contract -> zip(states, amplitudes); the numeric work is
+// a device plan (plan.h) instead of Tensor::multiply/reorder calls.
+#include "evaluate_circuit.h"
+
+#include <chrono>
+#include <iostream>
+
+#include "errors.h"
+
+namespace qflex {
+namespace {
+
+// Position of grid site `pos` in the string of active qubits.
+std::size_t find_output_pos(const QflexInput* input, const std::vector<std::size_t>& pos) {
+  std::size_t p = pos[0] * input->grid.J + pos[1];
+  for (const auto& off : input->grid.qubits_off)
+    if (off[0] < pos[0] || (off[0] == pos[0] && off[1] < pos[1])) --p;
+  return p;
+}
+
+double seconds_since(const std::chrono::steady_clock::time_point& t0) {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+}  // namespace
+
+std::string get_output_states(
+    const QflexInput* input, const std::list<ContractionOperation>& ordering,
+    std::vector<std::vector<std::size_t>>* final_qubits,
+    std::vector<std::string>* output_states) {
+  if (input == nullptr) throw ERROR_MSG("Input must be non-null.");
+  if (final_qubits == nullptr) throw ERROR_MSG("Final qubits must be non-null.");
+  if (output_states == nullptr) throw ERROR_MSG("Output states must be non-null");
+
+  std::string base_state = input->final_state;
+  const bool unspecified = input->final_state.empty();
+  if (unspecified) base_state = std::string(input->initial_state.length(), '0');
+
+  std::vector<std::size_t> where;
+  std::vector<std::vector<std::size_t>> what;
+  for (const auto& op : ordering) {
+    if (op.op_type != ContractionOperation::CUT || op.cut.tensors.size() != 1) continue;
+    const std::size_t p = find_output_pos(input, op.cut.tensors[0]);
+    if (unspecified) base_state[p] = 'x';
+    where.push_back(p);
+    what.push_back(op.cut.values.empty() ? std::vector<std::size_t>{0, 1} : op.cut.values);
+    final_qubits->push_back(op.cut.tensors[0]);
+  }
+  // each terminal cut multiplies the list; earlier cuts vary slowest
+  output_states->push_back(base_state);
+  for (std::size_t c = 0; c < where.size(); ++c) {
+    std::vector<std::string> grown;
+    for (const std::string& state : *output_states)
+      for (const std::size_t val : what[c]) {
+        std::string s = state;
+        s[where[c]] = std::to_string(val).at(0);
+        grown.push_back(std::move(s));
+      }
+    *output_states = std::move(grown);
+  }
+  for (std::size_t i = 0; i < output_states->at(0).length(); ++i) {
+    const char c = output_states->at(0)[i];
+    if (c != '0' && c != '1')
+      throw ERROR_MSG("Final state has non-binary character ", c, " at index ", i,
+                      "despite having no terminal cut there.");
+  }
+  return base_state;
+}
+
+std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
+                                                const DevicePlacement& where) {
+  if (input == nullptr) throw ERROR_MSG("Input must be non-null.");
+  const auto t0 = std::chrono::steady_clock::now();
+  double t_prev = 0;
+  auto lap = [&](const char* what) {
+    const double t = seconds_since(t0);
+    if (global::verbose > 0)
+      std::cerr << WARN_MSG(what, t - t_prev, "s") << std::endl;
+    t_prev = t;
+  };
+
+  std::list<ContractionOperation> ordering;
+  ordering_data_to_contraction_ordering(*input, &ordering);
+  lap("Time spent making contraction ordering: ");
+
+  const std::size_t n_active =
+      input->grid.I * input->grid.J - input->grid.qubits_off.size();
+  if (input->initial_state.empty()) input->initial_state = std::string(n_active, '0');
+
+  auto prepared = std::make_unique<PreparedCircuit>();
+  std::vector<std::vector<std::size_t>> final_qubits;
+  try {
+    input->final_state =
+        get_output_states(input, ordering, &final_qubits, &prepared->output_states);
+  } catch (const std::string& err_msg) {
+    throw ERROR_MSG("Failed to call get_output_states(). Error:\n\t[", err_msg, "]");
+  }
+
+  Plan plan = BuildPlan(*input, ordering, final_qubits);
+  plan.precision = where.precision;
+  for (auto& st : plan.steps) st.desc.precision = where.precision;
+  lap("Time spent planning the contraction: ");
+
+  const double alloc_size = (double)plan.arena_elems * sizeof(s_type);
+  if (alloc_size > (double)global::memory_limit)
+    throw ERROR_MSG("Required space (", utils::readable_memory_string(alloc_size),
+                    ") exceeds memory limit (",
+                    utils::readable_memory_string((double)global::memory_limit),
+                    "). Cancelling simulation.");
+  if (global::verbose > 0)
+    std::cerr << WARN_MSG("Allocating ", utils::readable_memory_string(alloc_size),
+                          " of device memory for this simulation.")
+              << std::endl;
+  if (plan.n_amplitudes != prepared->output_states.size())
+    throw ERROR_MSG("Planner produced ", plan.n_amplitudes, " amplitudes for ",
+                    prepared->output_states.size(), " output states.");
+
+  prepared->session = std::make_unique<Session>(std::move(plan), where.device);
+  lap("Time spent creating 2D grid of tensors on the device: ");
+  return prepared;
+}
+
+std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
+    QflexInput* input, const DevicePlacement& where, ExecStats* stats) {
+  const auto t0 = std::chrono::steady_clock::now();
+  auto prepared = PrepareCircuit(input, where);
+  std::vector<std::complex<double>> amplitudes;
+  try {
+    prepared->session->Contract(where.rank, where.world, &amplitudes);
+  } catch (const std::string& err_msg) {
+    throw ERROR_MSG("Failed to call ContractGrid(). Error:\n\t[", err_msg, "]");
+  }
+  std::vector<std::pair<std::string, std::complex<double>>> result;
+  for (std::size_t c = 0; c < amplitudes.size(); ++c)
+    result.emplace_back(prepared->output_states[c], amplitudes[c]);
+  if (stats) *stats = prepared->session->stats();
+  if (global::verbose > 0) {
+    std::cerr << WARN_MSG("Time spent contracting tensors: ",
+                          prepared->session->stats().seconds_contract, "s")
+              << std::endl;
+    std::cerr << WARN_MSG("Total time: ", seconds_since(t0), "s") << std::endl;
+  }
+  return result;
+}
+
+std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
+    QflexInput* input) {
+  return EvaluateCircuit(input, DevicePlacement{}, nullptr);
+}
+
+}  // namespace qflex

@@ -1,0 +1,54 @@
+// Drop-in entry point: same signature and semantics as the reference
+// qflex::EvaluateCircuit (src/evaluate_circuit.h:35-82,
+// src/evaluate_circuit.cpp:106-253), executed on one B200 (or on this rank's
+// share of the cut slices when a multi-GPU launcher sets rank/world).
+#ifndef QFLEX_HOST_EVALUATE_CIRCUIT_H_
+#define QFLEX_HOST_EVALUATE_CIRCUIT_H_
+
+#include <complex>
+#include <list>
+#include <memory>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "input.h"
+#include "plan.h"
+#include "schedule.h"
+
+namespace qflex {
+
+// Terminal cuts -> final qubits and the list of output bitstrings, in the order
+// the amplitudes are produced (first terminal cut = most significant).
+// Reference: src/evaluate_circuit.cpp:38-104.
+std::string get_output_states(
+    const QflexInput* input, const std::list<ContractionOperation>& ordering,
+    std::vector<std::vector<std::size_t>>* final_qubits,
+    std::vector<std::string>* output_states);
+
+// Multi-GPU placement for the additive entry points below (the reference is
+// single-process; defaults reproduce it: device 0, rank 0 of 1).
+struct DevicePlacement {
+  int device = 0;
+  int rank = 0;
+  int world = 1;
+  int precision = QFX_PREC_AUTO;
+};
+
+std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
+    QflexInput* input);
+std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
+    QflexInput* input, const DevicePlacement& where, ExecStats* stats);
+
+// Parse + plan + upload + flatten once, contract many times (what bench.py
+// times with the network resident in HBM).
+struct PreparedCircuit {
+  std::vector<std::string> output_states;
+  std::unique_ptr<Session> session;
+};
+std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
+                                                const DevicePlacement& where);
+
+}  // namespace qflex
+
+#endif  // QFLEX_HOST_EVALUATE_CIRCUIT_H_

@@ -1,0 +1,197 @@
+// extern "C" surface of libqflex_host.so (include/qflex_b200_host.h).
+#include <cstring>
+#include <exception>
+#include <sstream>
+#include <string>
+
+#include "errors.h"
+#include "evaluate_circuit.h"
+#include "qflex_b200_host.h"
+
+namespace {
+
+void set_err(char* err, uint64_t cap, const std::string& msg) {
+  if (err == nullptr || cap == 0) return;
+  const std::size_t n = std::min<std::size_t>(cap - 1, msg.size());
+  std::memcpy(err, msg.data(), n);
+  err[n] = 0;
+}
+
+void load_input(qflex::QflexInput* input, const char* circuit_text,
+                const char* ordering_text, const char* grid_text,
+                const char* initial_state, const char* final_state) {
+  input->circuit.load(std::stringstream(circuit_text ? circuit_text : ""));
+  input->ordering.load(std::stringstream(ordering_text ? ordering_text : ""));
+  input->grid.load(std::stringstream(grid_text ? grid_text : ""));
+  input->initial_state = initial_state ? initial_state : "";
+  input->final_state = final_state ? final_state : "";
+}
+
+void fill_stats(const qflex::Session& s, double* out) {
+  if (out == nullptr) return;
+  const qflex::ExecStats& e = s.stats();
+  const qflex::Plan& p = s.plan();
+  out[0] = e.seconds_upload;
+  out[1] = e.seconds_flatten;
+  out[2] = e.seconds_contract;
+  out[3] = e.device_ms_contract;
+  out[4] = (double)e.leaves;
+  out[5] = (double)e.device.launches_total;
+  out[6] = e.device.flops;
+  out[7] = e.device.bytes;
+  out[8] = (double)p.arena_elems * 8.0;
+  out[9] = p.flops_per_pass;
+  out[10] = p.bytes_per_pass;
+  out[11] = (double)e.device.launches_gemm_ffma;
+  out[12] = (double)e.device.launches_gemm_tc;
+  out[13] = (double)e.device.launches_reduce;
+  out[14] = (double)e.device.launches_permute;
+  out[15] = (double)p.n_amplitudes;
+}
+
+std::string join_states(const std::vector<std::string>& states) {
+  std::string s;
+  for (std::size_t i = 0; i < states.size(); ++i) {
+    if (i) s.push_back('\n');
+    s += states[i];
+  }
+  return s;
+}
+
+const char* kind_name(qflex::PlanStep::Kind k) {
+  switch (k) {
+    case qflex::PlanStep::CONTRACT: return "contract";
+    case qflex::PlanStep::DOT_ACCUMULATE: return "dot";
+    case qflex::PlanStep::SCALAR_ACCUMULATE: return "scalar";
+    case qflex::PlanStep::PERMUTE: return "permute";
+  }
+  return "?";
+}
+
+}  // namespace
+
+#define QFLEX_CAPI_CATCH(ret)                                   \
+  catch (const std::string& msg) {                              \
+    set_err(err, err_cap, msg);                                 \
+    return ret;                                                 \
+  }                                                             \
+  catch (const std::exception& ex) {                            \
+    set_err(err, err_cap, ex.what());                           \
+    return ret;                                                 \
+  }
+
+extern "C" {
+
+void qflex_b200_set_verbose(int level) { qflex::global::verbose = level; }
+
+void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
+                         const char* grid_text, const char* initial_state,
+                         const char* final_state, uint64_t memory_limit_bytes,
+                         int device, int precision, char* err, uint64_t err_cap) {
+  try {
+    if (memory_limit_bytes) qflex::global::memory_limit = memory_limit_bytes;
+    qflex::QflexInput input;
+    load_input(&input, circuit_text, ordering_text, grid_text, initial_state, final_state);
+    qflex::DevicePlacement where;
+    where.device = device;
+    where.precision = precision;
+    return qflex::PrepareCircuit(&input, where).release();
+  }
+  QFLEX_CAPI_CATCH(nullptr)
+}
+
+long qflex_b200_contract(void* prepared, int rank, int world, double* amps_out,
+                         uint64_t amps_cap_complex, double* stats_out, char* err,
+                         uint64_t err_cap) {
+  try {
+    if (prepared == nullptr) throw std::string("null handle");
+    auto* p = static_cast<qflex::PreparedCircuit*>(prepared);
+    std::vector<std::complex<double>> amps;
+    p->session->Contract(rank, world, &amps);
+    if (amps.size() > amps_cap_complex) throw std::string("amps_out too small");
+    for (std::size_t i = 0; i < amps.size(); ++i) {
+      amps_out[2 * i] = amps[i].real();
+      amps_out[2 * i + 1] = amps[i].imag();
+    }
+    fill_stats(*p->session, stats_out);
+    return (long)amps.size();
+  }
+  QFLEX_CAPI_CATCH(-1)
+}
+
+long qflex_b200_reload(void* prepared, char* err, uint64_t err_cap) {
+  try {
+    if (prepared == nullptr) throw std::string("null handle");
+    auto* p = static_cast<qflex::PreparedCircuit*>(prepared);
+    p->session->Upload();
+    p->session->Flatten();
+    return 0;
+  }
+  QFLEX_CAPI_CATCH(-1)
+}
+
+long qflex_b200_states(void* prepared, char* states_out, uint64_t states_cap) {
+  if (prepared == nullptr) return -1;
+  auto* p = static_cast<qflex::PreparedCircuit*>(prepared);
+  const std::string s = join_states(p->output_states);
+  if (states_out != nullptr && s.size() + 1 <= states_cap)
+    std::memcpy(states_out, s.c_str(), s.size() + 1);
+  return (long)s.size() + 1;
+}
+
+long qflex_b200_describe(void* prepared, char* out, uint64_t cap) {
+  if (prepared == nullptr) return -1;
+  auto* p = static_cast<qflex::PreparedCircuit*>(prepared);
+  std::stringstream ss;
+  auto dump = [&](const char* phase, const std::vector<qflex::PlanStep>& steps) {
+    for (const auto& st : steps)
+      ss << phase << ' ' << st.level << ' ' << kind_name(st.kind) << ' '
+         << (st.kind == qflex::PlanStep::PERMUTE ? st.n_bits : st.desc.m_bits) << ' '
+         << st.desc.n_bits << ' ' << st.desc.k_bits << ' ' << st.label << '\n';
+  };
+  dump("flatten", p->session->plan().flatten_steps);
+  dump("grid", p->session->plan().steps);
+  const std::string s = ss.str();
+  if (out != nullptr && s.size() + 1 <= cap) std::memcpy(out, s.c_str(), s.size() + 1);
+  return (long)s.size() + 1;
+}
+
+void qflex_b200_release(void* prepared) {
+  delete static_cast<qflex::PreparedCircuit*>(prepared);
+}
+
+long qflex_b200_evaluate(const char* circuit_text, const char* ordering_text,
+                         const char* grid_text, const char* initial_state,
+                         const char* final_state, uint64_t memory_limit_bytes,
+                         int device, int rank, int world, int precision,
+                         char* states_out, uint64_t states_cap, double* amps_out,
+                         uint64_t amps_cap_complex, double* stats_out, char* err,
+                         uint64_t err_cap) {
+  try {
+    if (memory_limit_bytes) qflex::global::memory_limit = memory_limit_bytes;
+    qflex::QflexInput input;
+    load_input(&input, circuit_text, ordering_text, grid_text, initial_state, final_state);
+    qflex::DevicePlacement where;
+    where.device = device;
+    where.rank = rank;
+    where.world = world;
+    where.precision = precision;
+    qflex::ExecStats stats;
+    auto prepared = qflex::PrepareCircuit(&input, where);
+    std::vector<std::complex<double>> amps;
+    prepared->session->Contract(rank, world, &amps);
+    if (amps.size() > amps_cap_complex) throw std::string("amps_out too small");
+    const std::string states = join_states(prepared->output_states);
+    if (states.size() + 1 > states_cap) throw std::string("states_out too small");
+    std::memcpy(states_out, states.c_str(), states.size() + 1);
+    for (std::size_t i = 0; i < amps.size(); ++i) {
+      amps_out[2 * i] = amps[i].real();
+      amps_out[2 * i + 1] = amps[i].imag();
+    }
+    fill_stats(*prepared->session, stats_out);
+    return (long)amps.size();
+  }
+  QFLEX_CAPI_CATCH(-1)
+}
+
+}  // extern "C"

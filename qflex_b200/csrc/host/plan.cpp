@@ -1,0 +1,683 @@
+// Planner: circuit + grid + schedule -> device steps.  See plan.h.
+#include "plan.h"
+
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <set>
+#include <unordered_map>
+#include <unordered_set>
+
+#include "errors.h"
+
+namespace qflex {
+namespace {
+
+constexpr uint64_t kAlignElems = 32;  // 256-byte alignment of every tensor
+
+uint64_t align_up(uint64_t x) { return (x + kAlignElems - 1) & ~(kAlignElems - 1); }
+
+int log2_exact(std::size_t dim) {
+  int b = 0;
+  while ((std::size_t(1) << b) < dim) ++b;
+  if ((std::size_t(1) << b) != dim)
+    throw ERROR_MSG("Dimension ", dim,
+                    " is not a power of two; the B200 engine addresses tensors "
+                    "by index bits.");
+  return b;
+}
+
+std::string tensor_to_string(const SymTensor& t) {
+  std::string s = "Tensor of rank " + std::to_string(t.idx.size()) + ", with indices {";
+  for (std::size_t i = 0; i < t.idx.size(); ++i) {
+    if (i) s += ", ";
+    s += t.idx[i].name;
+  }
+  s += "} and dimensions {";
+  for (std::size_t i = 0; i < t.idx.size(); ++i) {
+    if (i) s += ", ";
+    s += std::to_string(std::size_t(1) << t.idx[i].bits);
+  }
+  return s + "}.";
+}
+
+// C = A * B over every shared index; C indices = (A only, in A order) ++ (B only,
+// in B order), dense at c_off (reference src/tensor.cpp:1065-1087,1167-1182).
+SymTensor make_contract(const SymTensor& A, const SymTensor& B, uint64_t c_off,
+                        PlanStep* step) {
+  std::vector<const SymIndex*> left, right, common_a, common_b;
+  for (const auto& ia : A.idx) {
+    const int jb = B.find(ia.name);
+    if (jb < 0) {
+      left.push_back(&ia);
+    } else {
+      if (B.idx[jb].bits != ia.bits)
+        throw ERROR_MSG("Common indices must have matching dimensions, but at index: ",
+                        common_a.size(), ", the dimensions are A: ",
+                        (std::size_t(1) << ia.bits), ", B: ",
+                        (std::size_t(1) << B.idx[jb].bits), ".");
+      common_a.push_back(&ia);
+      common_b.push_back(&B.idx[jb]);
+    }
+  }
+  for (const auto& ib : B.idx)
+    if (A.find(ib.name) < 0) right.push_back(&ib);
+
+  SymTensor C;
+  for (const auto* l : left) C.idx.push_back(*l);
+  for (const auto* r : right) C.idx.push_back(*r);
+  C.off = c_off;
+  C.make_dense();
+
+  qfx_contract_desc& d = step->desc;
+  std::memset(&d, 0, sizeof(d));
+  d.off_a = A.off;
+  d.off_b = B.off;
+  d.off_c = c_off;
+  int m = 0, n = 0, k = 0;
+  for (std::size_t li = left.size(); li--;) {
+    const SymIndex& ci = C.idx[li];
+    for (int b = 0; b < left[li]->bits; ++b, ++m) {
+      d.a_m[m] = (int8_t)(left[li]->pos + b);
+      d.c_m[m] = (int8_t)(ci.pos + b);
+    }
+  }
+  for (std::size_t ri = right.size(); ri--;) {
+    const SymIndex& ci = C.idx[left.size() + ri];
+    for (int b = 0; b < right[ri]->bits; ++b, ++n) {
+      d.b_n[n] = (int8_t)(right[ri]->pos + b);
+      d.c_n[n] = (int8_t)(ci.pos + b);
+    }
+  }
+  for (std::size_t ki = common_a.size(); ki--;) {
+    for (int b = 0; b < common_a[ki]->bits; ++b, ++k) {
+      d.a_k[k] = (int8_t)(common_a[ki]->pos + b);
+      d.b_k[k] = (int8_t)(common_b[ki]->pos + b);
+    }
+  }
+  if (m + k > 32 || n + k > 32 || m + n > 32)
+    throw ERROR_MSG("Tensor of more than 2^32 elements in contraction.");
+  d.m_bits = m;
+  d.n_bits = n;
+  d.k_bits = k;
+  step->kind = PlanStep::CONTRACT;
+  step->var_a = A.var;
+  step->var_b = B.var;
+  const double M = (double)(1ull << m), N = (double)(1ull << n), K = (double)(1ull << k);
+  step->flops = 8.0 * M * N * K;
+  step->bytes = 8.0 * (M * K + K * N + M * N);
+  return C;
+}
+
+struct GateTensor {
+  SymTensor sym;             // dense
+  std::vector<s_type> data;
+};
+
+struct SiteNet {
+  std::vector<GateTensor> chain;                         // time order
+  std::unordered_map<std::string, std::string> virt_to_bond;
+};
+
+std::string time_leg(std::size_t i, std::size_t j, std::size_t n) {
+  return utils::concat("(", i, ",", j, "),(", n, ")");
+}
+
+GateTensor make_gate(const std::vector<std::string>& names,
+                     const std::vector<std::size_t>& dims,
+                     std::vector<s_type> data) {
+  GateTensor g;
+  std::size_t total = 1;
+  for (std::size_t q = 0; q < names.size(); ++q) {
+    SymIndex si;
+    si.name = names[q];
+    si.bits = log2_exact(dims[q]);
+    g.sym.idx.push_back(si);
+    total *= dims[q];
+  }
+  if (total != data.size())
+    throw ERROR_MSG("The total allocated space: ", total,
+                    ", is insufficient for the requested tensor dimensions: ",
+                    data.size(), ".");
+  g.sym.make_dense();
+  g.data = std::move(data);
+  return g;
+}
+
+// Gates -> per-site chains of small tensors.  Same names, dims, values and the
+// same validation as src/read_circuit.cpp:296-544.
+void build_network(const QflexInput& input,
+                   const std::vector<std::vector<std::size_t>>& final_qubits,
+                   std::vector<std::vector<SiteNet>>* net) {
+  const QflexCircuit& circuit = input.circuit;
+  const std::size_t I = input.grid.I, J = input.grid.J;
+  const auto& off = input.grid.qubits_off;
+  auto is_off = [&](std::size_t i, std::size_t j) {
+    return find_grid_coord_in_list(off, i, j);
+  };
+  const std::size_t active = I * J - off.size();
+  if (circuit.num_active_qubits != active)
+    throw ERROR_MSG("The number of active qubits read from the file: ",
+                    circuit.num_active_qubits,
+                    ", does not match the number of active qubits read from the grid: ",
+                    active, ".");
+  const std::string& initial_conf = input.initial_state;
+  const std::string& final_conf = input.final_state;
+  if (initial_conf.size() != active)
+    throw ERROR_MSG("Size of initial_conf: ", initial_conf.size(),
+                    ", must be equal to the number of qubits: ", active, ".");
+  if (final_conf.size() != initial_conf.size())
+    throw ERROR_MSG("Size of final_conf: ", final_conf.size(),
+                    ", must be equal to size of initial_conf: ",
+                    initial_conf.size(), ".");
+
+  net->assign(I, std::vector<SiteNet>(J));
+  std::vector<std::vector<std::size_t>> counter(I, std::vector<std::size_t>(J, 0));
+  std::unordered_map<std::string, std::size_t> link_counter;
+
+  std::size_t a = 0;
+  for (std::size_t q = 0; q < I * J; ++q) {
+    const std::size_t i = q / J, j = q % J;
+    if (is_off(i, j)) continue;
+    const char* delta = (initial_conf[a] == '0') ? "delta_0" : "delta_1";
+    (*net)[i][j].chain.push_back(
+        make_gate({time_leg(i, j, 0)}, {2}, gate_array(delta, {})));
+    ++a;
+  }
+  for (const auto& w : off)
+    if (w[0] >= I || w[1] >= J)
+      throw ERROR_MSG("Off qubit '(", w[0], ", ", w[1], ")' is outside the grid.");
+
+  std::unordered_set<std::size_t> busy;
+  std::size_t last_cycle = 0;
+  for (const auto& gate : circuit.gates) {
+    if (last_cycle != gate.cycle) {
+      last_cycle = gate.cycle;
+      busy.clear();
+    }
+    for (const auto q : gate.qubits)
+      if (!busy.insert(q).second)
+        throw ERROR_MSG("Qubit ", q,
+                        " has been used twice in the same cycle: ", gate.cycle);
+
+    if (gate.qubits.size() == 1) {
+      const std::size_t q1 = gate.qubits[0], i = q1 / J, j = q1 % J;
+      if (is_off(i, j))
+        throw ERROR_MSG("Qubit '", q1, "' in gate '", gate.raw,
+                        "' must correspond to an active qubit.");
+      const std::string in = time_leg(i, j, counter[i][j]);
+      const std::string out = time_leg(i, j, ++counter[i][j]);
+      try {
+        (*net)[i][j].chain.push_back(
+            make_gate({in, out}, {2, 2}, gate_array(gate.name, gate.params)));
+      } catch (const std::string& err_msg) {
+        throw ERROR_MSG("Failed to call Tensor(). Error:\n\t[", err_msg, "]");
+      }
+    } else if (gate.qubits.size() == 2) {
+      const std::size_t q1 = gate.qubits[0], q2 = gate.qubits[1];
+      const std::size_t i1 = q1 / J, j1 = q1 % J, i2 = q2 / J, j2 = q2 % J;
+      if (is_off(i1, j1))
+        throw ERROR_MSG("Qubit '", q1, "' in gate '", gate.raw,
+                        "' must correspond to an active qubit.");
+      if (is_off(i2, j2))
+        throw ERROR_MSG("Qubit '", q2, "' in gate '", gate.raw,
+                        "' must correspond to an active qubit.");
+      const std::size_t di = i1 > i2 ? i1 - i2 : i2 - i1;
+      const std::size_t dj = j1 > j2 ? j1 - j2 : j2 - j1;
+      if (di + dj != 1)
+        throw ERROR_MSG("Qubits ", q1, " and ", q2, " are not nearest neighbors.");
+
+      auto [half_1, half_2, dims] = gate_arrays(gate.name, gate.params);
+      const std::string link = index_name({i1, j1}, {i2, j2});
+      const std::size_t c = ++link_counter[link];
+      const std::size_t lo_i = std::min(i1, i2), lo_j = std::min(j1, j2);
+      const std::size_t hi_i = std::max(i1, i2), hi_j = std::max(j1, j2);
+      const std::string virt = index_name({lo_i, lo_j, c}, {hi_i, hi_j, c});
+      const std::string bond = index_name({lo_i, lo_j}, {hi_i, hi_j});
+      const std::string in_1 = time_leg(i1, j1, counter[i1][j1]);
+      const std::string in_2 = time_leg(i2, j2, counter[i2][j2]);
+      const std::string out_1 = time_leg(i1, j1, ++counter[i1][j1]);
+      const std::string out_2 = time_leg(i2, j2, ++counter[i2][j2]);
+      try {
+        (*net)[i1][j1].chain.push_back(make_gate({in_1, virt, out_1}, dims, half_1));
+        (*net)[i2][j2].chain.push_back(make_gate({in_2, virt, out_2}, dims, half_2));
+      } catch (const std::string& err_msg) {
+        throw ERROR_MSG("Failed to call Tensor(). Error:\n\t[", err_msg, "]");
+      }
+      (*net)[i1][j1].virt_to_bond[virt] = bond;
+      (*net)[i2][j2].virt_to_bond[virt] = bond;
+    } else {
+      throw ERROR_MSG("k-qubit gates with k > 2 not yet implemented.");
+    }
+  }
+
+  // close every world line: delta on fixed outputs, open "(i,j),(o)" leg on
+  // qubits with a terminal cut
+  a = 0;
+  for (std::size_t q = 0; q < I * J; ++q) {
+    const std::size_t i = q / J, j = q % J;
+    if (is_off(i, j)) continue;
+    const std::string last = time_leg(i, j, counter[i][j]);
+    if (find_grid_coord_in_list(final_qubits, i, j)) {
+      SymTensor& t = (*net)[i][j].chain.back().sym;
+      const int p = t.find(last);
+      if (p < 0) throw ERROR_MSG("old_name: ", last, ", has to be a valid index.");
+      t.idx[p].name = index_name({i, j}, {});
+    } else {
+      const char* delta = (final_conf[a] == '0') ? "delta_0" : "delta_1";
+      (*net)[i][j].chain.push_back(make_gate({last}, {2}, gate_array(delta, {})));
+    }
+    ++a;
+  }
+}
+
+// Comparator that orders the neighbours of `local` by when their bond is
+// consumed: cut bonds first (in cut order), then neighbours of the same patch
+// by expand position, then other patches by merge order
+// (semantics of order_func, src/read_circuit.cpp:191-291).
+struct NeighbourOrder {
+  const std::list<ContractionOperation>& ordering;
+  GridPos local;
+
+  std::vector<GridPos> bond_of(const GridPos& other) const {
+    if (local[0] < other[0] || local[1] < other[1]) return {local, other};
+    return {other, local};
+  }
+  bool find_expand(const GridPos& pos, std::string* patch, std::size_t* nth) const {
+    std::size_t n = 0;
+    for (const auto& op : ordering) {
+      if (op.op_type != ContractionOperation::EXPAND) continue;
+      if (op.expand.tensor == pos) {
+        *patch = op.expand.id;
+        *nth = n;
+        return true;
+      }
+      ++n;
+    }
+    return false;
+  }
+  bool operator()(const GridPos& lhs, const GridPos& rhs) const {
+    const auto lbond = bond_of(lhs), rbond = bond_of(rhs);
+    for (const auto& op : ordering) {
+      if (op.op_type != ContractionOperation::CUT) continue;
+      if (op.cut.tensors == lbond) return true;
+      if (op.cut.tensors == rbond) return false;
+    }
+    std::string lpatch, rpatch, home;
+    std::size_t lnth = 0, rnth = 0, hnth = 0;
+    if (!find_expand(lhs, &lpatch, &lnth))
+      throw ERROR_MSG("Left hand side of pair not found: (", local[0], ',', local[1],
+                      "),(", lhs[0], ',', lhs[1], ").");
+    if (!find_expand(rhs, &rpatch, &rnth))
+      throw ERROR_MSG("Right hand side of pair not found: (", local[0], ',', local[1],
+                      "),(", rhs[0], ',', rhs[1], ").");
+    if (lpatch == rpatch) return lnth < rnth;
+    find_expand(local, &home, &hnth);
+    if (lpatch == home) return true;
+    if (rpatch == home) return false;
+    for (const auto& op : ordering) {
+      if (op.op_type != ContractionOperation::MERGE) continue;
+      const auto& src = op.merge.source_id;
+      const auto& dst = op.merge.target_id;
+      if (home == src) {
+        if (lpatch == dst) return true;
+        if (rpatch == dst) return false;
+        home = dst;
+      } else if (home == dst) {
+        if (lpatch == src) return true;
+        if (rpatch == src) return false;
+      } else if (lpatch == src) {
+        lpatch = dst;
+      } else if (rpatch == src) {
+        rpatch = dst;
+      }
+    }
+    throw ERROR_MSG("Failed to compare (", lhs[0], ',', lhs[1], ") and (", rhs[0],
+                    ',', rhs[1], ") for local (", local[0], ',', local[1], ").");
+  }
+};
+
+}  // namespace
+
+Plan BuildPlan(const QflexInput& input,
+               const std::list<ContractionOperation>& ordering,
+               const std::vector<std::vector<std::size_t>>& final_qubits) {
+  Plan plan;
+  const std::size_t I = input.grid.I, J = input.grid.J;
+  const auto& off = input.grid.qubits_off;
+  auto is_off = [&](std::size_t i, std::size_t j) {
+    return find_grid_coord_in_list(off, i, j);
+  };
+
+  std::vector<std::vector<SiteNet>> net;
+  build_network(input, final_qubits, &net);
+
+  // ---------------------------------------------------------- arena: gates
+  uint64_t cursor = 0;
+  for (std::size_t i = 0; i < I; ++i)
+    for (std::size_t j = 0; j < J; ++j)
+      for (auto& g : net[i][j].chain) {
+        g.sym.off = cursor;
+        PlanUpload up;
+        up.off = cursor;
+        up.data = g.data;
+        plan.uploads.push_back(std::move(up));
+        cursor = align_up(cursor + g.sym.size());
+      }
+
+  // ------------------------------------------------- flatten: sizes first
+  plan.site.assign(I, std::vector<SymTensor>(J));
+  uint64_t max_chain = 1;
+  for (std::size_t i = 0; i < I; ++i)
+    for (std::size_t j = 0; j < J; ++j) {
+      if (is_off(i, j)) continue;
+      if (net[i][j].chain.empty()) throw ERROR_MSG("Time-direction cannot be empty");
+      SymTensor a = net[i][j].chain[0].sym;
+      for (std::size_t k = 1; k < net[i][j].chain.size(); ++k) {
+        PlanStep dummy;
+        a = make_contract(a, net[i][j].chain[k].sym, 0, &dummy);
+        max_chain = std::max(max_chain, a.size());
+      }
+      // final layout: [(o)] ++ bonds ordered by consumption
+      SymTensor& site = plan.site[i][j];
+      if (find_grid_coord_in_list(final_qubits, i, j)) {
+        SymIndex o;
+        o.name = index_name({i, j}, {});
+        o.bits = 1;
+        site.idx.push_back(o);
+      }
+      std::vector<GridPos> pairs;
+      if (i > 0 && !is_off(i - 1, j)) pairs.push_back({i - 1, j});
+      if (j > 0 && !is_off(i, j - 1)) pairs.push_back({i, j - 1});
+      if (i + 1 < I && !is_off(i + 1, j)) pairs.push_back({i + 1, j});
+      if (j + 1 < J && !is_off(i, j + 1)) pairs.push_back({i, j + 1});
+      NeighbourOrder cmp{ordering, {i, j}};
+      std::sort(pairs.begin(), pairs.end(), cmp);
+      for (const auto& p : pairs) {
+        SymIndex b;
+        b.name = (p[0] < i || p[1] < j) ? index_name(p, {i, j}) : index_name({i, j}, p);
+        b.bits = 0;
+        for (const auto& ix : a.idx) {
+          auto it = net[i][j].virt_to_bond.find(ix.name);
+          if (it != net[i][j].virt_to_bond.end() && it->second == b.name) b.bits += ix.bits;
+        }
+        site.idx.push_back(b);
+      }
+      site.make_dense();
+      if (site.rank_bits() != a.rank_bits())
+        throw ERROR_MSG("Flattened tensor at (", i, ",", j,
+                        ") has indices that are neither bonds nor outputs: ",
+                        tensor_to_string(a));
+      site.off = cursor;
+      cursor = align_up(cursor + site.size());
+    }
+  const uint64_t work_base = cursor;
+  const uint64_t ping = work_base, pong = align_up(work_base + max_chain);
+  uint64_t work_flatten = align_up(pong + max_chain) - work_base;
+
+  // ------------------------------------------------- flatten: real steps
+  for (std::size_t i = 0; i < I; ++i)
+    for (std::size_t j = 0; j < J; ++j) {
+      if (is_off(i, j)) continue;
+      const auto& chain = net[i][j].chain;
+      SymTensor a = chain[0].sym;
+      bool in_ping = false;
+      for (std::size_t k = 1; k < chain.size(); ++k) {
+        PlanStep st;
+        st.level = 0;
+        st.label = utils::concat("flatten (", i, ",", j, ") gate ", k);
+        const uint64_t dst = in_ping ? pong : ping;
+        a = make_contract(a, chain[k].sym, dst, &st);
+        st.desc.precision = QFX_PREC_FFMA;
+        in_ping = !in_ping;
+        plan.flatten_steps.push_back(std::move(st));
+      }
+      // one permute into the final layout
+      const SymTensor& site = plan.site[i][j];
+      PlanStep pm;
+      pm.kind = PlanStep::PERMUTE;
+      pm.level = 0;
+      pm.label = utils::concat("flatten (", i, ",", j, ") layout");
+      pm.src = a.off;
+      pm.dst = site.off;
+      pm.n_bits = a.rank_bits();
+      // destination position of every source index: (o) keeps its name, virtual
+      // legs land inside their bond in chronological order (first = slowest)
+      std::map<std::string, int> bond_fill;  // bits already placed, from the top
+      bool identity = true;
+      for (const auto& ix : a.idx) {
+        int dpos;
+        auto it = net[i][j].virt_to_bond.find(ix.name);
+        if (it == net[i][j].virt_to_bond.end()) {
+          const int s = site.find(ix.name);
+          if (s < 0)
+            throw ERROR_MSG("Index ", ix.name, " of flattened tensor (", i, ",", j,
+                            ") has no place in the grid tensor.");
+          dpos = site.idx[s].pos;
+        } else {
+          const int s = site.find(it->second);
+          int& used = bond_fill[it->second];
+          used += ix.bits;
+          dpos = site.idx[s].pos + site.idx[s].bits - used;
+        }
+        for (int b = 0; b < ix.bits; ++b) {
+          pm.dst_pos[ix.pos + b] = (int8_t)(dpos + b);
+          if (ix.pos + b != dpos + b) identity = false;
+        }
+      }
+      if (identity && !plan.flatten_steps.empty() && chain.size() > 1) {
+        // last world-line product can write the grid tensor directly
+        plan.flatten_steps.back().desc.off_c = site.off;
+      } else {
+        pm.bytes = 16.0 * (double)(1ull << pm.n_bits);
+        plan.flatten_steps.push_back(std::move(pm));
+      }
+    }
+
+  // ------------------------------------------------- schedule: patch sizes
+  // Symbolic replay (as ContractionData::Initialize does) to size patch slots.
+  struct Patch {
+    SymTensor cur;
+    bool active = false;
+    bool cur_in_own = false;
+    uint64_t own = 0;       // arena offset of the patch's own slot
+    uint64_t need = 0;      // largest contraction result stored for this patch
+  };
+  std::map<std::string, Patch> patches;
+  {
+    std::vector<std::vector<SymTensor>> site = plan.site;
+    std::map<std::string, SymTensor> cur;
+    std::map<std::string, bool> active;
+    for (const auto& op : ordering) {
+      if (op.op_type == ContractionOperation::EXPAND) {
+        const SymTensor& t = site[op.expand.tensor[0]][op.expand.tensor[1]];
+        patches[op.expand.id];
+        if (!active[op.expand.id]) {
+          cur[op.expand.id] = t;
+          active[op.expand.id] = true;
+        } else {
+          PlanStep dummy;
+          cur[op.expand.id] = make_contract(cur[op.expand.id], t, 0, &dummy);
+          patches[op.expand.id].need =
+              std::max(patches[op.expand.id].need, cur[op.expand.id].size());
+        }
+      } else if (op.op_type == ContractionOperation::MERGE) {
+        patches[op.merge.source_id];
+        patches[op.merge.target_id];
+        if (!active[op.merge.target_id]) {
+          cur[op.merge.target_id] = cur[op.merge.source_id];
+          active[op.merge.target_id] = true;
+        } else {
+          PlanStep dummy;
+          cur[op.merge.target_id] =
+              make_contract(cur[op.merge.source_id], cur[op.merge.target_id], 0, &dummy);
+          patches[op.merge.target_id].need =
+              std::max(patches[op.merge.target_id].need, cur[op.merge.target_id].size());
+        }
+      } else {
+        const std::string index = index_name(op.cut.tensors);
+        for (const auto& pos : op.cut.tensors) {
+          SymTensor& t = site[pos[0]][pos[1]];
+          const int p = t.find(index);
+          if (p >= 0) t.idx.erase(t.idx.begin() + p);
+        }
+      }
+    }
+  }
+  cursor = work_base;
+  std::map<uint64_t, uint64_t> spare;  // result size -> spare slot offset
+  for (auto& kv : patches) {
+    if (kv.second.need == 0) continue;
+    kv.second.own = cursor;
+    cursor = align_up(cursor + kv.second.need);
+    spare[kv.second.need] = 0;
+  }
+  for (auto& kv : spare) {
+    kv.second = cursor;
+    cursor = align_up(cursor + kv.first);
+  }
+  plan.arena_elems = std::max(cursor, work_base + work_flatten);
+
+  // ------------------------------------------------- schedule: real steps
+  std::vector<std::vector<SymTensor>> site = plan.site;
+  std::vector<std::vector<char>> site_used(I, std::vector<char>(J, 0));
+  int level = 0;
+  plan.n_amplitudes = 1;
+  bool last_was_contract = false;
+  SymTensor last_tensor;
+
+  auto store_result = [&](Patch& p, const SymTensor& A, const SymTensor& B,
+                          const std::string& label) {
+    PlanStep st;
+    st.level = level;
+    st.label = label;
+    uint64_t dst;
+    bool via_spare = false;
+    if (!p.cur_in_own) {
+      dst = p.own;
+    } else {
+      // result goes to the spare slot of this size, which then becomes the
+      // patch's slot (reference: scratch_map_ swap, contraction_utils.cpp:255-257)
+      dst = spare.at(p.need);
+      via_spare = true;
+    }
+    SymTensor c = make_contract(A, B, dst, &st);
+    st.desc.precision = plan.precision;
+    if (c.size() > p.need)
+      throw ERROR_MSG("C: ", p.need,
+                      " doesn't have enough space for the product of A*B: ", c.size(), ".");
+    if (via_spare) std::swap(p.own, spare.at(p.need));
+    p.cur = c;
+    p.cur_in_own = true;
+    plan.steps.push_back(std::move(st));
+    last_was_contract = true;
+    last_tensor = p.cur;
+  };
+
+  for (const auto& op : ordering) {
+    switch (op.op_type) {
+      case ContractionOperation::EXPAND: {
+        const std::size_t i = op.expand.tensor[0], j = op.expand.tensor[1];
+        Patch& p = patches[op.expand.id];
+        const SymTensor& next = site[i][j];
+        site_used[i][j] = 1;
+        if (!p.active) {
+          // first tensor of the patch: alias instead of the reference's copy
+          p.cur = next;
+          p.cur_in_own = false;
+          p.active = true;
+          last_was_contract = false;
+          last_tensor = p.cur;
+          break;
+        }
+        try {
+          store_result(p, p.cur, next,
+                       utils::concat("expand ", op.expand.id, " (", i, ",", j, ")"));
+        } catch (const std::string& err_msg) {
+          throw ERROR_MSG("Failed to call multiply(). Error:\n\t[", err_msg, "]");
+        }
+        break;
+      }
+      case ContractionOperation::MERGE: {
+        Patch& src = patches[op.merge.source_id];
+        Patch& dst = patches[op.merge.target_id];
+        if (!dst.active) {
+          dst.cur = src.cur;  // alias of the source patch' storage
+          dst.cur_in_own = false;
+          dst.active = true;
+          last_was_contract = false;
+          last_tensor = dst.cur;
+          break;
+        }
+        try {
+          store_result(dst, src.cur, dst.cur,
+                       utils::concat("merge ", op.merge.source_id, " ", op.merge.target_id));
+        } catch (const std::string& err_msg) {
+          throw ERROR_MSG("Failed to call multiply(). Error:\n\t[", err_msg, "]");
+        }
+        break;
+      }
+      case ContractionOperation::CUT: {
+        const std::string index = index_name(op.cut.tensors);
+        PlanCut cut;
+        cut.index = index;
+        cut.terminal = (op.cut.tensors.size() == 1);
+        cut.values = op.cut.values;
+        const int cut_id = (int)plan.cuts.size();
+        int width = -1;
+        for (const auto& pos : op.cut.tensors) {
+          SymTensor& t = site[pos[0]][pos[1]];
+          const int p = t.find(index);
+          if (p < 0 || site_used[pos[0]][pos[1]]) {
+            // the reference projects the leading index of an untouched grid
+            // tensor (src/tensor.cpp:280-285)
+            throw ERROR_MSG("Failed to call project(). Error:\n\t[Index: '", index,
+                            "' has to be equal to indices[0]: '",
+                            t.idx.empty() ? std::string("") : t.idx[0].name, "'.]");
+          }
+          width = t.idx[p].bits;
+          t.var.push_back(VarTerm{cut_id, t.idx[p].pos});
+          t.idx.erase(t.idx.begin() + p);
+        }
+        if (cut.values.empty())
+          for (std::size_t v = 0; v < (std::size_t(1) << width); ++v) cut.values.push_back(v);
+        for (const auto v : cut.values)
+          if (v >= (std::size_t(1) << width))
+            throw ERROR_MSG("Failed to call project(). Error:\n\t[index_value: ", v,
+                            " must be contained in [0, ", (std::size_t(1) << width), ").]");
+        if (cut.terminal) plan.n_amplitudes *= cut.values.size();
+        plan.cuts.push_back(std::move(cut));
+        ++level;
+        break;
+      }
+    }
+  }
+
+  // the schedule must end in a scalar, which is accumulated into the amplitude
+  // of the current output bitstring (src/contraction_utils.cpp:347-352)
+  if (ordering.empty()) throw ERROR_MSG("Empty contraction ordering.");
+  if (last_tensor.rank_bits() != 0)
+    throw ERROR_MSG("Contraction did not complete; final tensor is: ",
+                    tensor_to_string(last_tensor));
+  if (last_was_contract) {
+    plan.steps.back().kind = PlanStep::DOT_ACCUMULATE;
+  } else {
+    PlanStep st;
+    st.kind = PlanStep::SCALAR_ACCUMULATE;
+    st.level = level;
+    st.scalar_off = last_tensor.off;
+    st.var_scalar = last_tensor.var;
+    st.label = "accumulate scalar";
+    plan.steps.push_back(std::move(st));
+  }
+  if (plan.steps.back().level != level)
+    throw ERROR_MSG("Contraction ordering ends with a cut; nothing to contract after it.");
+
+  for (const auto& st : plan.steps) {
+    plan.flops_per_pass += st.flops;
+    plan.bytes_per_pass += st.bytes;
+  }
+  return plan;
+}
+
+}  // namespace qflex

@@ -1,0 +1,164 @@
+// Contraction planner: symbolic replay of network build + flatten + schedule
+// into a flat list of device steps (plan on host, execute on device).
+//
+// What it replaces in the reference, and how:
+//   circuit_data_to_tensor_network (src/read_circuit.cpp:296-544)  -> gate
+//       tensors with the same names/dims/data, uploaded once;
+//   flatten_grid_of_tensors (src/read_circuit.cpp:548-689)         -> the same
+//       world-line multiply chain per site (identical operand pairs, identical
+//       left++right result order), then ONE permute per site that lands the
+//       final [ (o), cut bonds, bonds in contraction order ] layout that the
+//       reference reaches through bundle_between + reorder;
+//   ContractionData::Initialize (src/contraction_utils.cpp:16-221)  -> arena
+//       layout (one slot per patch + one spare per distinct patch size; no
+//       reorder scratch and no cut copies are needed);
+//   ContractionData::ContractGrid (src/contraction_utils.cpp:223-354) -> steps
+//       tagged with their cut level; projections are operand base offsets,
+//       patch seeding / merge-into-empty are aliases.
+// Every tensor is described by named indices with power-of-two dimensions and
+// explicit bit positions, so reorders never run as separate passes.
+#ifndef QFLEX_HOST_PLAN_H_
+#define QFLEX_HOST_PLAN_H_
+
+#include <complex>
+#include <cstdint>
+#include <list>
+#include <string>
+#include <vector>
+
+#include "gates.h"
+#include "input.h"
+#include "qflex_b200.h"
+#include "schedule.h"
+
+namespace qflex {
+
+struct SymIndex {
+  std::string name;
+  int bits = 0;  // log2(dimension)
+  int pos = 0;   // position of the index' lowest bit in the linear offset
+};
+
+// Slice-dependent part of an operand's base: value(cut) << shift.
+struct VarTerm {
+  int cut = 0;
+  int shift = 0;
+};
+
+struct SymTensor {
+  std::vector<SymIndex> idx;  // slowest-varying first, as in the reference
+  uint64_t off = 0;           // arena offset (elements)
+  std::vector<VarTerm> var;
+  int span_bits = 0;          // log2 of the storage span addressed by `idx`+cuts
+
+  int rank_bits() const {
+    int b = 0;
+    for (const auto& i : idx) b += i.bits;
+    return b;
+  }
+  uint64_t size() const { return 1ull << rank_bits(); }
+  int find(const std::string& name) const {
+    for (std::size_t i = 0; i < idx.size(); ++i)
+      if (idx[i].name == name) return (int)i;
+    return -1;
+  }
+  // dense row-major positions from the index order
+  void make_dense() {
+    int p = 0;
+    for (std::size_t i = idx.size(); i--;) {
+      idx[i].pos = p;
+      p += idx[i].bits;
+    }
+    span_bits = p;
+  }
+  std::vector<std::string> names() const {
+    std::vector<std::string> n;
+    for (const auto& i : idx) n.push_back(i.name);
+    return n;
+  }
+};
+
+struct PlanStep {
+  enum Kind { CONTRACT, DOT_ACCUMULATE, SCALAR_ACCUMULATE, PERMUTE };
+  Kind kind = CONTRACT;
+  int level = 0;  // number of cuts that precede this step in the ordering
+  qfx_contract_desc desc{};
+  std::vector<VarTerm> var_a, var_b;
+  // PERMUTE
+  uint64_t src = 0, dst = 0;
+  int n_bits = 0;
+  int8_t dst_pos[QFX_MAX_BITS] = {0};
+  // SCALAR_ACCUMULATE
+  uint64_t scalar_off = 0;
+  std::vector<VarTerm> var_scalar;
+  // bookkeeping
+  double flops = 0, bytes = 0;
+  std::string label;
+};
+
+struct PlanCut {
+  std::vector<std::size_t> values;
+  bool terminal = false;
+  std::string index;
+};
+
+struct PlanUpload {
+  uint64_t off = 0;
+  std::vector<s_type> data;
+};
+
+struct Plan {
+  std::vector<PlanUpload> uploads;       // gate tensors
+  std::vector<PlanStep> flatten_steps;   // network -> one tensor per site
+  std::vector<PlanStep> steps;           // schedule, ordered by level
+  std::vector<PlanCut> cuts;
+  uint64_t arena_elems = 0;
+  uint64_t n_amplitudes = 1;
+  // final layout of every site tensor (for tests / parity with
+  // read_circuit_test.cpp:281-345)
+  std::vector<std::vector<SymTensor>> site;
+  double flops_per_pass = 0, bytes_per_pass = 0;  // one execution of every step
+  int precision = QFX_PREC_AUTO;
+};
+
+// Builds the full plan.  `final_qubits` = qubits with a terminal cut
+// (EvaluateCircuit passes get_output_states' list).  Throws std::string.
+Plan BuildPlan(const QflexInput& input,
+               const std::list<ContractionOperation>& ordering,
+               const std::vector<std::vector<std::size_t>>& final_qubits);
+
+struct ExecStats {
+  double seconds_upload = 0, seconds_flatten = 0, seconds_contract = 0;
+  double device_ms_contract = 0;  // CUDA events around the schedule's launches
+  uint64_t leaves = 0;            // scalar results accumulated (slices x outputs)
+  qfx_stats device{};
+};
+
+// One plan resident on one GPU: the constructor reserves the arena, uploads the
+// gate tensors and flattens the network into grid tensors; Contract() then runs
+// the schedule (any number of times).  Only the cut-slices dealt to `rank` of
+// `world` are executed (slice s -> rank s % world); partial amplitudes must be
+// summed across ranks by the caller.  Everything throws std::string.
+class Session {
+ public:
+  Session(Plan plan, int device);
+  ~Session();
+  Session(const Session&) = delete;
+  Session& operator=(const Session&) = delete;
+
+  void Upload();   // host -> device copy of the gate tensors
+  void Flatten();  // network -> grid tensors, on the device
+  void Contract(int rank, int world, std::vector<std::complex<double>>* amplitudes);
+
+  const Plan& plan() const { return plan_; }
+  const ExecStats& stats() const { return stats_; }
+
+ private:
+  Plan plan_;
+  qfx_ctx* ctx_ = nullptr;
+  ExecStats stats_;
+};
+
+}  // namespace qflex
+
+#endif  // QFLEX_HOST_PLAN_H_
