@@ -49,7 +49,7 @@ class DeviceError(RuntimeError):
 def load(path=DEFAULT_DEVICE_LIB):
     if not os.path.exists(path):
         raise DeviceError("%s not found: run __graft_entry__.build() (no CPU fallback)" % path)
-    c = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+    c = ctypes.CDLL(path)
     c.qfx_last_error.restype = ctypes.c_char_p
     u64, vp, i32 = ctypes.c_uint64, ctypes.c_void_p, ctypes.c_int32
     c.qfx_create.argtypes = [ctypes.c_int, ctypes.POINTER(vp)]

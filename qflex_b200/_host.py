@@ -116,7 +116,7 @@ class HostLibrary:
                 "%s not found: build it with `python -c 'import __graft_entry__ as g; "
                 "g.build()'` (there is no Python/CPU fallback)" % path)
         self.path = path
-        c = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        c = ctypes.CDLL(path)
         c.qflex_b200_evaluate.restype = ctypes.c_long
         c.qflex_b200_evaluate.argtypes = [
             ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,

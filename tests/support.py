@@ -1,0 +1,197 @@
+"""Shared helpers for the test-suite, bench.py's baseline legs and smoke().
+
+Holds the list of (circuit, ordering, grid) cases, access to the compiled
+reference (oracle/_ref, test infrastructure) and the CPU-emulated host library.
+"""
+import ctypes
+import os
+import re
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CONFIG = os.path.join(ROOT, "config")
+REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libqflex_ref.so")
+
+SIMPLE_CIRCUIT = """5
+0 h 0
+0 h 1
+0 h 2
+0 h 3
+0 h 5
+1 t 0
+1 t 1
+1 t 2
+1 t 3
+1 t 5
+2 cz 0 1
+3 cx 0 2
+4 cx 1 3
+5 cz 2 3
+6 cz 3 5
+11 cz 0 1
+12 cx 0 2
+13 cx 1 3
+14 cz 2 3
+15 cx 3 5
+17 h 0
+17 h 1
+17 h 2
+17 h 3
+17 h 5"""
+SIMPLE_ORDERING = """#
+cut () 1 3
+expand a 1
+expand a 0
+expand a 2
+cut () 5
+expand b 5
+expand b 3
+merge a b
+"""
+SIMPLE_GRID = "1 1\n1 1\n0 1\n"
+
+
+def restrict_cuts(ordering_text, values_per_cut):
+    """Rewrites the value list of the k-th `cut` line (k = 0, 1, ...) with
+    values_per_cut[k] (None keeps the line).  This is how a fixed subset of
+    slices is selected identically for the reference and for this engine."""
+    out, k = [], 0
+    for line in ordering_text.splitlines():
+        s = line.strip()
+        if s.startswith("cut"):
+            if k < len(values_per_cut) and values_per_cut[k] is not None:
+                vals = ",".join(str(v) for v in values_per_cut[k])
+                line = re.sub(r"\([0-9,\s]*\)", "(" + vals + ")", line, count=1)
+            k += 1
+        out.append(line)
+    return "\n".join(out) + "\n"
+
+
+# name -> files under config/ (or inline texts), optional final state
+CASES = {
+    "test": dict(circuit="test.txt", ordering="test.txt", grid="test.txt"),
+    "simple_1100x": dict(circuit_text=SIMPLE_CIRCUIT, ordering_text=SIMPLE_ORDERING,
+                         grid_text=SIMPLE_GRID, initial="00000", final="1100x"),
+    "rect2x2_0000": dict(circuit="rectangular_2x2_1-2-1_0.txt", ordering="rectangular_2x2.txt",
+                         grid="rectangular_2x2.txt", final="0000"),
+    "rect2x2_0110": dict(circuit="rectangular_2x2_1-2-1_0.txt", ordering="rectangular_2x2.txt",
+                         grid="rectangular_2x2.txt", final="0110"),
+    "sycamore_53_4": dict(circuit="sycamore_53_4_0.txt", ordering="sycamore_53.txt",
+                          grid="sycamore_53.txt"),
+    "bristlecone_70_1-12-1": dict(circuit="bristlecone_70_1-12-1_0.txt",
+                                  ordering="bristlecone_70.txt", grid="bristlecone_70.txt"),
+    "bristlecone_70_1-16-1": dict(circuit="bristlecone_70_1-16-1_0.txt",
+                                  ordering="bristlecone_70.txt", grid="bristlecone_70.txt"),
+    "bristlecone_48_1-16-1": dict(circuit="bristlecone_48_1-16-1_0.txt",
+                                  ordering="bristlecone_48.txt", grid="bristlecone_48.txt"),
+    "bristlecone_48_1-24-1": dict(circuit="bristlecone_48_1-24-1_0.txt",
+                                  ordering="bristlecone_48.txt", grid="bristlecone_48.txt"),
+    # 16 of the 4096 slices of config[1]'s little brother
+    "bristlecone_70_1-24-1_16slices": dict(
+        circuit="bristlecone_70_1-24-1_0.txt", ordering="bristlecone_70.txt",
+        grid="bristlecone_70.txt", cut_values=[[0, 1], [0, 1], [0, 1], [0, 1]]),
+}
+
+
+def _read(kind, name):
+    with open(os.path.join(CONFIG, kind, name)) as f:
+        return f.read()
+
+
+def case_texts(case):
+    c = case.get("circuit_text") or _read("circuits", case["circuit"])
+    o = case.get("ordering_text") or _read("ordering", case["ordering"])
+    g = case.get("grid_text") or _read("grid", case["grid"])
+    if case.get("cut_values"):
+        o = restrict_cuts(o, case["cut_values"])
+    return c, o, g
+
+
+_ref = None
+
+
+def reference_available():
+    return os.path.exists(REF_LIB)
+
+
+def reference_library():
+    global _ref
+    if _ref is None:
+        lib = ctypes.CDLL(REF_LIB)
+        lib.ref_evaluate.restype = ctypes.c_long
+        lib.ref_multiply.restype = ctypes.c_long
+        lib.ref_reorder.restype = ctypes.c_long
+        _ref = lib
+    return _ref
+
+
+def reference_set_threads(n):
+    reference_library().ref_set_blas_threads(int(n))
+
+
+def reference_evaluate(circuit, ordering, grid, initial="", final="", memory=64 << 30,
+                       cap=1 << 16):
+    """The reference's own EvaluateCircuit (oracle/ref_capi.cpp)."""
+    lib = reference_library()
+    amps = np.zeros(2 * cap)
+    states = ctypes.create_string_buffer(cap * 96)
+    err = ctypes.create_string_buffer(1 << 16)
+    secs = ctypes.c_double()
+    n = lib.ref_evaluate(circuit.encode(), ordering.encode(), grid.encode(), initial.encode(),
+                         final.encode(), ctypes.c_ulong(memory), states,
+                         ctypes.c_ulong(len(states)), amps.ctypes.data_as(ctypes.c_void_p),
+                         ctypes.c_ulong(cap), ctypes.byref(secs), err, ctypes.c_ulong(len(err)))
+    if n < 0:
+        raise RuntimeError(err.value.decode())
+    vals = amps[: 2 * n].view(np.complex128)
+    return list(zip(states.value.decode().split("\n"), [complex(v) for v in vals])), secs.value
+
+
+def reference_multiply(a, a_idx, a_dims, b, b_idx, b_dims):
+    """The reference's own qflex::multiply on caller data."""
+    lib = reference_library()
+    a = np.ascontiguousarray(a, dtype=np.complex64).copy()
+    b = np.ascontiguousarray(b, dtype=np.complex64).copy()
+    ad = (ctypes.c_ulong * len(a_dims))(*a_dims)
+    bd = (ctypes.c_ulong * len(b_dims))(*b_dims)
+    cap = int(np.prod(a_dims, dtype=np.int64) * np.prod(b_dims, dtype=np.int64))
+    c = np.zeros(max(cap, 1), dtype=np.complex64)
+    names = ctypes.create_string_buffer(4096)
+    cd = (ctypes.c_ulong * 64)()
+    err = ctypes.create_string_buffer(1 << 14)
+    n = lib.ref_multiply(";".join(a_idx).encode(), ad, a.ctypes.data_as(ctypes.c_void_p),
+                         ";".join(b_idx).encode(), bd, b.ctypes.data_as(ctypes.c_void_p),
+                         c.ctypes.data_as(ctypes.c_void_p), ctypes.c_ulong(c.size), names,
+                         ctypes.c_ulong(len(names)), cd, err, ctypes.c_ulong(len(err)))
+    if n < 0:
+        raise RuntimeError(err.value.decode())
+    dims = [int(cd[i]) for i in range(n)]
+    idx = names.value.decode().split(";") if n else []
+    return c[: int(np.prod(dims, dtype=np.int64)) if dims else 1], idx, dims
+
+
+def reference_reorder(data, idx, dims, new_idx):
+    lib = reference_library()
+    d = np.ascontiguousarray(data, dtype=np.complex64).copy()
+    dd = (ctypes.c_ulong * len(dims))(*dims)
+    err = ctypes.create_string_buffer(1 << 14)
+    rc = lib.ref_reorder(";".join(idx).encode(), dd, d.ctypes.data_as(ctypes.c_void_p),
+                         ";".join(new_idx).encode(), err, ctypes.c_ulong(len(err)))
+    if rc < 0:
+        raise RuntimeError(err.value.decode())
+    return d
+
+
+def emulated_host_library():
+    """Host layer linked against oracle/device_emul.cpp (CPU, tests only)."""
+    import sys
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as ge
+    from qflex_b200._host import HostLibrary
+    return HostLibrary(ge.build_emulated_host())
+
+
+def rel_err(got, want):
+    got, want = np.asarray(got), np.asarray(want)
+    return float(np.linalg.norm(got - want) / max(np.linalg.norm(want), 1e-300))

@@ -1,0 +1,89 @@
+"""End-to-end parity on the B200: EvaluateCircuit through the C ABI against the
+reference's golden amplitudes (tests/golden/amplitudes.json, generated from the
+unmodified reference by tests/golden/make_golden.py) and, when the prebuilt
+oracle/_ref travelled to the box, against the reference run live."""
+import numpy as np
+import pytest
+
+from tests import support
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4  # BASELINE.json: per-run normwise relative error of the amplitude vector
+
+
+def _amps(golden, name):
+    g = golden[name]
+    return g["states"], np.array(g["re"]) + 1j * np.array(g["im"])
+
+
+@pytest.mark.parametrize("name", list(support.CASES))
+def test_amplitudes_match_reference_golden(gpu_lib, golden, name):
+    case = support.CASES[name]
+    c, o, g = support.case_texts(case)
+    res, stats = gpu_lib.evaluate(c, o, g, case.get("initial", ""), case.get("final", ""),
+                                  memory_limit=64 << 30)
+    states, want = _amps(golden, name)
+    assert [s for s, _ in res] == states
+    err = support.rel_err([a for _, a in res], want)
+    assert err < TOL, err
+    assert stats["launches"] > 0
+
+
+@pytest.mark.parametrize("precision", ["ffma"])
+def test_precision_modes_agree(gpu_lib, golden, precision):
+    case = support.CASES["bristlecone_48_1-24-1"]
+    c, o, g = support.case_texts(case)
+    res, _ = gpu_lib.evaluate(c, o, g, memory_limit=8 << 30, precision=precision)
+    _, want = _amps(golden, "bristlecone_48_1-24-1")
+    assert support.rel_err([a for _, a in res], want) < TOL
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_rank_shares_sum_to_the_full_amplitudes(gpu_lib, golden, world):
+    case = support.CASES["bristlecone_70_1-16-1"]
+    p = gpu_lib.prepare(*support.case_texts(case), memory_limit=8 << 30)
+    full = p.contract(0, 1)
+    total = sum(p.contract(r, world) for r in range(world))
+    assert support.rel_err(total, full) < 1e-6
+    _, want = _amps(golden, "bristlecone_70_1-16-1")
+    assert support.rel_err(total, want) < TOL
+    p.close()
+
+
+def test_repeated_contract_is_deterministic(gpu_lib):
+    case = support.CASES["bristlecone_48_1-24-1"]
+    p = gpu_lib.prepare(*support.case_texts(case), memory_limit=8 << 30)
+    a1 = p.contract().copy()
+    p.reload()
+    a2 = p.contract().copy()
+    assert np.array_equal(a1, a2)
+    p.close()
+
+
+@pytest.mark.skipif(not support.reference_available(), reason="oracle/_ref did not travel")
+def test_live_reference_run_matches(gpu_lib):
+    # 4 of the 65536 slices of BASELINE configs[1] (bristlecone_70 1-32-1) would
+    # take minutes on the CPU; use its 1-24-1 sibling, 2 slices
+    case = dict(circuit="bristlecone_70_1-24-1_0.txt", ordering="bristlecone_70.txt",
+                grid="bristlecone_70.txt", cut_values=[[3], [5], [1], [0, 7]])
+    c, o, g = support.case_texts(case)
+    want, _ = support.reference_evaluate(c, o, g)
+    got, _ = gpu_lib.evaluate(c, o, g, memory_limit=8 << 30)
+    assert [s for s, _ in got] == [s for s, _ in want]
+    assert support.rel_err([a for _, a in got], [a for _, a in want]) < TOL
+
+
+def test_linearity_over_cut_values_full_size(gpu_lib):
+    # size-independent property at BASELINE configs[1] scale (bristlecone_70
+    # 1-32-1, 2^28-element patches): the amplitude of a set of slices is the sum
+    # of the amplitudes of its parts
+    base = dict(circuit="bristlecone_70_1-32-1_0.txt", ordering="bristlecone_70.txt",
+                grid="bristlecone_70.txt")
+    def run(vals):
+        c, o, g = support.case_texts(dict(base, cut_values=vals))
+        return gpu_lib.evaluate(c, o, g, memory_limit=64 << 30)[0][0][1]
+    both = run([[2], [9], [4], [0, 15]])
+    one = run([[2], [9], [4], [0]])
+    other = run([[2], [9], [4], [15]])
+    assert abs(both - (one + other)) < 1e-5 * max(abs(one), abs(other))

@@ -1,0 +1,188 @@
+"""Parity of the CUDA kernels (through the C ABI) with the oracle."""
+import numpy as np
+import pytest
+
+from oracle import kernel_oracle as ko
+from tests import support
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5  # fp32 accumulation vs the oracle evaluated in complex128, normwise
+
+
+def _rand(n, rng):
+    return (rng.uniform(-1, 1, n) + 1j * rng.uniform(-1, 1, n)).astype(np.complex64)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from qflex_b200 import _device
+    c = _device.Context(0)
+    yield c
+    c.close()
+
+
+def _random_tables(rng, m, n, k):
+    """Random placement of the m/k bits inside A, k/n inside B, m/n inside C."""
+    pa = rng.permutation(m + k)
+    pb = rng.permutation(n + k)
+    pc = rng.permutation(m + n)
+    return dict(a_m=[int(x) for x in pa[:m]], a_k=[int(x) for x in pa[m:]],
+                b_k=[int(x) for x in pb[:k]], b_n=[int(x) for x in pb[k:]],
+                c_m=[int(x) for x in pc[:m]], c_n=[int(x) for x in pc[m:]])
+
+
+def _run_contract(ctx, t, rng, off_jitter=0):
+    from qflex_b200 import _device
+    m, n, k = len(t["a_m"]), len(t["b_n"]), len(t["a_k"])
+    sa, sb, sc = 1 << (m + k), 1 << (n + k), 1 << (m + n)
+    a, b = _rand(sa, rng), _rand(sb, rng)
+    oa = off_jitter
+    ob = oa + sa + 32 + off_jitter
+    oc = ob + sb + 32 + off_jitter
+    ctx.reserve(oc + sc + 64)
+    ctx.upload(oa, a)
+    ctx.upload(ob, b)
+    ctx.upload(oc, np.zeros(sc, dtype=np.complex64))
+    ctx.contract(_device.make_desc(oa, ob, oc, t["a_m"], t["c_m"], t["b_n"], t["c_n"],
+                                   t["a_k"], t["b_k"]))
+    got = ctx.download(oc, sc)
+    want = ko.contract(a, b, acc_dtype=np.complex128, **t)
+    return support.rel_err(got, want)
+
+
+# (m_bits, n_bits, k_bits): every tile configuration, ragged tiles (m < tile),
+# split-K (small output, long K), tiny outputs (dot kernel), K = 1 and K = 2.
+SHAPES = [(0, 0, 0), (0, 0, 5), (0, 0, 14), (3, 0, 0), (1, 1, 1), (2, 3, 9), (6, 0, 12),
+          (4, 1, 1), (10, 1, 1), (11, 2, 1), (12, 3, 3), (13, 4, 4), (9, 5, 5), (12, 5, 3),
+          (8, 6, 6), (7, 6, 10), (6, 6, 8), (10, 7, 6), (8, 8, 8), (7, 7, 0), (9, 7, 12),
+          (3, 10, 4), (0, 9, 7), (14, 0, 2), (5, 4, 13), (15, 1, 0), (9, 9, 3)]
+
+
+@pytest.mark.parametrize("m,n,k", SHAPES)
+def test_contract_random_bit_placement(ctx, m, n, k):
+    rng = np.random.default_rng(1000 * m + 100 * n + k)
+    t = _random_tables(rng, m, n, k)
+    assert _run_contract(ctx, t, rng) < TOL
+
+
+@pytest.mark.parametrize("m,n,k", [(8, 6, 6), (12, 3, 3), (9, 7, 5), (0, 0, 10)])
+def test_contract_odd_base_offsets(ctx, m, n, k):
+    # cut projections shift operand bases; odd bases disable 16-byte accesses
+    rng = np.random.default_rng(7 * m + n + k)
+    t = _random_tables(rng, m, n, k)
+    assert _run_contract(ctx, t, rng, off_jitter=1) < TOL
+
+
+def test_contract_reference_multiply_golden(ctx):
+    # reference tests/src/tensor_test.cpp:496-530: {20, 14, 100, 78}
+    from qflex_b200 import _device
+    a = np.arange(8).astype(np.complex64)
+    b = np.arange(8, 0, -1).astype(np.complex64)
+    t, idx, dims = ko.bits_from_named(["a", "b", "c"], [2, 2, 2], ["b", "c", "d"], [2, 2, 2])
+    ctx.reserve(256)
+    ctx.upload(0, a)
+    ctx.upload(32, b)
+    ctx.contract(_device.make_desc(0, 32, 64, t["a_m"], t["c_m"], t["b_n"], t["c_n"],
+                                   t["a_k"], t["b_k"]))
+    np.testing.assert_allclose(ctx.download(64, 4).real, [20, 14, 100, 78])
+    assert idx == ["a", "d"] and dims == [2, 2]
+
+
+def test_contract_named_layout_as_planner_builds_it(ctx):
+    # the dominant shape family of the Bristlecone schedules: patch [.. k .. k ..]
+    # times grid tensor [k, k, r, r], d = 8 (bristlecone_48 1-24-1: 2^15 x 64 x 64)
+    rng = np.random.default_rng(5)
+    a_idx, a_dims = ["p", "x", "q", "y", "r", "s", "t"], [8] * 7
+    b_idx, b_dims = ["y", "x", "u", "v"], [8] * 4
+    t, _, _ = ko.bits_from_named(a_idx, a_dims, b_idx, b_dims)
+    assert (len(t["a_m"]), len(t["b_n"]), len(t["a_k"])) == (15, 6, 6)
+    assert _run_contract(ctx, t, rng) < TOL
+
+
+def test_contract_rejects_overlap_and_bad_tables(ctx):
+    from qflex_b200 import _device
+    ctx.reserve(1024)
+    d = _device.make_desc(0, 64, 32, [1, 2, 3, 4, 5], [0, 1, 2, 3, 4], [], [], [0], [0])
+    with pytest.raises(_device.DeviceError, match="overlaps"):
+        ctx.contract(d)
+    d = _device.make_desc(0, 64, 128, [1, 1], [0, 1], [], [], [0], [0])
+    with pytest.raises(_device.DeviceError, match="distinct"):
+        ctx.contract(d)
+    d = _device.make_desc(1000, 64, 128, [1, 2, 3, 4, 5], [0, 1, 2, 3, 4], [], [], [0], [0])
+    with pytest.raises(_device.DeviceError, match="outside the arena"):
+        ctx.contract(d)
+
+
+@pytest.mark.parametrize("k", [0, 3, 8, 13, 20])
+def test_dot_accumulate_complex128(ctx, k):
+    from qflex_b200 import _device
+    rng = np.random.default_rng(k)
+    n = 1 << k
+    a, b = _rand(n, rng), _rand(n, rng)
+    pa, pb = [int(x) for x in rng.permutation(k)], [int(x) for x in rng.permutation(k)]
+    ctx.reserve(2 * n + 64)
+    ctx.upload(0, a)
+    ctx.upload(n + 32, b)
+    ctx.amps_reserve(3)
+    d = _device.make_desc(0, n + 32, 0, [], [], [], [], pa, pb)
+    ctx.dot_accumulate(d, 1)
+    ctx.dot_accumulate(d, 1)  # accumulates
+    amps = ctx.amps(3)
+    want = ko.dot(a, b, pa, pb)
+    assert amps[0] == 0 and amps[2] == 0
+    assert abs(amps[1] - 2 * want) <= 1e-6 * max(1.0, np.sqrt(n))
+
+
+@pytest.mark.parametrize("nbits,seed", [(0, 0), (1, 0), (3, 1), (5, 2), (9, 3), (10, 4), (12, 5),
+                                        (12, 6), (16, 7), (20, 8), (22, 9)])
+def test_permute_bit_exact(ctx, nbits, seed):
+    rng = np.random.default_rng(seed)
+    n = 1 << nbits
+    src = _rand(n, rng)
+    dst_pos = [int(x) for x in rng.permutation(nbits)]
+    ctx.reserve(2 * n + 64)
+    ctx.upload(0, src)
+    ctx.permute(0, n + 32, dst_pos)
+    got = ctx.download(n + 32, n)
+    assert np.array_equal(got, ko.permute(src, dst_pos))
+
+
+def test_permute_reference_patterns(ctx):
+    # right-only / left-only / worst-case L-R-L patterns of
+    # tests/src/tensor_test.cpp:271-469, as bit permutations of a 2^16 tensor
+    rng = np.random.default_rng(11)
+    n_bits = 16
+    src = _rand(1 << n_bits, rng)
+    ident = list(range(n_bits))
+    pats = {
+        "right": list(rng.permutation(10)) + ident[10:],
+        "left": ident[:6] + [6 + int(x) for x in rng.permutation(10)],
+        "lrl": list(reversed(ident)),
+        "identity": ident,
+    }
+    ctx.reserve((2 << n_bits) + 64)
+    ctx.upload(0, src)
+    for name, p in pats.items():
+        p = [int(x) for x in p]
+        ctx.permute(0, (1 << n_bits) + 32, p)
+        got = ctx.download((1 << n_bits) + 32, 1 << n_bits)
+        assert np.array_equal(got, ko.permute(src, p)), name
+
+
+def test_permute_involution_full_size(ctx):
+    # size-independent property at a BASELINE-sized tensor (2^26 elements,
+    # 512 MB): permuting with sigma then sigma^-1 restores the input exactly
+    rng = np.random.default_rng(3)
+    nbits = 26
+    n = 1 << nbits
+    src = _rand(n, rng)
+    p = [int(x) for x in rng.permutation(nbits)]
+    inv = [0] * nbits
+    for b, d in enumerate(p):
+        inv[d] = b
+    ctx.reserve(3 * n)
+    ctx.upload(0, src)
+    ctx.permute(0, n, p)
+    ctx.permute(n, 2 * n, inv)
+    assert np.array_equal(ctx.download(2 * n, n), src)

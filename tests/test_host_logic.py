@@ -1,0 +1,159 @@
+"""Host layer (parsers, planner, executor recursion, slice dealing) on the
+CPU-emulated device ABI, against the reference's golden amplitudes."""
+import ctypes
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from tests import support
+
+TOL = 1e-4  # BASELINE.json north_star: normwise relative error of the amplitude vector
+
+CPU_CASES = ["test", "simple_1100x", "rect2x2_0000", "rect2x2_0110", "sycamore_53_4",
+             "bristlecone_70_1-12-1", "bristlecone_48_1-16-1"]
+
+
+def _amps(golden, name):
+    g = golden[name]
+    return g["states"], np.array(g["re"]) + 1j * np.array(g["im"])
+
+
+@pytest.mark.parametrize("name", CPU_CASES)
+def test_amplitudes_match_reference_golden(emul, golden, name):
+    case = support.CASES[name]
+    c, o, g = support.case_texts(case)
+    res, stats = emul.evaluate(c, o, g, case.get("initial", ""), case.get("final", ""),
+                               memory_limit=8 << 30)
+    states, want = _amps(golden, name)
+    assert [s for s, _ in res] == states
+    assert support.rel_err([a for _, a in res], want) < TOL
+    assert stats["n_amplitudes"] == len(states)
+
+
+def test_simple_circuit_reference_unit_test_values(emul):
+    # reference tests/src/evaluate_circuit_test.cpp:185-207
+    res, _ = emul.evaluate(support.SIMPLE_CIRCUIT, support.SIMPLE_ORDERING, support.SIMPLE_GRID,
+                           "00000", "1100x")
+    assert [s for s, _ in res] == ["11000", "11001"]
+    assert abs(res[0][1] - (0.10669 + 0.04419j)) < 1e-5
+    assert abs(res[1][1] - (-0.01831 - 0.25758j)) < 1e-5
+
+
+@pytest.mark.parametrize("world", [2, 3, 4])
+def test_slices_dealt_to_ranks_sum_to_full_result(emul, golden, world):
+    case = support.CASES["bristlecone_48_1-16-1"]
+    c, o, g = support.case_texts(case)
+    p = emul.prepare(c, o, g, memory_limit=8 << 30)
+    full = p.contract(0, 1)
+    leaves_full = p.stats["leaves"]
+    parts, leaves = np.zeros_like(full), 0
+    for r in range(world):
+        parts += p.contract(r, world)
+        leaves += p.stats["leaves"]
+    assert leaves == leaves_full
+    assert support.rel_err(parts, full) < 1e-6
+    _, want = _amps(golden, "bristlecone_48_1-16-1")
+    assert support.rel_err(parts, want) < TOL
+    p.close()
+
+
+def test_restricting_cut_values_matches_reference_subset(emul, golden):
+    # the mechanism bench.py uses to time a fixed subset of slices
+    o = support.restrict_cuts("cut () 1 3\ncut (0,1) 5\n", [[1], None])
+    assert o == "cut (1) 1 3\ncut (0,1) 5\n"
+
+
+def test_plan_describe_and_flop_model(emul):
+    case = support.CASES["bristlecone_48_1-16-1"]
+    p = emul.prepare(*support.case_texts(case), memory_limit=8 << 30)
+    rows = p.describe()
+    grid = [r for r in rows if r["phase"] == "grid"]
+    assert grid[-1]["kind"] == "dot"
+    assert all(r["kind"] in ("contract", "dot", "scalar") for r in grid)
+    # every grid tensor ends in one layout permute or a direct write
+    assert any(r["kind"] == "permute" for r in rows if r["phase"] == "flatten")
+    p.contract()
+    flops = sum(8.0 * 2 ** (r["m_bits"] + r["n_bits"] + r["k_bits"]) for r in grid)
+    assert abs(flops - p.stats["flops_per_pass"]) < 1e-6 * flops
+    p.close()
+
+
+@pytest.mark.parametrize("bad,needle", [
+    (dict(ordering="expand a 1\nexpand a 1\n"), "is contracted multiple times"),
+    (dict(ordering="frobnicate a 1\n"), "Received an invalid operation in config."),
+    (dict(ordering="expand a 9\n"), "Index 9 must be within grid boundaries."),
+    (dict(ordering="expand a 4\n"), "Index must specify an active qubit."),
+    (dict(ordering="cut (a) 1 3\n"), "Cut values must be comma-separated ints"),
+    (dict(circuit="5\n0 h 0\n1 cz 0 3\n"), "are not nearest neighbors"),
+    (dict(circuit="4\n0 h 0\n"), "does not match the number of active qubits"),
+    (dict(circuit="5\n1 h 0\n0 h 1\n"), "Cycle number can only increase."),
+    (dict(circuit="5\n0 h 0\n0 t 0\n"), "Qubits can only used once per cycle."),
+    (dict(circuit="5\n0 foo 0\n"), "Invalid gate name provided: foo"),
+    (dict(grid="1 1\n1\n"), "is inconsistent with a width"),
+    (dict(final="11"), "must be equal to size of initial_conf"),
+    (dict(ordering="expand a 1\nexpand a 0\n", final="11000"), "hand side of pair not found"),
+    (dict(memory=1024), "exceeds memory limit"),
+])
+def test_error_messages_follow_reference(emul, bad, needle):
+    from qflex_b200 import QflexError
+    with pytest.raises(QflexError) as e:
+        emul.evaluate(bad.get("circuit", support.SIMPLE_CIRCUIT),
+                      bad.get("ordering", support.SIMPLE_ORDERING),
+                      bad.get("grid", support.SIMPLE_GRID), "00000",
+                      bad.get("final", "1100x"), memory_limit=bad.get("memory"))
+    assert needle in str(e.value)
+
+
+def test_simulate_dict_surface_prints_and_returns_empty_on_error(emul, capsys):
+    import qflex_b200
+    out = qflex_b200.simulate({"circuit": ["5", "0 foo 0"], "ordering": ["expand a 0"],
+                               "grid": ["1 1", "1 1", "0 1"]}, lib=emul)
+    assert out == []
+    assert "Invalid gate name provided" in capsys.readouterr().err
+    ok = qflex_b200.simulate({
+        "circuit_filename": os.path.join(support.CONFIG, "circuits", "test.txt"),
+        "ordering_filename": os.path.join(support.CONFIG, "ordering", "test.txt"),
+        "grid_filename": os.path.join(support.CONFIG, "grid", "test.txt")}, lib=emul)
+    assert [s for s, _ in ok] == ["00000", "00001"]
+
+
+def test_product_libraries_export_the_declared_abi():
+    """Every function declared in include/*.h is exported by the in-tree
+    product libraries (no compute call: there is no GPU here)."""
+    root = support.ROOT
+    for header, lib in (("qflex_b200.h", "libqflex_b200.so"),
+                        ("qflex_b200_host.h", "libqflex_host.so")):
+        text = open(os.path.join(root, "include", header)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names = set(re.findall(r"\b(qfx_\w+|qflex_b200_\w+)\s*\(", text))
+        assert names, header
+        path = os.path.join(root, "qflex_b200", lib)
+        assert os.path.exists(path), "run __graft_entry__.build() first"
+        handle = ctypes.CDLL(path)
+        for n in sorted(names):
+            assert hasattr(handle, n), "%s does not export %s" % (lib, n)
+
+
+def test_product_path_fails_loudly_without_gpu():
+    """No CPU fallback: without a CUDA device the product library must raise."""
+    import qflex_b200
+    from qflex_b200 import _device
+    c = _device.load()
+    n = ctypes.c_int(0)
+    rc = c.qfx_device_count(ctypes.byref(n))
+    if rc == 0 and n.value > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(qflex_b200.QflexError):
+        qflex_b200.default_library().evaluate(*support.case_texts(support.CASES["test"]))
+
+
+def test_kernels_are_sm100a_sass():
+    out = subprocess.run(["cuobjdump", "-lelf",
+                          os.path.join(support.ROOT, "qflex_b200", "libqflex_b200.so")],
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    assert "sm_100a" in out.stdout
