@@ -145,6 +145,25 @@ typedef struct qfx_stats {
 int qfx_stats_get(qfx_ctx* ctx, qfx_stats* out);
 int qfx_stats_reset(qfx_ctx* ctx);
 
+/* Per-launch device timing (CUDA events on the context stream around every
+ * qfx_contract / qfx_dot_accumulate / qfx_permute), aggregated by shape class.
+ * Plays the role of the reference's verbose>1 "[M] Time multiplying A*B" /
+ * "[R] Time reordering" stopwatch lines (src/tensor.cpp:1059-1193).  Used by
+ * bench.py for the live roofline of the dominant kernel. */
+typedef struct qfx_profile_row {
+  int32_t kind; /* 0 contract (gemm/dot), 1 permute */
+  int32_t m_bits, n_bits, k_bits; /* as given by the caller (before role swap) */
+  uint64_t launches;
+  double ms;    /* summed device time */
+  double flops; /* summed algorithmic flops */
+  double bytes; /* summed algorithmic bytes */
+} qfx_profile_row;
+int qfx_profile_begin(qfx_ctx* ctx);
+/* Synchronises, fills up to cap rows (sorted by ms, descending), stops
+ * profiling.  *n_out = number of distinct classes seen. */
+int qfx_profile_end(qfx_ctx* ctx, qfx_profile_row* rows, int32_t cap,
+                    int32_t* n_out);
+
 #ifdef __cplusplus
 }
 #endif

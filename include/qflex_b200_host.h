@@ -59,6 +59,12 @@ long qflex_b200_states(void* prepared, char* states_out, uint64_t states_cap);
  * "<phase> <level> <kind> <m_bits> <n_bits> <k_bits> <label>". Returns bytes
  * needed (including NUL). */
 long qflex_b200_describe(void* prepared, char* out, uint64_t cap);
+/* Per-launch device timing by shape class for the following contract() calls
+ * (qfx_profile_begin/end).  Rows are 8 doubles: kind, m_bits, n_bits, k_bits,
+ * launches, summed ms, summed algorithmic flops, summed algorithmic bytes;
+ * sorted by ms descending.  Returns the number of rows available. */
+void qflex_b200_profile(void* prepared, int enable);
+long qflex_b200_profile_rows(void* prepared, double* out, uint64_t cap_rows);
 void qflex_b200_release(void* prepared);
 
 /* verbosity of the host layer (reference global::verbose, src/global.h:9). */

@@ -170,6 +170,11 @@ int qfx_timer_stop_ms(qfx_ctx*, float* ms) {
   *ms = 0.f;
   return QFX_OK;
 }
+int qfx_profile_begin(qfx_ctx*) { return QFX_OK; }
+int qfx_profile_end(qfx_ctx*, qfx_profile_row*, int32_t, int32_t* n) {
+  *n = 0;
+  return QFX_OK;
+}
 int qfx_stats_get(qfx_ctx* c, qfx_stats* o) {
   *o = c->stats;
   return QFX_OK;

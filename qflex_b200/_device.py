@@ -18,7 +18,7 @@ EXPORTS = (
     "qfx_arena_reserve", "qfx_arena_size", "qfx_upload", "qfx_download", "qfx_copy",
     "qfx_contract", "qfx_dot_accumulate", "qfx_scalar_accumulate", "qfx_amps_reserve",
     "qfx_amps_download", "qfx_permute", "qfx_timer_start", "qfx_timer_stop_ms",
-    "qfx_stats_get", "qfx_stats_reset",
+    "qfx_stats_get", "qfx_stats_reset", "qfx_profile_begin", "qfx_profile_end",
 )
 
 

@@ -97,6 +97,15 @@ class Prepared:
                              n_bits=int(n_), k_bits=int(k), label=label))
         return rows
 
+    def profile(self, enable=True):
+        self._lib._c.qflex_b200_profile(self._h, 1 if enable else 0)
+
+    def profile_rows(self):
+        out = np.zeros(8 * 256, dtype=np.float64)
+        n = self._lib._c.qflex_b200_profile_rows(self._h, out.ctypes.data_as(ctypes.c_void_p), 256)
+        keys = ("kind", "m_bits", "n_bits", "k_bits", "launches", "ms", "flops", "bytes")
+        return [dict(zip(keys, out[8 * i: 8 * i + 8].tolist())) for i in range(max(0, min(n, 256)))]
+
     def close(self):
         if self._h:
             self._lib._c.qflex_b200_release(self._h)
@@ -138,6 +147,10 @@ class HostLibrary:
         c.qflex_b200_states.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
         c.qflex_b200_describe.restype = ctypes.c_long
         c.qflex_b200_describe.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_profile.restype = None
+        c.qflex_b200_profile.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        c.qflex_b200_profile_rows.restype = ctypes.c_long
+        c.qflex_b200_profile_rows.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64]
         c.qflex_b200_release.restype = None
         c.qflex_b200_release.argtypes = [ctypes.c_void_p]
         c.qflex_b200_set_verbose.restype = None

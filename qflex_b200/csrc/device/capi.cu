@@ -4,6 +4,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "qfx_internal.h"
 
@@ -36,7 +37,74 @@ int qfx_ensure_ws(qfx_ctx* ctx, size_t bytes) {
   return QFX_OK;
 }
 
+namespace {
+cudaEvent_t prof_event(qfx_ctx* ctx) {
+  if (!ctx->ev_pool.empty()) {
+    cudaEvent_t e = ctx->ev_pool.back();
+    ctx->ev_pool.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+
+qfx_prof_scope::qfx_prof_scope(qfx_ctx* c, int kind, int m, int n, int k, double flops,
+                               double bytes)
+    : ctx(c) {
+  if (ctx == nullptr || !ctx->profiling) {
+    ctx = nullptr;
+    return;
+  }
+  qfx_ctx::ProfRec r{kind, m, n, k, flops, bytes, prof_event(c), prof_event(c)};
+  cudaEventRecord(r.e0, c->stream);
+  c->prof.push_back(r);
+}
+
+qfx_prof_scope::~qfx_prof_scope() {
+  if (ctx != nullptr) cudaEventRecord(ctx->prof.back().e1, ctx->stream);
+}
+
 extern "C" {
+
+int qfx_profile_begin(qfx_ctx* ctx) {
+  if (ctx == nullptr) return QFX_ERR_ARG;
+  ctx->profiling = true;
+  return QFX_OK;
+}
+
+int qfx_profile_end(qfx_ctx* ctx, qfx_profile_row* rows, int32_t cap, int32_t* n_out) {
+  if (ctx == nullptr || n_out == nullptr) return QFX_ERR_ARG;
+  ctx->profiling = false;
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+  std::vector<qfx_profile_row> agg;
+  for (auto& r : ctx->prof) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.e0, r.e1);
+    ctx->ev_pool.push_back(r.e0);
+    ctx->ev_pool.push_back(r.e1);
+    qfx_profile_row* hit = nullptr;
+    for (auto& a : agg)
+      if (a.kind == r.kind && a.m_bits == r.m && a.n_bits == r.n && a.k_bits == r.k) hit = &a;
+    if (hit == nullptr) {
+      agg.push_back(qfx_profile_row{r.kind, r.m, r.n, r.k, 0, 0.0, 0.0, 0.0});
+      hit = &agg.back();
+    }
+    hit->launches++;
+    hit->ms += ms;
+    hit->flops += r.flops;
+    hit->bytes += r.bytes;
+  }
+  ctx->prof.clear();
+  for (size_t i = 0; i < agg.size(); ++i)
+    for (size_t j = i + 1; j < agg.size(); ++j)
+      if (agg[j].ms > agg[i].ms) std::swap(agg[i], agg[j]);
+  *n_out = (int32_t)agg.size();
+  for (int32_t i = 0; i < cap && i < (int32_t)agg.size(); ++i)
+    if (rows != nullptr) rows[i] = agg[i];
+  return QFX_OK;
+}
 
 const char* qfx_last_error(void) { return g_last_error.c_str(); }
 
@@ -94,6 +162,11 @@ int qfx_destroy(qfx_ctx* ctx) {
   if (ctx->ws) cudaFree(ctx->ws);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  for (auto& r : ctx->prof) {
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  for (auto e : ctx->ev_pool) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return QFX_OK;
@@ -190,6 +263,8 @@ int qfx_dot_accumulate(qfx_ctx* ctx, const qfx_contract_desc* desc, uint64_t slo
 
 int qfx_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off, int32_t n_bits,
                 const int8_t* dst_pos) {
+  qfx_prof_scope scope(ctx, 1, n_bits, 0, 0, 0.0,
+                       16.0 * (double)(1ull << (n_bits < 0 ? 0 : n_bits > 40 ? 40 : n_bits)));
   return qfx_launch_permute(ctx, src_off, dst_off, n_bits, dst_pos);
 }
 

@@ -598,6 +598,8 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
                K = (double)(1ull << d.k_bits);
   ctx->stats.flops += 8.0 * M * N * K;
   ctx->stats.bytes += 8.0 * (M * K + K * N + M * N);
+  qfx_prof_scope prof_scope(ctx, 0, din->m_bits, din->n_bits, din->k_bits, 8.0 * M * N * K,
+                            8.0 * (M * K + K * N + M * N));
 
   const float2* A = ctx->arena + d.off_a;
   const float2* B = ctx->arena + d.off_b;

@@ -7,6 +7,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "qflex_b200.h"
 
@@ -23,6 +24,22 @@ struct qfx_ctx {
   size_t ws_bytes = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   qfx_stats stats{};
+  // per-launch profiling (qfx_profile_begin/end)
+  bool profiling = false;
+  struct ProfRec {
+    int kind, m, n, k;
+    double flops, bytes;
+    cudaEvent_t e0, e1;
+  };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> ev_pool;
+};
+
+// RAII scope: records an event pair around the launches issued inside it.
+struct qfx_prof_scope {
+  qfx_ctx* ctx;
+  qfx_prof_scope(qfx_ctx* c, int kind, int m, int n, int k, double flops, double bytes);
+  ~qfx_prof_scope();
 };
 
 void qfx_set_error(const std::string& msg);

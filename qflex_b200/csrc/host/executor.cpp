@@ -3,6 +3,7 @@
 // (reference src/contraction_utils.cpp:223-354): steps before a cut run once,
 // everything after it runs once per cut value; a bond cut adds into the same
 // amplitude, a terminal cut selects amplitude output_index*|values|+i.
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 
@@ -155,11 +156,18 @@ void Session::Contract(int rank, int world,
   const double t0 = now_s();
   check(qfx_amps_reserve(ctx_, plan_.n_amplitudes), "qfx_amps_reserve");
   check(qfx_stats_reset(ctx_), "qfx_stats_reset");
+  if (profile_) check(qfx_profile_begin(ctx_), "qfx_profile_begin");
   check(qfx_timer_start(ctx_), "qfx_timer_start");
   Runner runner(plan_, ctx_, rank, world);
   runner.run(plan_.steps);
   float ms = 0.f;
   check(qfx_timer_stop_ms(ctx_, &ms), "qfx_timer_stop_ms");
+  if (profile_) {
+    int32_t n = 0;
+    profile_rows_.assign(256, qfx_profile_row{});
+    check(qfx_profile_end(ctx_, profile_rows_.data(), 256, &n), "qfx_profile_end");
+    profile_rows_.resize(std::min<int32_t>(n, 256));
+  }
   stats_.device_ms_contract = ms;
   stats_.leaves = runner.leaves();
   check(qfx_stats_get(ctx_, &stats_.device), "qfx_stats_get");

@@ -156,6 +156,28 @@ long qflex_b200_describe(void* prepared, char* out, uint64_t cap) {
   return (long)s.size() + 1;
 }
 
+void qflex_b200_profile(void* prepared, int enable) {
+  if (prepared == nullptr) return;
+  static_cast<qflex::PreparedCircuit*>(prepared)->session->set_profile(enable != 0);
+}
+
+long qflex_b200_profile_rows(void* prepared, double* out, uint64_t cap_rows) {
+  if (prepared == nullptr) return -1;
+  const auto& rows = static_cast<qflex::PreparedCircuit*>(prepared)->session->profile_rows();
+  for (std::size_t i = 0; i < rows.size() && i < cap_rows && out != nullptr; ++i) {
+    double* o = out + 8 * i;
+    o[0] = rows[i].kind;
+    o[1] = rows[i].m_bits;
+    o[2] = rows[i].n_bits;
+    o[3] = rows[i].k_bits;
+    o[4] = (double)rows[i].launches;
+    o[5] = rows[i].ms;
+    o[6] = rows[i].flops;
+    o[7] = rows[i].bytes;
+  }
+  return (long)rows.size();
+}
+
 void qflex_b200_release(void* prepared) {
   delete static_cast<qflex::PreparedCircuit*>(prepared);
 }

@@ -153,10 +153,17 @@ class Session {
   const Plan& plan() const { return plan_; }
   const ExecStats& stats() const { return stats_; }
 
+  // Per-launch device timing of the next Contract() calls, by shape class
+  // (reference analogue: the verbose>1 [M]/[R] lines, src/tensor.cpp:1110-1164).
+  void set_profile(bool on) { profile_ = on; }
+  const std::vector<qfx_profile_row>& profile_rows() const { return profile_rows_; }
+
  private:
   Plan plan_;
   qfx_ctx* ctx_ = nullptr;
   ExecStats stats_;
+  bool profile_ = false;
+  std::vector<qfx_profile_row> profile_rows_;
 };
 
 }  // namespace qflex

@@ -109,7 +109,7 @@ def test_contract_rejects_overlap_and_bad_tables(ctx):
     d = _device.make_desc(0, 64, 128, [1, 1], [0, 1], [], [], [0], [0])
     with pytest.raises(_device.DeviceError, match="distinct"):
         ctx.contract(d)
-    d = _device.make_desc(1000, 64, 128, [1, 2, 3, 4, 5], [0, 1, 2, 3, 4], [], [], [0], [0])
+    d = _device.make_desc(1 << 40, 64, 128, [1, 2, 3, 4, 5], [0, 1, 2, 3, 4], [], [], [0], [0])
     with pytest.raises(_device.DeviceError, match="outside the arena"):
         ctx.contract(d)
 
