@@ -1,6 +1,7 @@
 // C ABI of libqflex_b200.so: context, arena, transfers, amplitude table.
 // See include/qflex_b200.h for the reference interfaces each entry replaces.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -146,6 +147,7 @@ int qfx_create(int device, qfx_ctx** ctx_out) {
   }
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
+  if (const char* e = getenv("QFLEX_TC_CHUNK")) ctx->tc_chunk = atoi(e);
   QFX_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   QFX_CUDA(cudaEventCreate(&ctx->ev0));
   QFX_CUDA(cudaEventCreate(&ctx->ev1));

@@ -605,6 +605,11 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
   const float2* B = ctx->arena + d.off_b;
   float2* C = accumulate_amp ? nullptr : ctx->arena + d.off_c;
 
+  // ---------------- compute-bound classes: tcgen05 split-bf16 path
+  if (!accumulate_amp && d.precision != QFX_PREC_FFMA && qfx_tc_eligible(d)) {
+    return qfx_launch_contract_tc(ctx, d, A, B, C);
+  }
+
   // ---------------- tiny outputs: block reduction over K
   if (d.m_bits + d.n_bits <= 6) {
     DotArgs g{};

@@ -25,6 +25,7 @@ struct qfx_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   qfx_stats stats{};
   // per-launch profiling (qfx_profile_begin/end)
+  int tc_chunk = 0;  // k blocks per TMEM accumulation chunk (0 = default)
   bool profiling = false;
   struct ProfRec {
     int kind, m, n, k;
@@ -55,6 +56,10 @@ int qfx_ensure_ws(qfx_ctx* ctx, size_t bytes);
 // contract.cu
 int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* d,
                         bool accumulate_amp, uint64_t slot);
+// tc_gemm.cu (tcgen05 split-bf16 path; d has roles swapped so m_bits >= n_bits)
+bool qfx_tc_eligible(const qfx_contract_desc& d);
+int qfx_launch_contract_tc(qfx_ctx* ctx, const qfx_contract_desc& d, const float2* A,
+                           const float2* B, float2* C);
 // permute.cu
 int qfx_launch_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
                        int n_bits, const int8_t* dst_pos);
