@@ -23,6 +23,9 @@ namespace {
 
 constexpr int kRunBits = 5;
 constexpr int kTileBits = 10;
+constexpr int kBigRunBits = 6;   // big tiles: >= 512-byte runs on both sides
+constexpr int kBigTileBits = 12; // 4096 elements = 32 KB of shared memory
+constexpr int kMaxTileBits = 12;
 constexpr int kThreads = 256;
 
 struct SplitArgs {
@@ -30,9 +33,9 @@ struct SplitArgs {
   uint32_t* hi;   // 2 x bf16 per complex element
   uint32_t* mid;
   int t_bits, o_bits, k_bits;
-  int8_t e_src[kTileBits];
-  int8_t f_dst[kTileBits];
-  int8_t f_to_e[kTileBits];
+  int8_t e_src[kMaxTileBits];
+  int8_t f_dst[kMaxTileBits];
+  int8_t f_to_e[kMaxTileBits];
   int8_t o_src[QFX_MAX_BITS], o_dst[QFX_MAX_BITS];
 };
 
@@ -100,6 +103,93 @@ __global__ void __launch_bounds__(kThreads) split_gather(const __grid_constant__
   }
 }
 
+// XOR swizzle of the tile index (bits 1..3 <- higher bits): whatever subset of
+// index bits a warp varies, its 8-byte accesses spread over the banks; pairs
+// (bit 0) stay adjacent for the 16-byte stores.
+__device__ __forceinline__ unsigned swz(unsigned e) {
+  return e ^ ((((e >> 4) ^ (e >> 7) ^ (e >> 10)) & 7u) << 1);
+}
+
+// Operand A, tensors of >= 2^12 elements: 4096-element tiles, every thread keeps
+// 8 independent 16-byte loads in flight and writes 16-byte runs of hi and mid.
+// Offsets split into a per-thread part (registers) and a per-iteration part
+// (tiny shared tables), so the inner loops are one add per access.
+__global__ void __launch_bounds__(kThreads) split_a_big(const __grid_constant__ SplitArgs g) {
+  __shared__ __align__(16) float2 tile[1 << kBigTileBits];
+  __shared__ unsigned s_hi[8], d_hi[4], e_hi[4];
+  const unsigned tid = threadIdx.x;
+  // source side: pair u = it*256 + tid, element e0 = 2u (bit 0 clear)
+  unsigned s_lo = 0;
+  for (int b = 0; b < 8; ++b) s_lo |= ((tid >> b) & 1u) << g.e_src[b + 1];
+  // destination side: quad q = it*256 + tid, element f0 = 4q
+  unsigned d_lo = 0, e_lo = 0;
+  for (int b = 0; b < 8; ++b) {
+    d_lo |= ((tid >> b) & 1u) << g.f_dst[b + 2];
+    e_lo |= ((tid >> b) & 1u) << g.f_to_e[b + 2];
+  }
+  if (tid < 8) {
+    unsigned v = 0;
+    for (int b = 0; b < 3; ++b) v |= ((tid >> b) & 1u) << g.e_src[b + 9];
+    s_hi[tid] = v;
+  }
+  if (tid < 4) {
+    unsigned v = 0, w = 0;
+    for (int b = 0; b < 2; ++b) {
+      v |= ((tid >> b) & 1u) << g.f_dst[b + 10];
+      w |= ((tid >> b) & 1u) << g.f_to_e[b + 10];
+    }
+    d_hi[tid] = v;
+    e_hi[tid] = w;
+  }
+  const unsigned e_j1 = 1u << g.f_to_e[0], e_j2 = 1u << g.f_to_e[1];
+  const unsigned s_d1 = 1u << g.e_src[0];
+  const bool vec = (g.e_src[0] == 0);
+  __syncthreads();
+  const unsigned long long n_outer = 1ull << g.o_bits;
+  for (unsigned long long o = blockIdx.x; o < n_outer; o += gridDim.x) {
+    unsigned long long sb = 0, db = 0;
+    for (int i = 0; i < g.o_bits; ++i) {
+      const unsigned long long b = (o >> i) & 1ull;
+      sb |= b << g.o_src[i];
+      db |= b << g.o_dst[i];
+    }
+    const float2* __restrict__ s = g.src + sb + s_lo;
+    float4 v[8];
+    if (vec) {
+#pragma unroll
+      for (int it = 0; it < 8; ++it) v[it] = __ldg(reinterpret_cast<const float4*>(s + s_hi[it]));
+    } else {
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const float2 a = __ldg(s + s_hi[it]), b = __ldg(s + s_hi[it] + s_d1);
+        v[it] = make_float4(a.x, a.y, b.x, b.y);
+      }
+    }
+#pragma unroll
+    for (int it = 0; it < 8; ++it)
+      *reinterpret_cast<float4*>(&tile[swz(2u * (it * 256u + tid))]) = v[it];
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const unsigned e0 = e_lo | e_hi[it];
+      uint32_t h[4], m[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 x = tile[swz(e0 + ((j & 1) ? e_j1 : 0u) + ((j & 2) ? e_j2 : 0u))];
+        __nv_bfloat16 rh, rm, ih, im;
+        split2(x.x, rh, rm);
+        split2(x.y, ih, im);
+        h[j] = pack(rh, ih);
+        m[j] = pack(rm, im);
+      }
+      const unsigned long long d = db + d_lo + d_hi[it];
+      *reinterpret_cast<uint4*>(g.hi + d) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(g.mid + d) = make_uint4(m[0], m[1], m[2], m[3]);
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace
 
 // row_pos/k_pos: operand address bit of every row (m or n) bit and of every k
@@ -121,18 +211,21 @@ int qfx_launch_split(qfx_ctx* ctx, const float2* src, int mode, const int8_t* ro
   std::vector<int> by_src(n);
   for (int i = 0; i < n; ++i) by_src[i] = i;
   std::sort(by_src.begin(), by_src.end(), [&](int x, int y) { return sp[x] < sp[y]; });
+  const bool big = (mode == 0 && n >= kBigTileBits);
+  const int run_bits = big ? kBigRunBits : kRunBits;
+  const int tile_bits = big ? kBigTileBits : kTileBits;
   std::vector<char> in_tile(n, 0);
   int t = 0;
-  for (int r = 0; r < n && r < kRunBits; ++r) {
+  for (int r = 0; r < n && r < run_bits; ++r) {
     in_tile[by_src[r]] = 1;
     ++t;
   }
   for (int i = 0; i < n; ++i)
-    if (dp[i] < kRunBits && !in_tile[i]) {
+    if (dp[i] < run_bits && !in_tile[i]) {
       in_tile[i] = 1;
       ++t;
     }
-  for (int r = 0; r < n && t < kTileBits; ++r)
+  for (int r = 0; r < n && t < tile_bits; ++r)
     if (!in_tile[by_src[r]]) {
       in_tile[by_src[r]] = 1;
       ++t;
@@ -167,7 +260,9 @@ int qfx_launch_split(qfx_ctx* ctx, const float2* src, int mode, const int8_t* ro
   const unsigned long long n_outer = 1ull << g.o_bits;
   const unsigned blocks =
       (unsigned)std::min<unsigned long long>(n_outer, 16ull * ctx->sm_count);
-  if (mode == 0)
+  if (big && t == kBigTileBits && g.f_dst[0] == 0 && g.f_dst[1] == 1)
+    split_a_big<<<blocks, kThreads, 0, ctx->stream>>>(g);
+  else if (mode == 0)
     split_gather<0><<<blocks, kThreads, 0, ctx->stream>>>(g);
   else
     split_gather<1><<<blocks, kThreads, 0, ctx->stream>>>(g);
