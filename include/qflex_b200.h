@@ -141,6 +141,7 @@ typedef struct qfx_stats {
   uint64_t launches_copy;
   double flops;
   double bytes;
+  uint64_t launches_gemm_tc_fused; /* subset of launches_gemm_tc: in-kernel fp32->bf16 split */
 } qfx_stats;
 int qfx_stats_get(qfx_ctx* ctx, qfx_stats* out);
 int qfx_stats_reset(qfx_ctx* ctx);

@@ -1,0 +1,730 @@
+// Fused tensor-core contraction: the fp32 -> split-bf16 conversion of the big
+// (streamed) operand happens INSIDE the GEMM kernel, so a contraction reads A
+// once from HBM as complex64, wherever its index bits live, and writes C once.
+//
+// Replaces, for the classes SURVEY 8d marks tensor-core candidates (and the
+// d=16 HBM-bound expands), the reference's A.reorder + cblas_cgemm
+// (src/tensor.cpp:1045-1194, 960-980): the reorder of A is folded into a
+// multi-dimensional TMA tensor map over A's address bits, the product is
+// tcgen05.mma kind::f16 on bf16 hi/mid pairs (x ~= hi + mid):
+//     a*b ~= a_mid*b_hi + a_hi*b_mid + a_hi*b_hi        (rel. error ~ 2^-17)
+// run as ONE real GEMM on the raw float views (see tc_split.cu for B'):
+//     C'[m][2n+c] = sum_k' A'[m][k'] * B'[2n+c][k'],  k' = 2k + {re,im}
+//
+// Persistent kernel, one CTA per SM, 512 threads in four warpgroups:
+//   warp 0      TMA producer for A: one box of 128 rows x 32 complex k per
+//               stage, gathered through <= 4 address-bit runs + one "offset"
+//               dimension (stride 16 B) that carries the tile base;
+//   warp 1      MMA issuer (one elected lane, tcgen05.mma cta_group::1);
+//   warp 2      TMA producer for B' (pre-split bf16 hi/mid, small, L2-resident);
+//   warps 4-7   converters: fp32 tile (smem) -> bf16 hi + mid tiles in the
+//               128B-swizzled K-major layout the MMA descriptors expect;
+//   warps 8-15  epilogue: tcgen05.ld -> fp32 fold of the k chunks -> C.
+// Register budget is rebalanced with setmaxnreg (40 / 72 / 200 / 200).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "qfx_internal.h"
+
+int qfx_launch_split(qfx_ctx* ctx, const float2* src, int mode, const int8_t* row_pos,
+                     int row_bits, const int8_t* k_pos, int k_bits, uint32_t* hi,
+                     uint32_t* mid);
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;                       // bf16 per k block = one 128-byte swizzle row
+constexpr int MAX_BN = 256;
+constexpr int A16_TILE = BM * BK * 2;        // 16 KB: one bf16 tile (hi or mid)
+constexpr int SC = 2;                        // bf16 A stages
+constexpr int FUSED_THREADS = 512;
+constexpr int CONV_WARP0 = 4, EPI_WARP0 = 8;
+constexpr int MAX_SA = 6, MAX_SB = 6;
+constexpr int SMEM_LIMIT = 232448;           // 227 KB opt-in maximum per CTA
+constexpr int MAX_TILE_BITS = 12;
+
+struct FusedArgs {
+  float2* C;
+  int m_bits, n_bits;
+  int kblocks;        // k blocks per tile
+  int nkk;            // 16-wide MMA k steps per k block (<= 4)
+  int chunk, nchunks; // k blocks accumulated in TMEM before the fp32 fold
+  int bn, tiles_n, tiles;
+  int c_natural;
+  int a_rank;         // rank of the A tensor map (in-tile runs + offset dim)
+  int kb_bits;        // complex k bits inside a k block
+  int tile_bits;      // 7 + kb_bits
+  int sa, sb;         // fp32 A stages, B slots (each slot = one bn x 64 bf16 tile)
+  uint32_t a32_bytes; // bytes of one fp32 A stage
+  uint32_t b_slot_bytes;
+  // tile base: address bit of every m bit >= 7 and every k bit >= kb_bits
+  int8_t a_m_hi[QFX_MAX_BITS], a_k_hi[QFX_MAX_BITS];
+  int n_m_hi, n_k_hi;
+  // converters: XOR masks of the destination byte offset per smem element bit
+  uint32_t cv_mask[MAX_TILE_BITS];
+  uint32_t cv_it[16];
+  int8_t c_m[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded spin: a protocol bug traps instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  const long long t0 = clock64();
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!ok && clock64() - t0 > 4000000000ll) __trap();
+  } while (!ok);
+}
+
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint32_t bar, uint32_t dst,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// A tile: all in-tile coordinates are 0, dimension 1 (stride 16 bytes, box 1)
+// carries the tile base offset in units of two complex64.
+__device__ __forceinline__ void tma_load_a(const CUtensorMap* map, int rank, uint32_t bar,
+                                           uint32_t dst, int off16) {
+  const uint64_t m = reinterpret_cast<uint64_t>(map);
+  const int z = 0;
+  if (rank == 2) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(m), "r"(bar), "r"(z), "r"(off16)
+        : "memory");
+  } else if (rank == 3) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %3}], [%2];"
+        ::"r"(dst), "l"(m), "r"(bar), "r"(z), "r"(off16)
+        : "memory");
+  } else if (rank == 4) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %3, %3}], [%2];"
+        ::"r"(dst), "l"(m), "r"(bar), "r"(z), "r"(off16)
+        : "memory");
+  } else {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %3, %3, %3}], [%2];"
+        ::"r"(dst), "l"(m), "r"(bar), "r"(z), "r"(off16)
+        : "memory");
+  }
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+               ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+// generic-proxy smem writes -> visible to the async proxy (UMMA operand reads)
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// K-major, 128-byte swizzle, dense 128-byte rows: SBO = 8 rows * 128 B = 1024.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3FFFFu) >> 4);  // start address
+  d |= (uint64_t)1 << 16;                   // leading byte offset (unused for SW128 K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;         // stride byte offset
+  d |= (uint64_t)1 << 46;                   // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                   // SWIZZLE_128B
+  return d;
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+template <int N>
+__device__ __forceinline__ void reg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void reg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+
+// fp32 pair (re, im) -> packed bf16 hi and packed bf16 mid (re in the low half)
+__device__ __forceinline__ void split_pair(float re, float im, uint32_t& hi, uint32_t& mid) {
+  const __nv_bfloat162 h = __float22bfloat162_rn(make_float2(re, im));
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  const float hre = __uint_as_float(hi << 16), him = __uint_as_float(hi & 0xffff0000u);
+  const __nv_bfloat162 m = __float22bfloat162_rn(make_float2(re - hre, im - him));
+  mid = *reinterpret_cast<const uint32_t*>(&m);
+}
+
+__global__ void __launch_bounds__(FUSED_THREADS, 1)
+    tc_fused_bf16x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
+                    const __grid_constant__ CUtensorMap tmBm, const __grid_constant__ FusedArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t a16_base = smem_base;                                   // SC x (hi, mid)
+  const uint32_t b_base = a16_base + SC * 2 * A16_TILE;                  // sb slots
+  const uint32_t a32_base = b_base + (uint32_t)g.sb * g.b_slot_bytes;    // sa stages
+  const uint32_t bar_base = a32_base + (uint32_t)g.sa * g.a32_bytes;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + (bar_base - smem_base) + 8 * 32);
+  auto a_full = [&](int s) { return bar_base + 8u * s; };
+  auto a_empty = [&](int s) { return bar_base + 8u * (MAX_SA + s); };
+  auto c_full = [&](int s) { return bar_base + 8u * (2 * MAX_SA + s); };
+  auto c_empty = [&](int s) { return bar_base + 8u * (2 * MAX_SA + SC + s); };
+  auto b_full = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * SC + s); };
+  auto b_empty = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * SC + MAX_SB + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * SC + 2 * MAX_SB + s); };
+  auto tempty_bar = [&](int s) {
+    return bar_base + 8u * (2 * MAX_SA + 2 * SC + 2 * MAX_SB + 2 + s);
+  };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bn = g.bn;
+  const uint32_t tmem_cols = (2 * bn < 32) ? 32u : (uint32_t)(2 * bn);
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < MAX_SA; ++s) {
+      mbar_init(a_full(s), 1);
+      mbar_init(a_empty(s), 4);
+    }
+    for (int s = 0; s < SC; ++s) {
+      mbar_init(c_full(s), 4);
+      mbar_init(c_empty(s), 1);
+    }
+    for (int s = 0; s < MAX_SB; ++s) {
+      mbar_init(b_full(s), 1);
+      mbar_init(b_empty(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 8);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32(tmem_slot)), "r"(tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < CONV_WARP0) {
+    reg_dec<40>();
+    if (warp == 0 && lane == 0) {
+      // ---------------- A producer: one gathered fp32 box per k block
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+        const unsigned mt = (unsigned)(t / g.tiles_n);
+        unsigned long long row_base = 0;
+        for (int i = 0; i < g.n_m_hi; ++i)
+          row_base |= (unsigned long long)((mt >> i) & 1u) << g.a_m_hi[i];
+        for (int kb = 0; kb < g.kblocks; ++kb) {
+          unsigned long long off = row_base;
+          for (int i = 0; i < g.n_k_hi; ++i)
+            off |= (unsigned long long)(((unsigned)kb >> i) & 1u) << g.a_k_hi[i];
+          mbar_wait(a_empty(stage), phase ^ 1u);
+          mbar_expect_tx(a_full(stage), g.a32_bytes);
+          tma_load_a(&tmA, g.a_rank, a_full(stage), a32_base + (uint32_t)stage * g.a32_bytes,
+                     (int)(off >> 1));
+          if (++stage == g.sa) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    } else if (warp == 2 && lane == 0) {
+      // ---------------- B producer: B'_mid then B'_hi of every k block
+      int slot = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+        const int nt = t % g.tiles_n;
+        for (int kb = 0; kb < g.kblocks; ++kb) {
+#pragma unroll
+          for (int part = 0; part < 2; ++part) {
+            mbar_wait(b_empty(slot), phase ^ 1u);
+            mbar_expect_tx(b_full(slot), g.b_slot_bytes);
+            tma_load_2d(part == 0 ? &tmBm : &tmBh, b_full(slot),
+                        b_base + (uint32_t)slot * g.b_slot_bytes, kb * BK, nt * bn);
+            if (++slot == g.sb) {
+              slot = 0;
+              phase ^= 1u;
+            }
+          }
+        }
+      }
+    } else if (warp == 1 && lane == 0) {
+      // ---------------- MMA issuer
+      // instruction descriptor: D=f32, A=B=bf16, both K-major, N=bn, M=128
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) |
+                             ((uint32_t)(BM >> 4) << 24);
+      int cs = 0, bs = 0, acc = 0;
+      uint32_t cph = 0, bph = 0, acc_phase = 0;
+      for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+        for (int ch = 0; ch < g.nchunks; ++ch) {
+          mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
+          const int kb_end = min(g.kblocks, (ch + 1) * g.chunk);
+          for (int kb = ch * g.chunk; kb < kb_end; ++kb) {
+            const bool first = (kb == ch * g.chunk);
+            const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE);
+            const uint64_t dAm = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE + A16_TILE);
+            mbar_wait(c_full(cs), cph);
+            mbar_wait(b_full(bs), bph);
+            tc_fence_after();
+            const uint64_t dBm = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
+            for (int kk = 0; kk < g.nkk; ++kk) {
+              const uint64_t adv = (uint64_t)(kk * 32 >> 4);  // 16 bf16 = 32 bytes along K
+              umma_bf16(d_tmem, dAh + adv, dBm + adv, idesc, (first && kk == 0) ? 0u : 1u);
+            }
+            umma_commit(b_empty(bs));
+            if (++bs == g.sb) {
+              bs = 0;
+              bph ^= 1u;
+            }
+            mbar_wait(b_full(bs), bph);
+            tc_fence_after();
+            const uint64_t dBh = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
+            for (int kk = 0; kk < g.nkk; ++kk) {
+              const uint64_t adv = (uint64_t)(kk * 32 >> 4);
+              umma_bf16(d_tmem, dAm + adv, dBh + adv, idesc, 1u);
+            }
+            for (int kk = 0; kk < g.nkk; ++kk) {
+              const uint64_t adv = (uint64_t)(kk * 32 >> 4);
+              umma_bf16(d_tmem, dAh + adv, dBh + adv, idesc, 1u);
+            }
+            umma_commit(b_empty(bs));
+            if (++bs == g.sb) {
+              bs = 0;
+              bph ^= 1u;
+            }
+            umma_commit(c_empty(cs));
+            if (++cs == SC) {
+              cs = 0;
+              cph ^= 1u;
+            }
+          }
+          umma_commit(tfull_bar(acc));  // chunk accumulator complete
+          if (++acc == 2) {
+            acc = 0;
+            acc_phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp < EPI_WARP0) {
+    reg_dec<72>();
+    // ---------------- converters: fp32 stage -> bf16 hi / mid (SW128 K-major)
+    const unsigned ctid = threadIdx.x - CONV_WARP0 * 32;
+    uint32_t dst_t = 0;
+#pragma unroll
+    for (int b = 0; b < 7; ++b)
+      if ((ctid >> b) & 1u) dst_t ^= g.cv_mask[b + 1];
+    const uint32_t mask1 = g.cv_mask[0];
+    const int its = 1 << (g.tile_bits - 8);
+    int as = 0, cs = 0;
+    uint32_t aph = 0, cph = 0;
+    for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+      for (int kb = 0; kb < g.kblocks; ++kb) {
+        mbar_wait(a_full(as), aph);
+        mbar_wait(c_empty(cs), cph ^ 1u);
+        const uint32_t src = a32_base + (uint32_t)as * g.a32_bytes + ctid * 16u;
+        const uint32_t hi_tile = a16_base + (uint32_t)cs * 2 * A16_TILE;
+        const uint32_t mid_tile = hi_tile + A16_TILE;
+        for (int it0 = 0; it0 < its; it0 += 8) {
+          float4 v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = lds128(src + (uint32_t)(it0 + j) * 2048u);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t d0 = dst_t ^ g.cv_it[it0 + j];
+            const uint32_t d1 = d0 ^ mask1;
+            uint32_t h, m;
+            split_pair(v[j].x, v[j].y, h, m);
+            sts32(hi_tile + d0, h);
+            sts32(mid_tile + d0, m);
+            split_pair(v[j].z, v[j].w, h, m);
+            sts32(hi_tile + d1, h);
+            sts32(mid_tile + d1, m);
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(c_full(cs));
+          mbar_arrive(a_empty(as));
+        }
+        if (++as == g.sa) {
+          as = 0;
+          aph ^= 1u;
+        }
+        if (++cs == SC) {
+          cs = 0;
+          cph ^= 1u;
+        }
+      }
+    }
+  } else {
+    reg_inc<200>();
+    // ---------------- epilogue: warp w may only touch TMEM lanes 32*(w%4) .. +31; two
+    // warps share a lane group and split the tile's columns.  The tensor core
+    // accumulates with truncation, which biases long sums towards zero, so an
+    // accumulator only integrates `chunk` k blocks; chunks are folded here in
+    // fp32 with round-to-nearest adds, in registers, and C is written once.
+    const int lane_group = warp & 3;
+    const int half = (warp - EPI_WARP0) >> 2;
+    const int row = lane_group * 32 + lane;
+    const int half_cols = bn >> 1;
+    const int npieces = half_cols >> 4;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const unsigned long long N = 1ull << g.n_bits;
+    for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+      const int nt = t % g.tiles_n, mt = t / g.tiles_n;
+      float sum[8][16];
+      for (int ch = 0; ch < g.nchunks; ++ch) {
+        mbar_wait(tfull_bar(acc), acc_phase);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) +
+                               (uint32_t)(acc * bn + half * half_cols);
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          if (p < npieces) {
+            uint32_t r[16];
+            tmem_ld16(t_row + (uint32_t)(p * 16), r);
+            if (ch == 0) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) sum[p][j] = __uint_as_float(r[j]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) sum[p][j] += __uint_as_float(r[j]);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1u;
+        }
+      }
+      const unsigned long long m = (unsigned long long)mt * BM + row;
+      unsigned long long row_off = 0;
+      if (g.c_natural) {
+        row_off = m * N;
+      } else {
+        for (int q = 0; q < g.m_bits; ++q) row_off |= ((m >> q) & 1ull) << g.c_m[q];
+      }
+#pragma unroll
+      for (int p = 0; p < 8; ++p) {
+        if (p < npieces) {
+          // complex column of the first element of this piece
+          const unsigned long long n0 =
+              ((unsigned long long)nt * bn + half * half_cols + p * 16) >> 1;
+          if (g.c_natural) {
+            float4* dst = reinterpret_cast<float4*>(g.C + row_off + n0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              dst[j] = make_float4(sum[p][4 * j], sum[p][4 * j + 1], sum[p][4 * j + 2],
+                                   sum[p][4 * j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const unsigned long long n = n0 + j;
+              unsigned long long co = 0;
+              for (int q = 0; q < g.n_bits; ++q) co |= ((n >> q) & 1ull) << g.c_n[q];
+              g.C[row_off + co] = make_float2(sum[p][2 * j], sum[p][2 * j + 1]);
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(tmem_cols)
+                 : "memory");
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor [rows][cols] row-major, box = 64 cols x box_rows, 128B swizzle.
+// cols may be 32 (K = 16): the box then reaches past the tensor and the
+// out-of-bounds half of every 128-byte row is zero-filled (never read by the MMA).
+bool make_map_b(CUtensorMap* map, void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct TileBit {
+  int addr, kind, idx;  // kind 0 = row (m) bit, 1 = k bit
+};
+
+// Gathered fp32 view of A: the tile's address bits, grouped into runs of
+// consecutive addresses, are the box dimensions; dimension 1 is an "offset"
+// dimension (stride 16 bytes, box 1) whose coordinate carries the tile base.
+// Fills the converter XOR tables.  Returns false when the tile cannot be
+// expressed (caller falls back to the pre-split path).
+bool make_map_a(CUtensorMap* map, const float2* A, const qfx_contract_desc& d, int kb_bits,
+                uint64_t span_elems, FusedArgs* g) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) return false;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) != 0) return false;
+  std::vector<TileBit> bits;
+  for (int i = 0; i < 7; ++i) bits.push_back({d.a_m[i], 0, i});
+  for (int j = 0; j < kb_bits; ++j) bits.push_back({d.a_k[j], 1, j});
+  std::sort(bits.begin(), bits.end(),
+            [](const TileBit& x, const TileBit& y) { return x.addr < y.addr; });
+  if (bits[0].addr != 0) return false;
+  // runs of consecutive addresses (first run <= 7 bits: 2 * 2^7 floats = 256 box limit)
+  std::vector<std::pair<int, int>> runs;  // (first addr, length)
+  for (size_t s = 0; s < bits.size(); ++s) {
+    const int cap = runs.size() == 1 ? 7 : 8;
+    if (!runs.empty() && runs.back().first + runs.back().second == bits[s].addr &&
+        runs.back().second < cap)
+      runs.back().second++;
+    else
+      runs.push_back({bits[s].addr, 1});
+  }
+  if (runs.size() > 4) return false;
+  const int rank = (int)runs.size() + 1;
+  cuuint64_t dims[5];
+  cuuint64_t strides[4];
+  cuuint32_t box[5], estr[5] = {1, 1, 1, 1, 1};
+  dims[0] = 2ull << runs[0].second;  // floats
+  box[0] = (cuuint32_t)dims[0];
+  dims[1] = (span_elems + 1) / 2;    // tile base in units of 16 bytes
+  box[1] = 1;
+  strides[0] = 16;
+  for (size_t r = 1; r < runs.size(); ++r) {
+    dims[r + 1] = 1ull << runs[r].second;
+    box[r + 1] = (cuuint32_t)dims[r + 1];
+    strides[r] = 8ull << runs[r].first;
+  }
+  if (fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<float2*>(A), dims,
+         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  g->a_rank = rank;
+  // destination byte offset inside a [128 rows][128 bytes] SW128 tile is XOR-linear
+  // in the element's (row, k) bits
+  for (size_t s = 0; s < bits.size(); ++s) {
+    const int i = bits[s].idx;
+    uint32_t msk;
+    if (bits[s].kind == 0)
+      msk = (1u << (7 + i)) | (i < 3 ? (1u << (4 + i)) : 0u);
+    else
+      msk = i < 2 ? (1u << (2 + i)) : (1u << (4 + (i - 2)));
+    g->cv_mask[s] = msk;
+  }
+  const int nb = (int)bits.size();
+  for (int it = 0; it < 16; ++it) {
+    uint32_t x = 0;
+    for (int b = 0; b + 8 < nb; ++b)
+      if ((it >> b) & 1) x ^= g->cv_mask[8 + b];
+    g->cv_it[it] = x;
+  }
+  return true;
+}
+
+}  // namespace
+
+// Roles already swapped (m_bits >= n_bits).  Returns QFX_OK and sets *done = true
+// when the fused kernel was launched; *done = false means "not applicable, use the
+// pre-split path" (not an error).
+int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, const float2* A,
+                                 const float2* B, float2* C, bool* done) {
+  *done = false;
+  static const bool disabled = [] {
+    const char* e = getenv("QFLEX_TC_FUSED");
+    return e != nullptr && atoi(e) == 0;
+  }();
+  if (disabled) return QFX_OK;
+  qfx_contract_desc d = din;
+  if (d.m_bits < 7 || d.n_bits < 4 || d.k_bits < 4) return QFX_OK;
+  // K enumeration is free: lowest A address bits first, so that a k block is
+  // made of A's most contiguous k bits (B' is gathered by the split pre-pass).
+  {
+    std::vector<int> idx(d.k_bits);
+    for (int i = 0; i < d.k_bits; ++i) idx[i] = i;
+    std::sort(idx.begin(), idx.end(), [&](int x, int y) { return d.a_k[x] < d.a_k[y]; });
+    int8_t ak[QFX_MAX_BITS], bk[QFX_MAX_BITS];
+    for (int i = 0; i < d.k_bits; ++i) {
+      ak[i] = d.a_k[idx[i]];
+      bk[i] = d.b_k[idx[i]];
+    }
+    memcpy(d.a_k, ak, d.k_bits);
+    memcpy(d.b_k, bk, d.k_bits);
+  }
+  const uint64_t M = 1ull << d.m_bits, N = 1ull << d.n_bits, K = 1ull << d.k_bits;
+  FusedArgs g{};
+  g.kb_bits = std::min(5, (int)d.k_bits);
+  g.tile_bits = 7 + g.kb_bits;
+  uint64_t span = 0;
+  for (int i = 0; i < d.m_bits; ++i) span |= 1ull << d.a_m[i];
+  for (int i = 0; i < d.k_bits; ++i) span |= 1ull << d.a_k[i];
+  span += 1;
+  CUtensorMap mA, mBh, mBm;
+  if (!make_map_a(&mA, A, d, g.kb_bits, span, &g)) return QFX_OK;
+
+  // workspace: B' hi/mid (2N x 2K bf16 each)
+  const size_t b_bytes = (size_t)N * K * 8;
+  int rc = qfx_ensure_ws(ctx, 2 * b_bytes + 4096);
+  if (rc) return rc;
+  uint8_t* ws = reinterpret_cast<uint8_t*>(ctx->ws);
+  uint32_t* b_hi = reinterpret_cast<uint32_t*>(ws);
+  uint32_t* b_mid = reinterpret_cast<uint32_t*>(ws + b_bytes);
+  rc = qfx_launch_split(ctx, B, 1, d.b_n, d.n_bits, d.b_k, d.k_bits, b_hi, b_mid);
+  if (rc) return rc;
+
+  g.C = C;
+  g.m_bits = d.m_bits;
+  g.n_bits = d.n_bits;
+  g.kblocks = (int)std::max<uint64_t>(1, (2 * K) / BK);
+  g.nkk = (int)std::min<uint64_t>(4, (2 * K) / 16);
+  g.chunk = ctx->tc_chunk > 0 ? ctx->tc_chunk : 2;
+  g.nchunks = (g.kblocks + g.chunk - 1) / g.chunk;
+  g.bn = (int)std::min<uint64_t>(2 * N, MAX_BN);
+  g.tiles_n = (int)((2 * N) / g.bn);
+  g.tiles = (int)((M / BM) * g.tiles_n);
+  g.c_natural = 1;
+  for (int i = 0; i < d.n_bits; ++i)
+    if (d.c_n[i] != i) g.c_natural = 0;
+  for (int i = 0; i < d.m_bits; ++i)
+    if (d.c_m[i] != d.n_bits + i) g.c_natural = 0;
+  if ((reinterpret_cast<uintptr_t>(C) & 15) != 0) g.c_natural = 0;
+  memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
+  memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
+  g.n_m_hi = d.m_bits - 7;
+  for (int i = 0; i < g.n_m_hi; ++i) g.a_m_hi[i] = d.a_m[7 + i];
+  g.n_k_hi = d.k_bits - g.kb_bits;
+  for (int i = 0; i < g.n_k_hi; ++i) g.a_k_hi[i] = d.a_k[g.kb_bits + i];
+
+  // shared memory plan
+  g.a32_bytes = 8u << g.tile_bits;
+  g.b_slot_bytes = (uint32_t)g.bn * 128u;
+  const int avail = SMEM_LIMIT - 1024 - 512 - SC * 2 * A16_TILE;
+  g.sb = std::max(3, std::min(MAX_SB, (avail - 3 * (int)g.a32_bytes) / (int)g.b_slot_bytes));
+  g.sa = std::max(1, std::min(MAX_SA, (avail - g.sb * (int)g.b_slot_bytes) / (int)g.a32_bytes));
+  const int smem_bytes =
+      1024 + 512 + SC * 2 * A16_TILE + g.sb * (int)g.b_slot_bytes + g.sa * (int)g.a32_bytes;
+  if (smem_bytes > SMEM_LIMIT) return QFX_OK;
+
+  if (!make_map_b(&mBh, b_hi, 2 * N, 2 * K, (uint32_t)g.bn) ||
+      !make_map_b(&mBm, b_mid, 2 * N, 2 * K, (uint32_t)g.bn)) {
+    qfx_set_error("cuTensorMapEncodeTiled failed");
+    return QFX_ERR_CUDA;
+  }
+  static bool attr = false;
+  if (!attr) {
+    QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  SMEM_LIMIT));
+    attr = true;
+  }
+  const int grid = std::min(g.tiles, ctx->sm_count);
+  tc_fused_bf16x3<<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  QFX_CUDA(cudaGetLastError());
+  ctx->stats.launches_gemm_tc++;
+  ctx->stats.launches_gemm_tc_fused++;
+  ctx->stats.launches_total++;
+  *done = true;
+  return QFX_OK;
+}

@@ -375,8 +375,8 @@ bool make_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t cols, uint32
 // Eligibility: called with roles already swapped (m_bits >= n_bits).
 bool qfx_tc_eligible(const qfx_contract_desc& d) {
   if (d.m_bits < 7) return false;                  // one full 128-row tile
-  if (d.n_bits < 5) return false;                  // UMMA N = 2N >= 64
-  if (d.k_bits < 5) return false;                  // 2K >= one 64-wide k block
+  if (d.n_bits < 4) return false;                  // UMMA N = 2N >= 32 (pre-split path: >= 64)
+  if (d.k_bits < 4) return false;                  // 2K >= 32 (pre-split path: one 64-wide k block)
   const double flops = 8.0 * (double)(1ull << d.m_bits) * (double)(1ull << d.n_bits) *
                        (double)(1ull << d.k_bits);
   return flops >= (double)(1ull << 27);

@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(kThreads) split_a_big(const __grid_constant__ 
   }
   const unsigned e_j1 = 1u << g.f_to_e[0], e_j2 = 1u << g.f_to_e[1];
   const unsigned s_d1 = 1u << g.e_src[0];
-  const bool vec = (g.e_src[0] == 0);
+  const bool vec = (g.e_src[0] == 0) && ((reinterpret_cast<uintptr_t>(g.src) & 15) == 0);
   __syncthreads();
   const unsigned long long n_outer = 1ull << g.o_bits;
   for (unsigned long long o = blockIdx.x; o < n_outer; o += gridDim.x) {

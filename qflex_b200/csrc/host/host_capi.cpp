@@ -144,10 +144,26 @@ long qflex_b200_describe(void* prepared, char* out, uint64_t cap) {
   auto* p = static_cast<qflex::PreparedCircuit*>(prepared);
   std::stringstream ss;
   auto dump = [&](const char* phase, const std::vector<qflex::PlanStep>& steps) {
-    for (const auto& st : steps)
+    for (const auto& st : steps) {
       ss << phase << ' ' << st.level << ' ' << kind_name(st.kind) << ' '
          << (st.kind == qflex::PlanStep::PERMUTE ? st.n_bits : st.desc.m_bits) << ' '
-         << st.desc.n_bits << ' ' << st.desc.k_bits << ' ' << st.label << '\n';
+         << st.desc.n_bits << ' ' << st.desc.k_bits << ' ' << st.label;
+      if (st.kind != qflex::PlanStep::PERMUTE) {
+        // operand bit tables (debugging aid for kernel work)
+        auto tab = [&](const char* name, const int8_t* t, int n) {
+          ss << ' ' << name << '=';
+          for (int i = 0; i < n; ++i) ss << (i ? "," : "") << (int)t[i];
+        };
+        ss << " |";
+        tab("a_m", st.desc.a_m, st.desc.m_bits);
+        tab("a_k", st.desc.a_k, st.desc.k_bits);
+        tab("b_n", st.desc.b_n, st.desc.n_bits);
+        tab("b_k", st.desc.b_k, st.desc.k_bits);
+        tab("c_m", st.desc.c_m, st.desc.m_bits);
+        tab("c_n", st.desc.c_n, st.desc.n_bits);
+      }
+      ss << '\n';
+    }
   };
   dump("flatten", p->session->plan().flatten_steps);
   dump("grid", p->session->plan().steps);
