@@ -41,10 +41,12 @@ constexpr int BM = 128;
 constexpr int BK = 64;                       // bf16 per k block = one 128-byte swizzle row
 constexpr int MAX_BN = 256;
 constexpr int A16_TILE = BM * BK * 2;        // 16 KB: one bf16 tile (hi or mid)
-constexpr int SC = 2;                        // bf16 A stages
-constexpr int FUSED_THREADS = 512;
-constexpr int CONV_WARP0 = 4, EPI_WARP0 = 8;
-constexpr int MAX_SA = 6, MAX_SB = 6;
+constexpr int MAX_SC = 4;                    // bf16 A stages (hi + mid each)
+constexpr int CONV_WARP0 = 4, CONV_WARPS = 8, EPI_WARP0 = CONV_WARP0 + CONV_WARPS;
+constexpr int CONV_THREADS = CONV_WARPS * 32;
+constexpr int FUSED_THREADS = (EPI_WARP0 + 8) * 32;  // 640
+constexpr int MAX_SA = 6, MAX_SB = 6, MAX_ACC = 8;
+constexpr int NUM_BARS = 2 * MAX_SA + 2 * MAX_SC + 2 * MAX_SB + 2 * MAX_ACC;
 constexpr int SMEM_LIMIT = 232448;           // 227 KB opt-in maximum per CTA
 constexpr int MAX_TILE_BITS = 12;
 
@@ -60,14 +62,23 @@ struct FusedArgs {
   int kb_bits;        // complex k bits inside a k block
   int tile_bits;      // 7 + kb_bits
   int sa, sb;         // fp32 A stages, B slots (each slot = one bn x 64 bf16 tile)
+  int sc, acc_stages; // bf16 A stages, TMEM accumulator stages
+  int b_resident;     // all of B' fits the slots (one n tile): loaded once, never released
   uint32_t a32_bytes; // bytes of one fp32 A stage
   uint32_t b_slot_bytes;
   // tile base: address bit of every m bit >= 7 and every k bit >= kb_bits
   int8_t a_m_hi[QFX_MAX_BITS], a_k_hi[QFX_MAX_BITS];
   int n_m_hi, n_k_hi;
-  // converters: XOR masks of the destination byte offset per smem element bit
-  uint32_t cv_mask[MAX_TILE_BITS];
-  uint32_t cv_it[16];
+  // converters: one work item = one 16-byte chunk of an A' row (4 complex k of one
+  // row).  Source / destination byte offsets are XOR-linear in the item index:
+  // bits 0..7 = converter thread, higher bits = iteration.
+  uint32_t cv_src[8], cv_dst[8];
+  uint32_t cv_src_it[4], cv_dst_it[4];
+  int cv_its;         // items per thread per k block
+  uint32_t cv_ok0, cv_ok1;  // source byte offsets of k bit 0 / k bit 1
+  int cv_vec;         // k0, k1 are the two lowest smem element bits: 16-byte loads
+  int8_t row_perm[7]; // tile row bit i is m bit row_perm[i]
+  int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads (timing experiments)
   int8_t c_m[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
 };
 
@@ -201,6 +212,13 @@ __device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
   asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
+// 32-byte global store (sm_100 256-bit vector store): one full L2 sector per thread
+__device__ __forceinline__ void stg256(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]),
+               "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+               : "memory");
+}
+
 template <int N>
 __device__ __forceinline__ void reg_dec() {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
@@ -219,6 +237,33 @@ __device__ __forceinline__ void split_pair(float re, float im, uint32_t& hi, uin
   mid = *reinterpret_cast<const uint32_t*>(&m);
 }
 
+__device__ __forceinline__ float2 lds64(uint32_t addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
+                                       uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c),
+               "r"(d)
+               : "memory");
+}
+
+// Spin on an mbarrier phase.  Bounded: a protocol bug traps instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0, spins = 0;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!ok && ++spins > (1u << 28)) __trap();
+  } while (!ok);
+}
+
 __global__ void __launch_bounds__(FUSED_THREADS, 1)
     tc_fused_bf16x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                     const __grid_constant__ CUtensorMap tmBm, const __grid_constant__ FusedArgs g) {
@@ -226,40 +271,42 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
   const uint32_t smem_base = smem_u32(smem);
-  const uint32_t a16_base = smem_base;                                   // SC x (hi, mid)
-  const uint32_t b_base = a16_base + SC * 2 * A16_TILE;                  // sb slots
+  const uint32_t a16_base = smem_base;                                   // sc x (hi, mid)
+  const uint32_t b_base = a16_base + (uint32_t)g.sc * 2 * A16_TILE;      // sb slots
   const uint32_t a32_base = b_base + (uint32_t)g.sb * g.b_slot_bytes;    // sa stages
   const uint32_t bar_base = a32_base + (uint32_t)g.sa * g.a32_bytes;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + (bar_base - smem_base) + 8 * 32);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + (bar_base - smem_base) + 8 * NUM_BARS);
   auto a_full = [&](int s) { return bar_base + 8u * s; };
   auto a_empty = [&](int s) { return bar_base + 8u * (MAX_SA + s); };
   auto c_full = [&](int s) { return bar_base + 8u * (2 * MAX_SA + s); };
-  auto c_empty = [&](int s) { return bar_base + 8u * (2 * MAX_SA + SC + s); };
-  auto b_full = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * SC + s); };
-  auto b_empty = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * SC + MAX_SB + s); };
-  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * SC + 2 * MAX_SB + s); };
+  auto c_empty = [&](int s) { return bar_base + 8u * (2 * MAX_SA + MAX_SC + s); };
+  auto b_full = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * MAX_SC + s); };
+  auto b_empty = [&](int s) { return bar_base + 8u * (2 * MAX_SA + 2 * MAX_SC + MAX_SB + s); };
+  auto tfull_bar = [&](int s) {
+    return bar_base + 8u * (2 * MAX_SA + 2 * MAX_SC + 2 * MAX_SB + s);
+  };
   auto tempty_bar = [&](int s) {
-    return bar_base + 8u * (2 * MAX_SA + 2 * SC + 2 * MAX_SB + 2 + s);
+    return bar_base + 8u * (2 * MAX_SA + 2 * MAX_SC + 2 * MAX_SB + MAX_ACC + s);
   };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bn = g.bn;
-  const uint32_t tmem_cols = (2 * bn < 32) ? 32u : (uint32_t)(2 * bn);
+  const uint32_t tmem_cols = (uint32_t)max(32, g.acc_stages * bn);
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < MAX_SA; ++s) {
       mbar_init(a_full(s), 1);
-      mbar_init(a_empty(s), 4);
+      mbar_init(a_empty(s), CONV_WARPS);
     }
-    for (int s = 0; s < SC; ++s) {
-      mbar_init(c_full(s), 4);
+    for (int s = 0; s < MAX_SC; ++s) {
+      mbar_init(c_full(s), CONV_WARPS);
       mbar_init(c_empty(s), 1);
     }
     for (int s = 0; s < MAX_SB; ++s) {
       mbar_init(b_full(s), 1);
       mbar_init(b_empty(s), 1);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < MAX_ACC; ++s) {
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), 8);
     }
@@ -278,23 +325,29 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
 
   if (warp < CONV_WARP0) {
     reg_dec<40>();
-    if (warp == 0 && lane == 0) {
-      // ---------------- A producer: one gathered fp32 box per k block
+    if (warp == 0) {
+      // ---------------- A producer: one gathered fp32 box per k block.  Lane i owns
+      // bit i of the tile / k-block index; the tile base (in 16-byte units) is a
+      // warp-wide OR, so the per-tile cost does not grow with the operand rank.
+      const int m_sh = lane < g.n_m_hi ? g.a_m_hi[lane] - 1 : -1;
+      const int k_sh = lane < g.n_k_hi ? g.a_k_hi[lane] - 1 : -1;
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
         const unsigned mt = (unsigned)(t / g.tiles_n);
-        unsigned long long row_base = 0;
-        for (int i = 0; i < g.n_m_hi; ++i)
-          row_base |= (unsigned long long)((mt >> i) & 1u) << g.a_m_hi[i];
+        const unsigned row_base =
+            __reduce_or_sync(0xffffffffu, (m_sh >= 0 && ((mt >> lane) & 1u)) ? (1u << m_sh) : 0u);
         for (int kb = 0; kb < g.kblocks; ++kb) {
-          unsigned long long off = row_base;
-          for (int i = 0; i < g.n_k_hi; ++i)
-            off |= (unsigned long long)(((unsigned)kb >> i) & 1u) << g.a_k_hi[i];
-          mbar_wait(a_empty(stage), phase ^ 1u);
-          mbar_expect_tx(a_full(stage), g.a32_bytes);
-          tma_load_a(&tmA, g.a_rank, a_full(stage), a32_base + (uint32_t)stage * g.a32_bytes,
-                     (int)(off >> 1));
+          const unsigned off16 =
+              row_base | __reduce_or_sync(0xffffffffu, (k_sh >= 0 && (((unsigned)kb >> lane) & 1u))
+                                                           ? (1u << k_sh)
+                                                           : 0u);
+          if (lane == 0) {
+            mbar_wait_spin(a_empty(stage), phase ^ 1u);
+            mbar_expect_tx(a_full(stage), g.a32_bytes);
+            tma_load_a(&tmA, g.a_rank, a_full(stage), a32_base + (uint32_t)stage * g.a32_bytes,
+                       (int)off16);
+          }
           if (++stage == g.sa) {
             stage = 0;
             phase ^= 1u;
@@ -307,10 +360,11 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
         const int nt = t % g.tiles_n;
+        if (g.b_resident && t != (int)blockIdx.x) break;
         for (int kb = 0; kb < g.kblocks; ++kb) {
 #pragma unroll
           for (int part = 0; part < 2; ++part) {
-            mbar_wait(b_empty(slot), phase ^ 1u);
+            if (!g.b_resident) mbar_wait_spin(b_empty(slot), phase ^ 1u);
             mbar_expect_tx(b_full(slot), g.b_slot_bytes);
             tma_load_2d(part == 0 ? &tmBm : &tmBh, b_full(slot),
                         b_base + (uint32_t)slot * g.b_slot_bytes, kb * BK, nt * bn);
@@ -330,7 +384,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       uint32_t cph = 0, bph = 0, acc_phase = 0;
       for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
         for (int ch = 0; ch < g.nchunks; ++ch) {
-          mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+          mbar_wait_spin(tempty_bar(acc), acc_phase ^ 1u);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
           const int kb_end = min(g.kblocks, (ch + 1) * g.chunk);
@@ -338,43 +392,44 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
             const bool first = (kb == ch * g.chunk);
             const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE);
             const uint64_t dAm = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE + A16_TILE);
-            mbar_wait(c_full(cs), cph);
-            mbar_wait(b_full(bs), bph);
+            mbar_wait_spin(c_full(cs), cph);
+            mbar_wait_spin(b_full(bs), bph);
             tc_fence_after();
             const uint64_t dBm = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
-            for (int kk = 0; kk < g.nkk; ++kk) {
+            const int nkk = (g.dbg & 4) ? 0 : g.nkk;
+            for (int kk = 0; kk < nkk; ++kk) {
               const uint64_t adv = (uint64_t)(kk * 32 >> 4);  // 16 bf16 = 32 bytes along K
               umma_bf16(d_tmem, dAh + adv, dBm + adv, idesc, (first && kk == 0) ? 0u : 1u);
             }
-            umma_commit(b_empty(bs));
+            if (!g.b_resident) umma_commit(b_empty(bs));
             if (++bs == g.sb) {
               bs = 0;
-              bph ^= 1u;
+              bph ^= g.b_resident ? 0u : 1u;
             }
-            mbar_wait(b_full(bs), bph);
+            mbar_wait_spin(b_full(bs), bph);
             tc_fence_after();
             const uint64_t dBh = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
-            for (int kk = 0; kk < g.nkk; ++kk) {
+            for (int kk = 0; kk < nkk; ++kk) {
               const uint64_t adv = (uint64_t)(kk * 32 >> 4);
               umma_bf16(d_tmem, dAm + adv, dBh + adv, idesc, 1u);
             }
-            for (int kk = 0; kk < g.nkk; ++kk) {
+            for (int kk = 0; kk < nkk; ++kk) {
               const uint64_t adv = (uint64_t)(kk * 32 >> 4);
               umma_bf16(d_tmem, dAh + adv, dBh + adv, idesc, 1u);
             }
-            umma_commit(b_empty(bs));
+            if (!g.b_resident) umma_commit(b_empty(bs));
             if (++bs == g.sb) {
               bs = 0;
-              bph ^= 1u;
+              bph ^= g.b_resident ? 0u : 1u;
             }
             umma_commit(c_empty(cs));
-            if (++cs == SC) {
+            if (++cs == g.sc) {
               cs = 0;
               cph ^= 1u;
             }
           }
           umma_commit(tfull_bar(acc));  // chunk accumulator complete
-          if (++acc == 2) {
+          if (++acc == g.acc_stages) {
             acc = 0;
             acc_phase ^= 1u;
           }
@@ -382,39 +437,58 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       }
     }
   } else if (warp < EPI_WARP0) {
-    reg_dec<72>();
-    // ---------------- converters: fp32 stage -> bf16 hi / mid (SW128 K-major)
+    reg_dec<64>();
+    // ---------------- converters: fp32 stage -> bf16 hi / mid (SW128 K-major).
+    // One item = the 4 complex (k bits 0,1) of one row = one 16-byte chunk of the
+    // hi tile and one of the mid tile.
     const unsigned ctid = threadIdx.x - CONV_WARP0 * 32;
-    uint32_t dst_t = 0;
+    uint32_t src_t = 0, dst_t = 0;
 #pragma unroll
-    for (int b = 0; b < 7; ++b)
-      if ((ctid >> b) & 1u) dst_t ^= g.cv_mask[b + 1];
-    const uint32_t mask1 = g.cv_mask[0];
-    const int its = 1 << (g.tile_bits - 8);
+    for (int b = 0; b < 8; ++b)
+      if ((ctid >> b) & 1u) {
+        src_t ^= g.cv_src[b];
+        dst_t ^= g.cv_dst[b];
+      }
+    const uint32_t ok0 = g.cv_ok0, ok1 = g.cv_ok1;
+    // 16-byte loads (k0 = lowest smem bit): lanes with bit 2 set read the k1 = 1
+    // half first, so that a quarter warp touches 8 distinct 16-byte bank groups
+    const bool vec = g.cv_vec != 0;
+    const uint32_t flip = (vec && ((ctid >> 2) & 1u)) ? ok1 : 0u;
     int as = 0, cs = 0;
     uint32_t aph = 0, cph = 0;
     for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
       for (int kb = 0; kb < g.kblocks; ++kb) {
-        mbar_wait(a_full(as), aph);
-        mbar_wait(c_empty(cs), cph ^ 1u);
-        const uint32_t src = a32_base + (uint32_t)as * g.a32_bytes + ctid * 16u;
+        mbar_wait_spin(a_full(as), aph);
+        mbar_wait_spin(c_empty(cs), cph ^ 1u);
+        // offsets are XOR-combined first, bases (only 1 KB aligned) added last
+        const uint32_t src = a32_base + (uint32_t)as * g.a32_bytes;
         const uint32_t hi_tile = a16_base + (uint32_t)cs * 2 * A16_TILE;
-        const uint32_t mid_tile = hi_tile + A16_TILE;
-        for (int it0 = 0; it0 < its; it0 += 8) {
-          float4 v[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = lds128(src + (uint32_t)(it0 + j) * 2048u);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t d0 = dst_t ^ g.cv_it[it0 + j];
-            const uint32_t d1 = d0 ^ mask1;
-            uint32_t h, m;
-            split_pair(v[j].x, v[j].y, h, m);
-            sts32(hi_tile + d0, h);
-            sts32(mid_tile + d0, m);
-            split_pair(v[j].z, v[j].w, h, m);
-            sts32(hi_tile + d1, h);
-            sts32(mid_tile + d1, m);
+        for (int it = 0; it < 4; ++it) {
+          if (it < g.cv_its && !(g.dbg & 1)) {
+            const uint32_t s = src_t ^ g.cv_src_it[it];
+            float2 e00, e10, e01, e11;  // e<k0><k1>
+            if (vec) {
+              const float4 p = lds128(src + (s ^ flip)), q = lds128(src + (s ^ flip ^ ok1));
+              const float4 lo = flip ? q : p, hi = flip ? p : q;  // lo: k1 = 0, hi: k1 = 1
+              e00 = make_float2(lo.x, lo.y);
+              e10 = make_float2(lo.z, lo.w);
+              e01 = make_float2(hi.x, hi.y);
+              e11 = make_float2(hi.z, hi.w);
+            } else {
+              e00 = lds64(src + s);
+              e10 = lds64(src + (s ^ ok0));
+              e01 = lds64(src + (s ^ ok1));
+              e11 = lds64(src + (s ^ ok0 ^ ok1));
+            }
+            uint32_t h0, h1, h2, h3, m0, m1, m2, m3;
+            split_pair(e00.x, e00.y, h0, m0);
+            split_pair(e10.x, e10.y, h1, m1);
+            split_pair(e01.x, e01.y, h2, m2);
+            split_pair(e11.x, e11.y, h3, m3);
+            const uint32_t d = hi_tile + (dst_t ^ g.cv_dst_it[it]);
+            sts128(d, h0, h1, h2, h3);
+            sts128(d + A16_TILE, m0, m1, m2, m3);
           }
         }
         fence_proxy_async();
@@ -427,14 +501,14 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
           as = 0;
           aph ^= 1u;
         }
-        if (++cs == SC) {
+        if (++cs == g.sc) {
           cs = 0;
           cph ^= 1u;
         }
       }
     }
   } else {
-    reg_inc<200>();
+    reg_inc<152>();
     // ---------------- epilogue: warp w may only touch TMEM lanes 32*(w%4) .. +31; two
     // warps share a lane group and split the tile's columns.  The tensor core
     // accumulates with truncation, which biases long sums towards zero, so an
@@ -443,6 +517,9 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
     const int lane_group = warp & 3;
     const int half = (warp - EPI_WARP0) >> 2;
     const int row = lane_group * 32 + lane;
+    unsigned m_local = 0;  // tile rows are a bit permutation of the tile's m values
+#pragma unroll
+    for (int i = 0; i < 7; ++i) m_local |= (unsigned)((row >> i) & 1) << g.row_perm[i];
     const int half_cols = bn >> 1;
     const int npieces = half_cols >> 4;
     int acc = 0;
@@ -452,13 +529,13 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       const int nt = t % g.tiles_n, mt = t / g.tiles_n;
       float sum[8][16];
       for (int ch = 0; ch < g.nchunks; ++ch) {
-        mbar_wait(tfull_bar(acc), acc_phase);
+        mbar_wait_spin(tfull_bar(acc), acc_phase);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) +
                                (uint32_t)(acc * bn + half * half_cols);
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
-          if (p < npieces) {
+          if (p < npieces && !(g.dbg & 8)) {
             uint32_t r[16];
             tmem_ld16(t_row + (uint32_t)(p * 16), r);
             if (ch == 0) {
@@ -473,12 +550,12 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty_bar(acc));
-        if (++acc == 2) {
+        if (++acc == g.acc_stages) {
           acc = 0;
           acc_phase ^= 1u;
         }
       }
-      const unsigned long long m = (unsigned long long)mt * BM + row;
+      const unsigned long long m = (unsigned long long)mt * BM + m_local;
       unsigned long long row_off = 0;
       if (g.c_natural) {
         row_off = m * N;
@@ -487,16 +564,14 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       }
 #pragma unroll
       for (int p = 0; p < 8; ++p) {
-        if (p < npieces) {
+        if (p < npieces && !(g.dbg & 2)) {
           // complex column of the first element of this piece
           const unsigned long long n0 =
               ((unsigned long long)nt * bn + half * half_cols + p * 16) >> 1;
           if (g.c_natural) {
-            float4* dst = reinterpret_cast<float4*>(g.C + row_off + n0);
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              dst[j] = make_float4(sum[p][4 * j], sum[p][4 * j + 1], sum[p][4 * j + 2],
-                                   sum[p][4 * j + 3]);
+            float* dst = reinterpret_cast<float*>(g.C + row_off + n0);
+            stg256(dst, &sum[p][0]);
+            stg256(dst + 8, &sum[p][8]);
           } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -604,24 +679,69 @@ bool make_map_a(CUtensorMap* map, const float2* A, const qfx_contract_desc& d, i
          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
     return false;
   g->a_rank = rank;
-  // destination byte offset inside a [128 rows][128 bytes] SW128 tile is XOR-linear
-  // in the element's (row, k) bits
-  for (size_t s = 0; s < bits.size(); ++s) {
-    const int i = bits[s].idx;
-    uint32_t msk;
-    if (bits[s].kind == 0)
-      msk = (1u << (7 + i)) | (i < 3 ? (1u << (4 + i)) : 0u);
-    else
-      msk = i < 2 ? (1u << (2 + i)) : (1u << (4 + (i - 2)));
-    g->cv_mask[s] = msk;
-  }
+  // ---- converter tables.  smem element bit s of the fp32 stage is tile bit bits[s].
   const int nb = (int)bits.size();
-  for (int it = 0; it < 16; ++it) {
-    uint32_t x = 0;
-    for (int b = 0; b + 8 < nb; ++b)
-      if ((it >> b) & 1) x ^= g->cv_mask[8 + b];
-    g->cv_it[it] = x;
+  int sk0 = -1, sk1 = -1;
+  for (int s = 0; s < nb; ++s)
+    if (bits[s].kind == 1 && bits[s].idx == 0) sk0 = s;
+    else if (bits[s].kind == 1 && bits[s].idx == 1) sk1 = s;
+  std::vector<int> item;  // smem bits enumerated by the item index (all but k0, k1)
+  for (int s = 0; s < nb; ++s)
+    if (s != sk0 && s != sk1) item.push_back(s);
+  // tile-row bit order: the three lowest row bits take part in the 128B swizzle
+  // (chunk ^= row & 7); pick them so that lanes 0..2 of a converter warp hit 8
+  // distinct 16-byte bank groups: a lane that walks k bit 2+j owns slot j, a lane
+  // that walks an m bit takes a free slot as row bit.
+  int slot_m[3] = {-1, -1, -1};
+  bool slot_k[3] = {false, false, false};
+  for (int i = 0; i < 3; ++i)
+    if (bits[item[i]].kind == 1) slot_k[bits[item[i]].idx - 2] = true;
+  for (int i = 0; i < 3; ++i)
+    if (bits[item[i]].kind == 0)
+      for (int j = 0; j < 3; ++j)
+        if (!slot_k[j] && slot_m[j] < 0) {
+          slot_m[j] = bits[item[i]].idx;
+          break;
+        }
+  bool used[7] = {false, false, false, false, false, false, false};
+  for (int j = 0; j < 3; ++j)
+    if (slot_m[j] >= 0) used[slot_m[j]] = true;
+  int next = 0;
+  int pos_of_m[7];
+  for (int q = 0; q < 7; ++q) {
+    int mi = q < 3 ? slot_m[q] : -1;
+    if (mi < 0) {
+      while (used[next]) ++next;
+      mi = next;
+      used[mi] = true;
+    }
+    g->row_perm[q] = (int8_t)mi;
+    pos_of_m[mi] = q;
   }
+  auto dst_mask = [&](const TileBit& tb) -> uint32_t {
+    if (tb.kind == 1) return 1u << (4 + (tb.idx - 2));
+    const int q = pos_of_m[tb.idx];
+    return (1u << (7 + q)) | (q < 3 ? (1u << (4 + q)) : 0u);
+  };
+  const int n_item = (int)item.size();  // 9 (K = 16) or 10
+  for (int b = 0; b < 8; ++b) {
+    g->cv_src[b] = 8u << item[b];
+    g->cv_dst[b] = dst_mask(bits[item[b]]);
+  }
+  g->cv_its = 1 << (n_item - 8);
+  for (int it = 0; it < 4; ++it) {
+    uint32_t xs = 0, xd = 0;
+    for (int b = 0; 8 + b < n_item; ++b)
+      if ((it >> b) & 1) {
+        xs ^= 8u << item[8 + b];
+        xd ^= dst_mask(bits[item[8 + b]]);
+      }
+    g->cv_src_it[it] = xs;
+    g->cv_dst_it[it] = xd;
+  }
+  g->cv_ok0 = 8u << sk0;
+  g->cv_ok1 = 8u << sk1;
+  g->cv_vec = (sk0 == 0 && sk1 == 1) ? 1 : 0;
   return true;
 }
 
@@ -690,7 +810,7 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
     if (d.c_n[i] != i) g.c_natural = 0;
   for (int i = 0; i < d.m_bits; ++i)
     if (d.c_m[i] != d.n_bits + i) g.c_natural = 0;
-  if ((reinterpret_cast<uintptr_t>(C) & 15) != 0) g.c_natural = 0;
+  if ((reinterpret_cast<uintptr_t>(C) & 31) != 0) g.c_natural = 0;
   memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
   memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
   g.n_m_hi = d.m_bits - 7;
@@ -698,15 +818,29 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   g.n_k_hi = d.k_bits - g.kb_bits;
   for (int i = 0; i < g.n_k_hi; ++i) g.a_k_hi[i] = d.a_k[g.kb_bits + i];
 
-  // shared memory plan
+  // shared memory plan: bf16 A stages, B slots, fp32 A stages
   g.a32_bytes = 8u << g.tile_bits;
   g.b_slot_bytes = (uint32_t)g.bn * 128u;
-  const int avail = SMEM_LIMIT - 1024 - 512 - SC * 2 * A16_TILE;
-  g.sb = std::max(3, std::min(MAX_SB, (avail - 3 * (int)g.a32_bytes) / (int)g.b_slot_bytes));
-  g.sa = std::max(1, std::min(MAX_SA, (avail - g.sb * (int)g.b_slot_bytes) / (int)g.a32_bytes));
-  const int smem_bytes =
-      1024 + 512 + SC * 2 * A16_TILE + g.sb * (int)g.b_slot_bytes + g.sa * (int)g.a32_bytes;
-  if (smem_bytes > SMEM_LIMIT) return QFX_OK;
+  g.acc_stages = std::min(MAX_ACC, 512 / g.bn);
+  const int fixed = 1024 + 512;
+  const int slot = (int)g.b_slot_bytes, a32 = (int)g.a32_bytes, a16 = 2 * A16_TILE;
+  g.sc = 2;
+  g.sb = 3;
+  g.sa = 2;
+  g.b_resident = (g.tiles_n == 1 && 2 * g.kblocks <= MAX_SB) ? 1 : 0;
+  if (g.b_resident) g.sb = 2 * g.kblocks;
+  auto total = [&]() { return fixed + g.sc * a16 + g.sb * slot + g.sa * a32; };
+  if (total() > SMEM_LIMIT) return QFX_OK;
+  // grow round-robin while it fits: fp32 stages (memory-level parallelism) first
+  for (bool grew = true; grew;) {
+    grew = false;
+    if (g.sa < MAX_SA && total() + a32 <= SMEM_LIMIT) { ++g.sa; grew = true; }
+    if (!g.b_resident && g.sb < MAX_SB && total() + slot <= SMEM_LIMIT) { ++g.sb; grew = true; }
+    if (g.sc < MAX_SC && g.sc < g.sa && total() + a16 <= SMEM_LIMIT) { ++g.sc; grew = true; }
+  }
+  const int smem_bytes = total();
+  if (const char* e = getenv("QFLEX_FUSED_DBG")) g.dbg = atoi(e);
+  if (const char* e = getenv("QFLEX_FUSED_ACC")) g.acc_stages = std::min(g.acc_stages, std::max(1, atoi(e)));
 
   if (!make_map_b(&mBh, b_hi, 2 * N, 2 * K, (uint32_t)g.bn) ||
       !make_map_b(&mBm, b_mid, 2 * N, 2 * K, (uint32_t)g.bn)) {
