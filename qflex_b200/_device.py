@@ -48,6 +48,8 @@ class DeviceError(RuntimeError):
 
 
 def load(path=DEFAULT_DEVICE_LIB):
+    # A/B experiments (tools/ only): alternative build of the same library
+    path = os.environ.get("QFLEX_B200_DEVICE_LIB", path)
     if not os.path.exists(path):
         raise DeviceError("%s not found: run __graft_entry__.build() (no CPU fallback)" % path)
     c = ctypes.CDLL(path)

@@ -219,6 +219,17 @@ __device__ __forceinline__ void stg256(float* p, const float* v) {
                : "memory");
 }
 
+// one lane of a converged warp (the same lane every time)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 template <int N>
 __device__ __forceinline__ void reg_dec() {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
@@ -375,60 +386,77 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
           }
         }
       }
-    } else if (warp == 1 && lane == 0) {
-      // ---------------- MMA issuer
+    } else if (warp == 1) {
+      // ---------------- MMA issuer.  The whole warp runs the (warp-uniform) control
+      // flow and the barrier waits, so that descriptors live in uniform registers
+      // and there are only a handful of instructions between two tcgen05.mma; one
+      // elected lane issues the MMAs and commits.  The issue rate of this warp is
+      // on the critical path of the kernel.
+      const bool leader = elect_one();
       // instruction descriptor: D=f32, A=B=bf16, both K-major, N=bn, M=128
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) |
                              ((uint32_t)(BM >> 4) << 24);
       int cs = 0, bs = 0, acc = 0;
       uint32_t cph = 0, bph = 0, acc_phase = 0;
+      const int nkk = (g.dbg & 4) ? 0 : g.nkk;
       for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
         for (int ch = 0; ch < g.nchunks; ++ch) {
           mbar_wait_spin(tempty_bar(acc), acc_phase ^ 1u);
-          tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
           const int kb_end = min(g.kblocks, (ch + 1) * g.chunk);
           for (int kb = ch * g.chunk; kb < kb_end; ++kb) {
-            const bool first = (kb == ch * g.chunk);
+            const uint32_t first_acc = (kb == ch * g.chunk) ? 0u : 1u;
             const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE);
-            const uint64_t dAm = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE + A16_TILE);
+            const uint64_t dAm = dAh + (uint64_t)(A16_TILE >> 4);
+            const uint64_t dBm = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
             mbar_wait_spin(c_full(cs), cph);
             mbar_wait_spin(b_full(bs), bph);
             tc_fence_after();
-            const uint64_t dBm = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
-            const int nkk = (g.dbg & 4) ? 0 : g.nkk;
-            for (int kk = 0; kk < nkk; ++kk) {
-              const uint64_t adv = (uint64_t)(kk * 32 >> 4);  // 16 bf16 = 32 bytes along K
-              umma_bf16(d_tmem, dAh + adv, dBm + adv, idesc, (first && kk == 0) ? 0u : 1u);
+            if (leader) {
+              if (nkk == 4) {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  umma_bf16(d_tmem, dAh + 2 * kk, dBm + 2 * kk, idesc, kk == 0 ? first_acc : 1u);
+              } else {
+                for (int kk = 0; kk < nkk; ++kk)
+                  umma_bf16(d_tmem, dAh + 2 * kk, dBm + 2 * kk, idesc, kk == 0 ? first_acc : 1u);
+              }
+              if (!g.b_resident) umma_commit(b_empty(bs));
             }
-            if (!g.b_resident) umma_commit(b_empty(bs));
             if (++bs == g.sb) {
               bs = 0;
               bph ^= g.b_resident ? 0u : 1u;
             }
+            const uint64_t dBh = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
             mbar_wait_spin(b_full(bs), bph);
             tc_fence_after();
-            const uint64_t dBh = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
-            for (int kk = 0; kk < nkk; ++kk) {
-              const uint64_t adv = (uint64_t)(kk * 32 >> 4);
-              umma_bf16(d_tmem, dAm + adv, dBh + adv, idesc, 1u);
+            if (leader) {
+              if (nkk == 4) {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  umma_bf16(d_tmem, dAm + 2 * kk, dBh + 2 * kk, idesc, 1u);
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  umma_bf16(d_tmem, dAh + 2 * kk, dBh + 2 * kk, idesc, 1u);
+              } else {
+                for (int kk = 0; kk < nkk; ++kk)
+                  umma_bf16(d_tmem, dAm + 2 * kk, dBh + 2 * kk, idesc, 1u);
+                for (int kk = 0; kk < nkk; ++kk)
+                  umma_bf16(d_tmem, dAh + 2 * kk, dBh + 2 * kk, idesc, 1u);
+              }
+              if (!g.b_resident) umma_commit(b_empty(bs));
+              umma_commit(c_empty(cs));
             }
-            for (int kk = 0; kk < nkk; ++kk) {
-              const uint64_t adv = (uint64_t)(kk * 32 >> 4);
-              umma_bf16(d_tmem, dAh + adv, dBh + adv, idesc, 1u);
-            }
-            if (!g.b_resident) umma_commit(b_empty(bs));
             if (++bs == g.sb) {
               bs = 0;
               bph ^= g.b_resident ? 0u : 1u;
             }
-            umma_commit(c_empty(cs));
             if (++cs == g.sc) {
               cs = 0;
               cph ^= 1u;
             }
           }
-          umma_commit(tfull_bar(acc));  // chunk accumulator complete
+          if (leader) umma_commit(tfull_bar(acc));  // chunk accumulator complete
           if (++acc == g.acc_stages) {
             acc = 0;
             acc_phase ^= 1u;
