@@ -219,6 +219,7 @@ def main():
     import torch
     import torch.distributed as dist
     import qflex_b200
+    from qflex_b200 import sharded
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -237,10 +238,8 @@ def main():
         torch.cuda.synchronize()
 
     def allreduce_amps(a):
-        t = torch.from_numpy(np.ascontiguousarray(a).view(np.float64)).to(dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.SUM)  # one NCCL sum of 2*n_amps doubles
-        return t.cpu().numpy().view(np.complex128)
+        # one NCCL sum of 2*n_amps doubles (qflex_b200/sharded.py)
+        return sharded.allreduce_amplitudes(a, device=dev)
 
     def max_over_ranks(x):
         t = torch.tensor([x], dtype=torch.float64, device=dev)
@@ -350,6 +349,16 @@ def main():
                 "unit": "TFLOP/s"}
     roof["frac"] = roof["achieved"] / roof["peak"]
     roof["traffic"] = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel class
+        # from one `ncu --set full` capture (profiles/ncu_traffic.json names the file)
+        with open(tpath) as f:
+            t = json.load(f).get("%d,%d,%d" % dom_key[1:])
+        if t:
+            roof["traffic"] = t["dram_bytes_per_launch"]
+            roof["traffic_source"] = t["source"]
+            roof["algorithmic_bytes_per_launch"] = dom["bytes"] / dom["launches"]
     roof["kernel"] = "contract m=%d n=%d k=%d bits" % dom_key[1:]
     roof["launches"] = int(dom["launches"])
     roof["ms_per_launch"] = per_launch_ms

@@ -175,17 +175,21 @@ class HostLibrary:
                  memory_limit=None, device=0, rank=0, world=1, precision="auto",
                  max_amplitudes=1 << 20):
         """EvaluateCircuit: returns ([(bitstring, complex)], stats dict)."""
-        cap = max_amplitudes
-        amps = np.zeros(2 * cap, dtype=np.float64)
-        stats = np.zeros(N_STATS, dtype=np.float64)
-        states = ctypes.create_string_buffer(cap * 128 if cap < 4096 else cap * 64)
-        err = ctypes.create_string_buffer(1 << 16)
-        n = self._c.qflex_b200_evaluate(
-            _text(circuit), _text(ordering), _text(grid), _text(initial_state),
-            _text(final_state), _memory_bytes(memory_limit), device, rank, world,
-            PRECISIONS[precision], states, len(states),
-            amps.ctypes.data_as(ctypes.c_void_p), cap,
-            stats.ctypes.data_as(ctypes.c_void_p), err, len(err))
+        # output buffers sized for the common case first (a 2^20-entry table costs
+        # ~80 MB of zeroed host memory per call); grown once when the engine says so
+        for cap in sorted({min(4096, max_amplitudes), max_amplitudes}):
+            amps = np.zeros(2 * cap, dtype=np.float64)
+            stats = np.zeros(N_STATS, dtype=np.float64)
+            states = ctypes.create_string_buffer(cap * 128 if cap <= 4096 else cap * 64)
+            err = ctypes.create_string_buffer(1 << 16)
+            n = self._c.qflex_b200_evaluate(
+                _text(circuit), _text(ordering), _text(grid), _text(initial_state),
+                _text(final_state), _memory_bytes(memory_limit), device, rank, world,
+                PRECISIONS[precision], states, len(states),
+                amps.ctypes.data_as(ctypes.c_void_p), cap,
+                stats.ctypes.data_as(ctypes.c_void_p), err, len(err))
+            if n >= 0 or not err.value.decode().endswith("_out too small"):
+                break
         if n < 0:
             raise QflexError(err.value.decode())
         names = states.value.decode().split("\n")

@@ -216,11 +216,14 @@ long qflex_b200_evaluate(const char* circuit_text, const char* ordering_text,
     where.precision = precision;
     qflex::ExecStats stats;
     auto prepared = qflex::PrepareCircuit(&input, where);
+    // capacity checks before any device work, so a caller can retry cheaply
+    if (prepared->output_states.size() > amps_cap_complex)
+      throw std::string("amps_out too small");
+    const std::string states = join_states(prepared->output_states);
+    if (states.size() + 1 > states_cap) throw std::string("states_out too small");
     std::vector<std::complex<double>> amps;
     prepared->session->Contract(rank, world, &amps);
     if (amps.size() > amps_cap_complex) throw std::string("amps_out too small");
-    const std::string states = join_states(prepared->output_states);
-    if (states.size() + 1 > states_cap) throw std::string("states_out too small");
     std::memcpy(states_out, states.c_str(), states.size() + 1);
     for (std::size_t i = 0; i < amps.size(); ++i) {
       amps_out[2 * i] = amps[i].real();

@@ -1,0 +1,88 @@
+"""The N>1 path on CPU: two processes (gloo), each contracting the slices dealt
+to its rank on the CPU-emulated device ABI, then the one all-reduce of
+qflex_b200/sharded.py.  Mirrors what bench.py / a torchrun launch does on the
+GPUs with NCCL."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+
+from tests import support
+
+WORKER = r"""
+import json, os, sys
+sys.path.insert(0, %(root)r)
+import numpy as np
+import torch.distributed as dist
+from tests import support
+from qflex_b200 import sharded
+dist.init_process_group("gloo")
+lib = support.emulated_host_library()
+case = support.CASES[%(case)r]
+c, o, g = support.case_texts(case)
+p = lib.prepare(c, o, g, memory_limit=8 << 30)
+full = sharded.contract_sharded(p)
+leaves = p.stats["leaves"]
+p.close()
+res, _ = sharded.evaluate_sharded(lib, c, o, g, memory_limit=8 << 30)
+print("RESULT " + json.dumps({"rank": dist.get_rank(), "leaves": leaves,
+      "re": full.real.tolist(), "im": full.imag.tolist(),
+      "ev_states": [s for s, _ in res],
+      "ev_re": [a.real for _, a in res], "ev_im": [a.imag for _, a in res]}))
+dist.destroy_process_group()
+"""
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _run_world(case, world=2):
+    support.emulated_host_library()  # build once, not concurrently in the workers
+    port = _free_port()
+    code = WORKER % dict(root=support.ROOT, case=case)
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK=str(r),
+                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), OMP_NUM_THREADS="2")
+        procs.append(subprocess.Popen([sys.executable, "-c", code], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = []
+    for p in procs:
+        out, err = p.communicate(timeout=300)
+        assert p.returncode == 0, err[-3000:]
+        line = [l for l in out.splitlines() if l.startswith("RESULT ")][-1]
+        outs.append(json.loads(line[7:]))
+    return outs
+
+
+def test_two_ranks_allreduce_to_the_reference_amplitudes(golden):
+    name = "bristlecone_48_1-16-1"   # 2 bond-cut slices x 4 terminal leaves
+    outs = _run_world(name, 2)
+    g = golden[name]
+    want = np.array(g["re"]) + 1j * np.array(g["im"])
+    assert sum(o["leaves"] for o in outs) == 8          # every leaf exactly once
+    assert all(o["leaves"] > 0 for o in outs)           # and both ranks worked
+    for o in outs:
+        got = np.array(o["re"]) + 1j * np.array(o["im"])
+        assert support.rel_err(got, want) < 1e-4
+        ev = np.array(o["ev_re"]) + 1j * np.array(o["ev_im"])
+        assert o["ev_states"] == g["states"]
+        assert support.rel_err(ev, want) < 1e-4
+    # the all-reduce leaves the same table on both ranks
+    assert outs[0]["re"] == outs[1]["re"] and outs[0]["im"] == outs[1]["im"]
+
+
+def test_single_process_is_the_identity_collective(emul, golden):
+    from qflex_b200 import sharded
+    name = "test"
+    p = emul.prepare(*support.case_texts(support.CASES[name]))
+    got = sharded.contract_sharded(p)
+    p.close()
+    g = golden[name]
+    assert support.rel_err(got, np.array(g["re"]) + 1j * np.array(g["im"])) < 1e-4
