@@ -142,6 +142,7 @@ typedef struct qfx_stats {
   double flops;
   double bytes;
   uint64_t launches_gemm_tc_fused; /* subset of launches_gemm_tc: in-kernel fp32->bf16 split */
+  uint64_t launches_gemm_tc_pair;  /* subset of launches_gemm_tc_fused: CTA-pair kernel (cta_group::2) */
 } qfx_stats;
 int qfx_stats_get(qfx_ctx* ctx, qfx_stats* out);
 int qfx_stats_reset(qfx_ctx* ctx);

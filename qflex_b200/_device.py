@@ -40,6 +40,7 @@ class Stats(ctypes.Structure):
         ("launches_permute", ctypes.c_uint64), ("launches_copy", ctypes.c_uint64),
         ("flops", ctypes.c_double), ("bytes", ctypes.c_double),
         ("launches_gemm_tc_fused", ctypes.c_uint64),
+        ("launches_gemm_tc_pair", ctypes.c_uint64),
     ]
 
 

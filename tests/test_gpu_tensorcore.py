@@ -143,3 +143,36 @@ def test_ffma_precision_request_is_honoured(ctx):
     err, used = _run(ctx, _natural(13, 6, 6), rng, precision=1)
     assert err < 1e-5
     assert used["launches_gemm_tc"] == 0 and used["launches_gemm_ffma"] == 1, used
+
+
+# ---- CTA-pair kernel (tc_pair.cu): k, n <= 8 bits and at least 74 256-row tiles
+@pytest.mark.parametrize("m,n,k,groups", [
+    (15, 8, 8, None),      # two n tiles, 8 k blocks: the 2^20 x 256 x 256 family
+    (15, 8, 8, (1, 4)),    # a_k = 4..7, 16..19
+    (15, 8, 8, (0, 2)),
+    (16, 7, 8, None),      # one n tile of 256 columns, two accumulator sets
+    (16, 6, 7, (1, 3)),
+    (17, 4, 4, (1,)),      # 2^24 x 16 x 16 family: resident B', half-filled k block
+    (17, 4, 4, (4,)),
+    (16, 5, 5, None),
+    (16, 8, 4, None),
+    (15, 4, 8, (0, 1)),
+])
+def test_pair_kernel_matches_oracle(ctx, m, n, k, groups):
+    rng = np.random.default_rng(1000 * m + 10 * n + k)
+    t = _natural(m, n, k) if groups is None else _grouped(m, n, k, groups)
+    err, used = _run(ctx, t, rng)
+    assert err < TOL_TC
+    assert ctx.stats()["launches_gemm_tc_pair"] >= 1
+
+
+def test_pair_kernel_scattered_c_and_repeatability(ctx):
+    rng = np.random.default_rng(78)
+    t = _grouped(15, 6, 6, (1, 2))
+    pc = [int(x) for x in rng.permutation(15 + 6)]
+    t["c_m"], t["c_n"] = pc[:15], pc[15:]
+    before = ctx.stats()["launches_gemm_tc_pair"]
+    e1, _ = _run(ctx, t, np.random.default_rng(5))
+    e2, _ = _run(ctx, t, np.random.default_rng(5))
+    assert e1 < TOL_TC and e1 == e2
+    assert ctx.stats()["launches_gemm_tc_pair"] == before + 2
