@@ -372,6 +372,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
     int set = 0;
     uint32_t set_phase = 0;
     const unsigned long long N = 1ull << g.n_bits;
+    // quad-transposed stores: the tile rows of the four lanes of this lane's quad
+    unsigned mq[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = lane_group * 32 + (lane & ~3) + i;
+      mq[i] = 0;
+#pragma unroll
+      for (int b = 0; b < 7; ++b) mq[i] |= (unsigned)((r >> b) & 1) << g.row_perm[b];
+    }
+    const bool quad_stores = g.c_natural && npieces >= 4 && !(g.dbg & 32);
     for (int t = pair0; t < g.tiles; t += pair_step) {
       const unsigned long long m = (2ull * (unsigned long long)t + rank) * BM + m_local;
       unsigned long long row_off = 0;
@@ -399,12 +409,38 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+        if (quad_stores) {
+          float* tile_c = reinterpret_cast<float*>(
+              g.C + (2ull * (unsigned long long)t + rank) * BM * N);
+          const int col0 = nt * bn + half * half_cols + 8 * (lane & 3);  // float column
+#pragma unroll
+          for (int pp = 0; pp < 4; ++pp) {
+            if (2 * pp < npieces && !(g.dbg & 2)) {
+              quad_transpose(sum[2 * pp], sum[2 * pp + 1], lane);
+              float* dst = tile_c + col0 + pp * 32;
+              stg256(dst + 2ull * mq[0] * N, &sum[2 * pp][0]);
+              stg256(dst + 2ull * mq[1] * N, &sum[2 * pp][8]);
+              stg256(dst + 2ull * mq[2] * N, &sum[2 * pp + 1][0]);
+              stg256(dst + 2ull * mq[3] * N, &sum[2 * pp + 1][8]);
+            }
+          }
+          continue;
+        }
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
           if (p < npieces && !(g.dbg & 2)) {
             const unsigned long long n0 =
                 ((unsigned long long)nt * bn + half * half_cols + p * 16) >> 1;
-            if (g.c_natural) {
+            if (g.dbg & 16) {
+              // timing experiment: same bytes into the same tile, but every warp store
+              // covers 1 KB of contiguous memory (results are wrong)
+              const unsigned long long tile0 =
+                  ((2ull * (unsigned long long)t + rank) * BM + lane_group * 32) * N;
+              float* dst = reinterpret_cast<float*>(g.C + tile0) +
+                           (size_t)((nt * 2 + half) * 16 + p * 2) * 256 + lane * 8;
+              stg256(dst, &sum[p][0]);
+              stg256(dst + 256, &sum[p][8]);
+            } else if (g.c_natural) {
               float* dst = reinterpret_cast<float*>(g.C + row_off + n0);
               stg256(dst, &sum[p][0]);
               stg256(dst + 8, &sum[p][8]);
