@@ -60,6 +60,8 @@ struct FusedArgs {
   uint32_t cv_ok0, cv_ok1;  // source byte offsets of k bit 0 / k bit 1
   int cv_vec;         // k0, k1 are the two lowest smem element bits: 16-byte loads
   int8_t row_perm[7]; // tile row bit i is m bit row_perm[i]
+  int ksplit;         // tc_fused split-K: work items = tiles * ksplit, kblocks = k blocks per item
+  float2* part;       // split-K partial results [ksplit][M][N] (natural layout)
   int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads (timing experiments)
   int8_t c_m[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
 };

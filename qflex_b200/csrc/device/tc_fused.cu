@@ -94,13 +94,14 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       const int k_sh = lane < g.n_k_hi ? g.a_k_hi[lane] - 1 : -1;
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+      for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
+        const int t = w % g.tiles, kb0 = (w / g.tiles) * g.kblocks;
         const unsigned mt = (unsigned)(t / g.tiles_n);
         const unsigned row_base =
             __reduce_or_sync(0xffffffffu, (m_sh >= 0 && ((mt >> lane) & 1u)) ? (1u << m_sh) : 0u);
         for (int kb = 0; kb < g.kblocks; ++kb) {
           const unsigned off16 =
-              row_base | __reduce_or_sync(0xffffffffu, (k_sh >= 0 && (((unsigned)kb >> lane) & 1u))
+              row_base | __reduce_or_sync(0xffffffffu, (k_sh >= 0 && (((unsigned)(kb0 + kb) >> lane) & 1u))
                                                            ? (1u << k_sh)
                                                            : 0u);
           if (lane == 0) {
@@ -119,10 +120,11 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       // ---------------- B producer: B'_mid then B'_hi of every k block
       int slot = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+      for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
+        const int t = w % g.tiles, kb0 = (w / g.tiles) * g.kblocks;
         const int nt = t % g.tiles_n;
-        if (g.b_resident && t != (int)blockIdx.x) break;
-        for (int kb = 0; kb < g.kblocks; ++kb) {
+        if (g.b_resident && w != (int)blockIdx.x) break;
+        for (int kb = kb0; kb < kb0 + g.kblocks; ++kb) {
 #pragma unroll
           for (int part = 0; part < 2; ++part) {
             if (!g.b_resident) mbar_wait_spin(b_empty(slot), phase ^ 1u);
@@ -149,7 +151,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       int cs = 0, bs = 0, acc = 0;
       uint32_t cph = 0, bph = 0, acc_phase = 0;
       const int nkk = (g.dbg & 4) ? 0 : g.nkk;
-      for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+      for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
         for (int ch = 0; ch < g.nchunks; ++ch) {
           mbar_wait_spin(tempty_bar(acc), acc_phase ^ 1u);
           const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
@@ -234,7 +236,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
     const uint32_t flip = (vec && ((ctid >> 2) & 1u)) ? ok1 : 0u;
     int as = 0, cs = 0;
     uint32_t aph = 0, cph = 0;
-    for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+    for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
       for (int kb = 0; kb < g.kblocks; ++kb) {
         mbar_wait_spin(a_full(as), aph);
         mbar_wait_spin(c_empty(cs), cph ^ 1u);
@@ -303,8 +305,23 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
     int acc = 0;
     uint32_t acc_phase = 0;
     const unsigned long long N = 1ull << g.n_bits;
-    for (int t = blockIdx.x; t < g.tiles; t += gridDim.x) {
+    // quad-transposed stores (tc_common.cuh): tile rows of the four lanes of this quad
+    unsigned mq[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = lane_group * 32 + (lane & ~3) + i;
+      mq[i] = 0;
+#pragma unroll
+      for (int b = 0; b < 7; ++b) mq[i] |= (unsigned)((r >> b) & 1) << g.row_perm[b];
+    }
+    const bool quad_stores = g.c_natural && npieces >= 4 && !(g.dbg & 32);
+    for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
+      const int t = w % g.tiles;
       const int nt = t % g.tiles_n, mt = t / g.tiles_n;
+      // split-K: this item's partial sums go to its own [M][N] slab (summed in a
+      // fixed order by tc_splitk_finish)
+      float2* const Cout =
+          g.ksplit > 1 ? g.part + ((unsigned long long)(w / g.tiles) << (g.m_bits + g.n_bits)) : g.C;
       float sum[8][16];
       for (int ch = 0; ch < g.nchunks; ++ch) {
         mbar_wait_spin(tfull_bar(acc), acc_phase);
@@ -340,6 +357,22 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       } else {
         for (int q = 0; q < g.m_bits; ++q) row_off |= ((m >> q) & 1ull) << g.c_m[q];
       }
+      if (quad_stores) {
+        float* tile_c = reinterpret_cast<float*>(Cout + (unsigned long long)mt * BM * N);
+        const int col0 = nt * bn + half * half_cols + 8 * (lane & 3);  // float column
+#pragma unroll
+        for (int pp = 0; pp < 4; ++pp) {
+          if (2 * pp < npieces && !(g.dbg & 2)) {
+            quad_transpose(sum[2 * pp], sum[2 * pp + 1], lane);
+            float* dst = tile_c + col0 + pp * 32;
+            stg256(dst + 2ull * mq[0] * N, &sum[2 * pp][0]);
+            stg256(dst + 2ull * mq[1] * N, &sum[2 * pp][8]);
+            stg256(dst + 2ull * mq[2] * N, &sum[2 * pp + 1][0]);
+            stg256(dst + 2ull * mq[3] * N, &sum[2 * pp + 1][8]);
+          }
+        }
+        continue;
+      }
 #pragma unroll
       for (int p = 0; p < 8; ++p) {
         if (p < npieces && !(g.dbg & 2)) {
@@ -347,7 +380,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
           const unsigned long long n0 =
               ((unsigned long long)nt * bn + half * half_cols + p * 16) >> 1;
           if (g.c_natural) {
-            float* dst = reinterpret_cast<float*>(g.C + row_off + n0);
+            float* dst = reinterpret_cast<float*>(Cout + row_off + n0);
             stg256(dst, &sum[p][0]);
             stg256(dst + 8, &sum[p][8]);
           } else {
@@ -356,7 +389,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
               const unsigned long long n = n0 + j;
               unsigned long long co = 0;
               for (int q = 0; q < g.n_bits; ++q) co |= ((n >> q) & 1ull) << g.c_n[q];
-              g.C[row_off + co] = make_float2(sum[p][2 * j], sum[p][2 * j + 1]);
+              Cout[row_off + co] = make_float2(sum[p][2 * j], sum[p][2 * j + 1]);
             }
           }
         }
@@ -371,6 +404,41 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
                  "r"(tmem_cols)
                  : "memory");
+  }
+}
+
+struct FinishArgs {
+  const float2* part;
+  float2* C;
+  int m_bits, n_bits, ksplit, natural;
+  int8_t c_m[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
+};
+
+// C = sum over the split-K slabs, in slab order; two complex per thread (n >= 4 bits)
+__global__ void tc_splitk_finish(const __grid_constant__ FinishArgs g) {
+  const unsigned long long total = 1ull << (g.m_bits + g.n_bits - 1);
+  const float4* p = reinterpret_cast<const float4*>(g.part);
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+       i < total; i += (unsigned long long)gridDim.x * blockDim.x) {
+    float4 s = p[i];
+    for (int k = 1; k < g.ksplit; ++k) {
+      const float4 v = p[((unsigned long long)k << (g.m_bits + g.n_bits - 1)) + i];
+      s.x += v.x;
+      s.y += v.y;
+      s.z += v.z;
+      s.w += v.w;
+    }
+    if (g.natural) {
+      reinterpret_cast<float4*>(g.C)[i] = s;
+    } else {
+      const unsigned long long e = 2 * i;
+      const unsigned long long n = e & ((1ull << g.n_bits) - 1ull), m = e >> g.n_bits;
+      unsigned long long o = 0;
+      for (int q = 1; q < g.n_bits; ++q) o |= ((n >> q) & 1ull) << g.c_n[q];
+      for (int q = 0; q < g.m_bits; ++q) o |= ((m >> q) & 1ull) << g.c_m[q];
+      g.C[o] = make_float2(s.x, s.y);
+      g.C[o | (1ull << g.c_n[0])] = make_float2(s.z, s.w);
+    }
   }
 }
 
@@ -414,9 +482,22 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   CUtensorMap mA, mBh, mBm;
   if (!make_map_a(&mA, A, d, g.kb_bits, span, &g)) return QFX_OK;
 
-  // workspace: B' hi/mid (2N x 2K bf16 each)
+  // split-K: few output tiles and a long K (the final merges, e.g. 2^12 x 256 x 2^16
+  // = 64 tiles for 148 SMs).  Work items = tiles x ksplit, each item accumulates a
+  // power-of-two share of the k blocks into its own [M][N] slab; tc_splitk_finish
+  // adds the slabs in a fixed order (deterministic) and applies C's layout.
+  const int kblocks_all = (int)std::max<uint64_t>(1, (2 * K) / BK);
+  const int tiles_all = (int)((M / BM) * ((2 * N) / std::min<uint64_t>(2 * N, MAX_BN)));
+  int ksplit = 1;
+  if (tiles_all < 2 * ctx->sm_count && kblocks_all >= 64) {
+    while (tiles_all * ksplit * 2 <= 8 * ctx->sm_count && kblocks_all / (ksplit * 2) >= 8) ksplit *= 2;
+  }
+  if (const char* e = getenv("QFLEX_TC_KSPLIT")) ksplit = std::max(1, atoi(e));
+  const size_t part_bytes = ksplit > 1 ? (size_t)ksplit * M * N * 8 : 0;
+
+  // workspace: B' hi/mid (2N x 2K bf16 each), then the split-K slabs
   const size_t b_bytes = (size_t)N * K * 8;
-  int rc = qfx_ensure_ws(ctx, 2 * b_bytes + 4096);
+  int rc = qfx_ensure_ws(ctx, 2 * b_bytes + 4096 + part_bytes);
   if (rc) return rc;
   uint8_t* ws = reinterpret_cast<uint8_t*>(ctx->ws);
   uint32_t* b_hi = reinterpret_cast<uint32_t*>(ws);
@@ -425,11 +506,13 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   if (rc) return rc;
 
   g.C = C;
+  g.ksplit = ksplit;
+  g.part = reinterpret_cast<float2*>(ws + ((2 * b_bytes + 4095) & ~(size_t)4095));
   g.m_bits = d.m_bits;
   g.n_bits = d.n_bits;
-  g.kblocks = (int)std::max<uint64_t>(1, (2 * K) / BK);
+  g.kblocks = kblocks_all / ksplit;
   g.nkk = (int)std::min<uint64_t>(4, (2 * K) / 16);
-  g.chunk = ctx->tc_chunk > 0 ? ctx->tc_chunk : 2;
+  g.chunk = ctx->tc_chunk > 0 ? ctx->tc_chunk : 4;
   g.nchunks = (g.kblocks + g.chunk - 1) / g.chunk;
   g.bn = (int)std::min<uint64_t>(2 * N, MAX_BN);
   g.tiles_n = (int)((2 * N) / g.bn);
@@ -440,6 +523,8 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   for (int i = 0; i < d.m_bits; ++i)
     if (d.c_m[i] != d.n_bits + i) g.c_natural = 0;
   if ((reinterpret_cast<uintptr_t>(C) & 31) != 0) g.c_natural = 0;
+  const int c_is_natural = g.c_natural;
+  if (ksplit > 1) g.c_natural = 1;  // the slabs are [M][N]; C's layout is applied by the finish
   memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
   memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
   g.n_m_hi = d.m_bits - 7;
@@ -456,7 +541,7 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   g.sc = 2;
   g.sb = 3;
   g.sa = 2;
-  g.b_resident = (g.tiles_n == 1 && 2 * g.kblocks <= MAX_SB) ? 1 : 0;
+  g.b_resident = (ksplit == 1 && g.tiles_n == 1 && 2 * g.kblocks <= MAX_SB) ? 1 : 0;
   if (g.b_resident) g.sb = 2 * g.kblocks;
   auto total = [&]() { return fixed + g.sc * a16 + g.sb * slot + g.sa * a32; };
   if (total() > SMEM_LIMIT) return QFX_OK;
@@ -482,9 +567,27 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
                                   SMEM_LIMIT));
     attr = true;
   }
-  const int grid = std::min(g.tiles, ctx->sm_count);
+  const int grid = std::min(g.tiles * g.ksplit, ctx->sm_count);
   tc_fused_bf16x3<<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
   QFX_CUDA(cudaGetLastError());
+  if (ksplit > 1) {
+    FinishArgs f{};
+    f.part = g.part;
+    f.C = C;
+    f.m_bits = d.m_bits;
+    f.n_bits = d.n_bits;
+    f.ksplit = ksplit;
+    f.natural = c_is_natural;
+    memcpy(f.c_m, d.c_m, QFX_MAX_BITS);
+    memcpy(f.c_n, d.c_n, QFX_MAX_BITS);
+    const unsigned long long pairs = (M * N) / 2;
+    const unsigned fb = (unsigned)std::min<unsigned long long>((pairs + 255) / 256,
+                                                               16ull * ctx->sm_count);
+    tc_splitk_finish<<<fb, 256, 0, ctx->stream>>>(f);
+    QFX_CUDA(cudaGetLastError());
+    ctx->stats.launches_reduce++;
+    ctx->stats.launches_total++;
+  }
   ctx->stats.launches_gemm_tc++;
   ctx->stats.launches_gemm_tc_fused++;
   ctx->stats.launches_total++;

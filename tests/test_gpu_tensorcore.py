@@ -176,3 +176,21 @@ def test_pair_kernel_scattered_c_and_repeatability(ctx):
     e2, _ = _run(ctx, t, np.random.default_rng(5))
     assert e1 < TOL_TC and e1 == e2
     assert ctx.stats()["launches_gemm_tc_pair"] == before + 2
+
+
+# ---- split-K in tc_fused.cu: few output tiles, long K (the final merges)
+@pytest.mark.parametrize("m,n,k,scatter", [(10, 8, 12, False), (9, 6, 13, True), (8, 8, 14, False),
+                                           (12, 8, 12, True)])
+def test_fused_split_k(ctx, m, n, k, scatter):
+    rng = np.random.default_rng(7000 + 100 * m + 10 * n + k)
+    t = _natural(m, n, k)
+    if scatter:
+        pc = [int(x) for x in rng.permutation(m + n)]
+        t["c_m"], t["c_n"] = pc[:m], pc[m:]
+    before = ctx.stats()
+    e1, used = _run(ctx, t, np.random.default_rng(11))
+    e2, _ = _run(ctx, t, np.random.default_rng(11))
+    after = ctx.stats()
+    assert e1 < TOL_TC and e1 == e2          # fixed-order slab sum: deterministic
+    assert used["launches_gemm_tc_fused"] == 1, used
+    assert after["launches_reduce"] - before["launches_reduce"] == 2  # one finish per run
