@@ -52,6 +52,11 @@ int qfx_device_count(int* n_out);
  * src/tensor.cpp:83) with an explicit handle. */
 int qfx_create(int device, qfx_ctx** ctx_out);
 int qfx_destroy(qfx_ctx* ctx);
+/* A destroyed context parks its arena and workspace (one of each per device)
+ * for the next context of the process; this frees them.  (The reference
+ * allocates its scratch once per EvaluateCircuit, src/contraction_utils.cpp:
+ * 16-221; parking removes the per-call cudaMalloc/cudaFree of the arena.) */
+int qfx_trim_cache(int device);
 int qfx_sync(qfx_ctx* ctx);
 
 /* Arena of n_elems complex64.  Replaces the scratch arena that

@@ -5,6 +5,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <mutex>
 #include <vector>
 
 #include "qfx_internal.h"
@@ -20,6 +21,76 @@ int qfx_fail_cuda(cudaError_t e, const char* what) {
   return QFX_ERR_CUDA;
 }
 
+// ---- device-buffer cache.  A destroyed context parks its arena and workspace
+// here (one of each per device) and the next context of the process takes them
+// over when they are big enough: repeated EvaluateCircuit calls (one per output
+// bitstring in the reference's Python interface, src/pybind_main.cpp:75-138) then
+// skip a multi-GB cudaMalloc + cudaFree per call.  qfx_trim_cache() frees them.
+namespace {
+struct ParkedBuffers {
+  void* arena = nullptr;
+  size_t arena_bytes = 0;
+  void* ws = nullptr;
+  size_t ws_bytes = 0;
+};
+std::mutex g_park_mu;
+ParkedBuffers g_parked[64];
+
+void* take_parked(int device, bool arena, size_t need, size_t* got) {
+  if (device < 0 || device >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(g_park_mu);
+  ParkedBuffers& p = g_parked[device];
+  void*& ptr = arena ? p.arena : p.ws;
+  size_t& bytes = arena ? p.arena_bytes : p.ws_bytes;
+  if (ptr == nullptr || bytes < need) return nullptr;
+  void* out = ptr;
+  *got = bytes;
+  ptr = nullptr;
+  bytes = 0;
+  return out;
+}
+
+// keeps the larger of (parked, offered); frees the other.  Device must be current.
+void park(int device, bool arena, void* ptr, size_t bytes) {
+  if (ptr == nullptr) return;
+  if (device < 0 || device >= 64) {
+    cudaFree(ptr);
+    return;
+  }
+  void* drop = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_park_mu);
+    ParkedBuffers& p = g_parked[device];
+    void*& slot = arena ? p.arena : p.ws;
+    size_t& slot_bytes = arena ? p.arena_bytes : p.ws_bytes;
+    if (slot == nullptr || slot_bytes < bytes) {
+      drop = slot;
+      slot = ptr;
+      slot_bytes = bytes;
+    } else {
+      drop = ptr;
+    }
+  }
+  if (drop) cudaFree(drop);
+}
+}  // namespace
+
+extern "C" int qfx_trim_cache(int device) {
+  if (device < 0 || device >= 64) return QFX_ERR_ARG;
+  ParkedBuffers p;
+  {
+    std::lock_guard<std::mutex> lock(g_park_mu);
+    p = g_parked[device];
+    g_parked[device] = ParkedBuffers{};
+  }
+  if (p.arena || p.ws) {
+    cudaSetDevice(device);
+    if (p.arena) cudaFree(p.arena);
+    if (p.ws) cudaFree(p.ws);
+  }
+  return QFX_OK;
+}
+
 int qfx_ensure_ws(qfx_ctx* ctx, size_t bytes) {
   if (bytes <= ctx->ws_bytes) return QFX_OK;
   // The workspace may still be in use by earlier launches on the stream.
@@ -28,6 +99,12 @@ int qfx_ensure_ws(qfx_ctx* ctx, size_t bytes) {
   ctx->ws = nullptr;
   ctx->ws_bytes = 0;
   size_t want = bytes < (1u << 20) ? (1u << 20) : bytes;
+  size_t got = 0;
+  if (void* p = take_parked(ctx->device, false, want, &got)) {
+    ctx->ws = p;
+    ctx->ws_bytes = got;
+    return QFX_OK;
+  }
   cudaError_t e = cudaMalloc(&ctx->ws, want);
   if (e != cudaSuccess) {
     cudaGetLastError();
@@ -159,9 +236,9 @@ int qfx_destroy(qfx_ctx* ctx) {
   if (ctx == nullptr) return QFX_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  if (ctx->arena) cudaFree(ctx->arena);
+  park(ctx->device, true, ctx->arena, ctx->arena_elems * sizeof(float2));
   if (ctx->amps) cudaFree(ctx->amps);
-  if (ctx->ws) cudaFree(ctx->ws);
+  park(ctx->device, false, ctx->ws, ctx->ws_bytes);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   for (auto& r : ctx->prof) {
@@ -194,7 +271,19 @@ int qfx_arena_reserve(qfx_ctx* ctx, uint64_t n_elems) {
   if (ctx->arena) QFX_CUDA(cudaFree(ctx->arena));
   ctx->arena = nullptr;
   ctx->arena_elems = 0;
+  size_t got = 0;
+  if (void* p = take_parked(ctx->device, true, n_elems * sizeof(float2), &got)) {
+    ctx->arena = reinterpret_cast<float2*>(p);
+    ctx->arena_elems = got / sizeof(float2);
+    return QFX_OK;
+  }
   cudaError_t e = cudaMalloc(&ctx->arena, n_elems * sizeof(float2));
+  if (e != cudaSuccess) {
+    // a parked buffer that was too small may be what is in the way
+    cudaGetLastError();
+    qfx_trim_cache(ctx->device);
+    e = cudaMalloc(&ctx->arena, n_elems * sizeof(float2));
+  }
   if (e != cudaSuccess) {
     cudaGetLastError();
     char buf[160];
