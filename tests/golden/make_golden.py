@@ -15,9 +15,15 @@ from tests.support import CASES, case_texts, reference_evaluate  # noqa: E402
 
 
 def main():
+    # `make_golden.py name...` regenerates only those cases and keeps the rest
+    only = set(sys.argv[1:])
+    path = os.path.join(ROOT, "tests", "golden", "amplitudes.json")
     out = {}
+    if only and os.path.exists(path):
+        with open(path) as f:
+            out = json.load(f)
     for name, case in CASES.items():
-        if not case.get("golden", True):
+        if not case.get("golden", True) or (only and name not in only):
             continue
         c, o, g = case_texts(case)
         res, secs = reference_evaluate(c, o, g, case.get("initial", ""), case.get("final", ""))
@@ -28,7 +34,7 @@ def main():
             "reference_seconds": secs,
         }
         print(name, len(res), "amplitudes", "%.2fs" % secs, flush=True)
-    with open(os.path.join(ROOT, "tests", "golden", "amplitudes.json"), "w") as f:
+    with open(path, "w") as f:
         json.dump(out, f, indent=1)
 
 

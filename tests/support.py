@@ -87,6 +87,22 @@ CASES = {
                                   ordering="bristlecone_48.txt", grid="bristlecone_48.txt"),
     "bristlecone_48_1-24-1": dict(circuit="bristlecone_48_1-24-1_0.txt",
                                   ordering="bristlecone_48.txt", grid="bristlecone_48.txt"),
+    # BASELINE configs[3]: 7x7 grid with the reference's ExampleOrdering schedule
+    # (config/ordering/rectangular_7x7_v2.txt); 1 of the 256 slices, 4 of the 64
+    # terminal-cut amplitudes (2^12x2^12x2^12 merges, 2^16x256x256 expands)
+    "rect7x7_1-32-1_4amps": dict(
+        circuit="rectangular_7x7_1-32-1_0.txt", ordering="rectangular_7x7_v2.txt",
+        grid="rectangular_7x7.txt",
+        cut_values=[[5], [9], [0, 1], [1], [0], [0, 1], [1], [0]]),
+    # BASELINE configs[2] at the depth the reference's data model can hold (SURVEY
+    # section 0.4: m >= 12 is not representable): Sycamore-53 m=8, the six terminal
+    # cuts opened -> a batch of 64 output bitstrings per call; 1 and 2 of the 4096 slices
+    "sycamore_53_8_64amps": dict(
+        circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+        cut_values=[[3], [7], [11]] + [[0, 1]] * 6),
+    "sycamore_53_8_2slices_64amps": dict(
+        circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+        cut_values=[[3, 12], [7], [11]] + [[0, 1]] * 6),
     # 16 of the 4096 slices of config[1]'s little brother
     "bristlecone_70_1-24-1_16slices": dict(
         circuit="bristlecone_70_1-24-1_0.txt", ordering="bristlecone_70.txt",

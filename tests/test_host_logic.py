@@ -13,7 +13,7 @@ from tests import support
 TOL = 1e-4  # BASELINE.json north_star: normwise relative error of the amplitude vector
 
 CPU_CASES = ["test", "simple_1100x", "rect2x2_0000", "rect2x2_0110", "sycamore_53_4",
-             "bristlecone_70_1-12-1", "bristlecone_48_1-16-1"]
+             "bristlecone_70_1-12-1", "bristlecone_48_1-16-1", "sycamore_53_8_64amps"]
 
 
 def _amps(golden, name):
