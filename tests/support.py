@@ -103,6 +103,11 @@ CASES = {
     "sycamore_53_8_2slices_64amps": dict(
         circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         cut_values=[[3, 12], [7], [11]] + [[0, 1]] * 6),
+    # BASELINE configs[4] stand-in: Sycamore-53 m=10, one of its 16384
+    # slices (2^18 x 2^10 x 2^10 contractions; 199 s and 32.6 GB on the reference)
+    "sycamore_53_10_1slice": dict(
+        circuit="sycamore_53_10_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+        cut_values=[[3], [7], [11]]),
     # 16 of the 4096 slices of config[1]'s little brother
     "bristlecone_70_1-24-1_16slices": dict(
         circuit="bristlecone_70_1-24-1_0.txt", ordering="bristlecone_70.txt",
