@@ -108,6 +108,15 @@ typedef struct qfx_contract_desc {
 
 int qfx_contract(qfx_ctx* ctx, const qfx_contract_desc* desc);
 
+/* n_chains independent chains of small contractions in ONE launch: chain c is the
+ * steps descs[chain_first[c] .. chain_first[c+1]) executed in order (a step may
+ * read what earlier steps of ITS chain wrote; chains must not touch each
+ * other's results).  k_bits <= 6, result <= 2^26 elements per step, fp32.
+ * Replaces the per-site world-line products of flatten_grid_of_tensors
+ * (src/read_circuit.cpp:548-689: one multiply() per gate, ~30 per qubit). */
+int qfx_contract_chains(qfx_ctx* ctx, const qfx_contract_desc* descs,
+                        const int32_t* chain_first, int32_t n_chains);
+
 /* Final scalar contraction (m_bits = n_bits = 0) accumulated in complex128 into
  * amplitude slot `slot`.  Replaces _multiply_vv + `(*amplitudes_)[output_index]
  * += *output->data()` (src/tensor.cpp:1027-1042,

@@ -138,6 +138,14 @@ static int contract_impl(qfx_ctx* c, const qfx_contract_desc* d, bool acc, uint6
 }
 
 int qfx_contract(qfx_ctx* c, const qfx_contract_desc* d) { return contract_impl(c, d, false, 0); }
+int qfx_contract_chains(qfx_ctx* c, const qfx_contract_desc* d, const int32_t* first, int32_t n) {
+  if (c == nullptr || d == nullptr || first == nullptr || n < 0)
+    return fail("qfx_contract_chains: bad argument");
+  for (int32_t ch = 0; ch < n; ++ch)
+    for (int32_t s = first[ch]; s < first[ch + 1]; ++s)
+      if (int rc = contract_impl(c, d + s, false, 0)) return rc;
+  return QFX_OK;
+}
 int qfx_dot_accumulate(qfx_ctx* c, const qfx_contract_desc* d, uint64_t slot) {
   return contract_impl(c, d, true, slot);
 }

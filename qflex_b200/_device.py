@@ -65,6 +65,9 @@ def load(path=DEFAULT_DEVICE_LIB):
     c.qfx_copy.argtypes = [vp, u64, u64, u64]
     c.qfx_contract.argtypes = [vp, ctypes.POINTER(ContractDesc)]
     c.qfx_dot_accumulate.argtypes = [vp, ctypes.POINTER(ContractDesc), u64]
+    c.qfx_contract_chains.argtypes = [vp, ctypes.POINTER(ContractDesc),
+                                      ctypes.POINTER(ctypes.c_int32), i32]
+    c.qfx_trim_cache.argtypes = [ctypes.c_int]
     c.qfx_scalar_accumulate.argtypes = [vp, u64, u64]
     c.qfx_amps_reserve.argtypes = [vp, u64]
     c.qfx_amps_download.argtypes = [vp, vp, u64]
@@ -114,6 +117,16 @@ class Context:
         out = np.empty(n, dtype=np.complex64)
         self._ck(self.c.qfx_download(self.h, off, out.ctypes.data_as(ctypes.c_void_p), n))
         return out
+
+    def contract_chains(self, chains):
+        """chains: list of lists of ContractDesc; one launch (qfx_contract_chains)."""
+        flat = [d for ch in chains for d in ch]
+        arr = (ContractDesc * max(1, len(flat)))(*flat)
+        first = [0]
+        for ch in chains:
+            first.append(first[-1] + len(ch))
+        farr = (ctypes.c_int32 * len(first))(*first)
+        self._ck(self.c.qfx_contract_chains(self.h, arr, farr, len(chains)))
 
     def contract(self, desc):
         self._ck(self.c.qfx_contract(self.h, ctypes.byref(desc)))

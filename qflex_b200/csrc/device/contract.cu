@@ -757,3 +757,116 @@ extern "C" int qfx_scalar_accumulate(qfx_ctx* ctx, uint64_t off, uint64_t slot) 
   ctx->stats.launches_total++;
   return QFX_OK;
 }
+
+// ---------------------------------------------------------------- chains
+// World-line flattening (reference flatten_grid_of_tensors, src/read_circuit.cpp:
+// 548-689): every grid site multiplies its gate tensors one after the other, a
+// chain of ~30 tiny contractions (K = 2 or 4, results of 2 .. 2^20 elements), and
+// the sites are independent.  One thread block runs one whole chain, step after
+// step with a block barrier in between, so ~2000 launch-bound kernels (12 ms for
+// bristlecone_70 1-32-1) become one launch.
+namespace {
+
+__device__ __forceinline__ unsigned long long chain_deposit(unsigned long long v, int bits,
+                                                            const int8_t* pos) {
+  unsigned long long o = 0;
+  for (int q = 0; q < bits; ++q) o |= ((v >> q) & 1ull) << pos[q];
+  return o;
+}
+
+__global__ void __launch_bounds__(1024)
+    contract_chains(float2* arena, const qfx_contract_desc* descs, const int32_t* chain_first) {
+  __shared__ qfx_contract_desc d;
+  const int first = chain_first[blockIdx.x], last = chain_first[blockIdx.x + 1];
+  for (int s = first; s < last; ++s) {
+    __syncthreads();  // previous step's results visible; `d` no longer in use
+    for (int i = threadIdx.x; i < (int)(sizeof(qfx_contract_desc) / 4); i += blockDim.x)
+      reinterpret_cast<uint32_t*>(&d)[i] = reinterpret_cast<const uint32_t*>(descs + s)[i];
+    __syncthreads();
+    const float2* A = arena + d.off_a;
+    const float2* B = arena + d.off_b;
+    float2* C = arena + d.off_c;
+    const unsigned long long total = 1ull << (d.m_bits + d.n_bits);
+    const unsigned K = 1u << d.k_bits;
+    for (unsigned long long idx = threadIdx.x; idx < total; idx += blockDim.x) {
+      const unsigned long long n = idx & ((1ull << d.n_bits) - 1ull), m = idx >> d.n_bits;
+      const unsigned long long ao = chain_deposit(m, d.m_bits, d.a_m);
+      const unsigned long long bo = chain_deposit(n, d.n_bits, d.b_n);
+      const unsigned long long co =
+          chain_deposit(m, d.m_bits, d.c_m) | chain_deposit(n, d.n_bits, d.c_n);
+      float sx = 0.f, sy = 0.f;
+      for (unsigned k = 0; k < K; ++k) {
+        const float2 a = A[ao | chain_deposit(k, d.k_bits, d.a_k)];
+        const float2 b = B[bo | chain_deposit(k, d.k_bits, d.b_k)];
+        sx = fmaf(a.x, b.x, sx);
+        sx = fmaf(-a.y, b.y, sx);
+        sy = fmaf(a.x, b.y, sy);
+        sy = fmaf(a.y, b.x, sy);
+      }
+      C[co] = make_float2(sx, sy);
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int qfx_contract_chains(qfx_ctx* ctx, const qfx_contract_desc* descs,
+                                   const int32_t* chain_first, int32_t n_chains) {
+  if (ctx == nullptr || descs == nullptr || chain_first == nullptr || n_chains < 0) {
+    qfx_set_error("qfx_contract_chains: bad argument");
+    return QFX_ERR_ARG;
+  }
+  if (n_chains == 0) return QFX_OK;
+  const int n_steps = chain_first[n_chains];
+  double flops = 0, bytes = 0;
+  for (int c = 0; c < n_chains; ++c)
+    if (chain_first[c] > chain_first[c + 1] || chain_first[c] < 0) {
+      qfx_set_error("qfx_contract_chains: chain_first must be non-decreasing");
+      return QFX_ERR_ARG;
+    }
+  for (int s = 0; s < n_steps; ++s) {
+    const qfx_contract_desc& d = descs[s];
+    if (d.m_bits < 0 || d.n_bits < 0 || d.k_bits < 0 || d.k_bits > 6 ||
+        d.m_bits + d.n_bits > 26) {
+      qfx_set_error("qfx_contract_chains: a step is not a small contraction (k <= 6 bits, "
+                    "result <= 2^26 elements)");
+      return QFX_ERR_ARG;
+    }
+    const uint64_t mask_a = operand_mask(d.a_m, d.m_bits, d.a_k, d.k_bits);
+    const uint64_t mask_b = operand_mask(d.b_k, d.k_bits, d.b_n, d.n_bits);
+    const uint64_t mask_c = operand_mask(d.c_m, d.m_bits, d.c_n, d.n_bits);
+    if (mask_a == ~0ull || mask_b == ~0ull || mask_c == ~0ull) {
+      qfx_set_error("qfx_contract_chains: bit positions of an operand must be distinct and < 32");
+      return QFX_ERR_ARG;
+    }
+    if (d.off_a + mask_a + 1 > ctx->arena_elems || d.off_b + mask_b + 1 > ctx->arena_elems ||
+        d.off_c + mask_c + 1 > ctx->arena_elems) {
+      qfx_set_error("qfx_contract_chains: operand outside the arena");
+      return QFX_ERR_ARG;
+    }
+    const double M = (double)(1ull << d.m_bits), N = (double)(1ull << d.n_bits),
+                 K = (double)(1ull << d.k_bits);
+    flops += 8.0 * M * N * K;
+    bytes += 8.0 * (M * K + K * N + M * N);
+  }
+  // descriptors + chain table travel through the workspace
+  const size_t desc_bytes = (size_t)n_steps * sizeof(qfx_contract_desc);
+  const size_t first_bytes = (size_t)(n_chains + 1) * sizeof(int32_t);
+  const size_t desc_pad = (desc_bytes + 255) & ~(size_t)255;
+  int rc = qfx_ensure_ws(ctx, desc_pad + first_bytes);
+  if (rc) return rc;
+  uint8_t* ws = reinterpret_cast<uint8_t*>(ctx->ws);
+  QFX_CUDA(cudaMemcpyAsync(ws, descs, desc_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  QFX_CUDA(cudaMemcpyAsync(ws + desc_pad, chain_first, first_bytes, cudaMemcpyHostToDevice,
+                           ctx->stream));
+  QFX_CUDA(cudaStreamSynchronize(ctx->stream));  // pageable host buffers may be reused
+  contract_chains<<<n_chains, 1024, 0, ctx->stream>>>(
+      ctx->arena, reinterpret_cast<const qfx_contract_desc*>(ws),
+      reinterpret_cast<const int32_t*>(ws + desc_pad));
+  QFX_CUDA(cudaGetLastError());
+  ctx->stats.launches_gemm_ffma++;
+  ctx->stats.launches_total++;
+  ctx->stats.flops += flops;
+  ctx->stats.bytes += bytes;
+  return QFX_OK;
+}

@@ -161,7 +161,28 @@ void Session::Flatten() {
   // replicated on every rank: site tensors are MB-scale
   Plan no_cuts;
   Runner r(no_cuts, ctx_, 0, 1);
-  r.run(plan_.flatten_steps);
+  if (!plan_.flatten_parallel) {
+    r.run(plan_.flatten_steps);
+    check(qfx_sync(ctx_), "qfx_sync");
+    return;
+  }
+  // every world-line product of every site in one launch, then the layout permutes
+  std::vector<qfx_contract_desc> descs;
+  std::vector<int32_t> first(plan_.n_chains + 1, 0);
+  std::vector<PlanStep> permutes;
+  descs.reserve(plan_.flatten_steps.size());
+  for (const auto& st : plan_.flatten_steps) {  // steps are ordered by chain
+    if (st.kind == PlanStep::CONTRACT) {
+      descs.push_back(st.desc);
+      first[st.chain + 1] = (int32_t)descs.size();
+    } else {
+      permutes.push_back(st);
+    }
+  }
+  for (int c = 0; c < plan_.n_chains; ++c) first[c + 1] = std::max(first[c + 1], first[c]);
+  check(qfx_contract_chains(ctx_, descs.data(), first.data(), plan_.n_chains),
+        "qfx_contract_chains");
+  r.run(permutes);
   check(qfx_sync(ctx_), "qfx_sync");
 }
 

@@ -343,6 +343,8 @@ Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits) {
   Plan plan;
+  plan.flatten_steps.reserve(4096);  // PlanStep is ~300 bytes: avoid regrowth copies
+  plan.steps.reserve(512);
   const std::size_t I = input.grid.I, J = input.grid.J;
   const auto& off = input.grid.qubits_off;
   auto is_off = [&](std::size_t i, std::size_t j) {
@@ -412,19 +414,33 @@ Plan BuildPlan(const QflexInput& input,
       cursor = align_up(cursor + site.size());
     }
   const uint64_t work_base = cursor;
-  const uint64_t ping = work_base, pong = align_up(work_base + max_chain);
-  uint64_t work_flatten = align_up(pong + max_chain) - work_base;
+  // Ping-pong buffers of the world-line products.  One pair PER SITE when that is
+  // affordable (<= 2^26 elements = 512 MB in all): the chains are then independent
+  // and run concurrently (qfx_contract_chains); otherwise one shared pair and the
+  // sites are flattened one after the other.
+  uint64_t n_sites = 0;
+  for (std::size_t i = 0; i < I; ++i)
+    for (std::size_t j = 0; j < J; ++j)
+      if (!is_off(i, j)) ++n_sites;
+  const uint64_t pair_elems = 2 * align_up(max_chain);
+  plan.flatten_parallel = n_sites * pair_elems <= (uint64_t(1) << 26);
+  uint64_t work_flatten = plan.flatten_parallel ? n_sites * pair_elems : pair_elems;
 
   // ------------------------------------------------- flatten: real steps
   for (std::size_t i = 0; i < I; ++i)
     for (std::size_t j = 0; j < J; ++j) {
       if (is_off(i, j)) continue;
       const auto& chain = net[i][j].chain;
+      const int chain_id = plan.n_chains++;
+      const uint64_t ping =
+          work_base + (plan.flatten_parallel ? (uint64_t)chain_id * pair_elems : 0);
+      const uint64_t pong = ping + align_up(max_chain);
       SymTensor a = chain[0].sym;
       bool in_ping = false;
       for (std::size_t k = 1; k < chain.size(); ++k) {
         PlanStep st;
         st.level = 0;
+        st.chain = chain_id;
         st.label = utils::concat("flatten (", i, ",", j, ") gate ", k);
         const uint64_t dst = in_ping ? pong : ping;
         a = make_contract(a, chain[k].sym, dst, &st);
@@ -437,6 +453,7 @@ Plan BuildPlan(const QflexInput& input,
       PlanStep pm;
       pm.kind = PlanStep::PERMUTE;
       pm.level = 0;
+      pm.chain = chain_id;
       pm.label = utils::concat("flatten (", i, ",", j, ") layout");
       pm.src = a.off;
       pm.dst = site.off;

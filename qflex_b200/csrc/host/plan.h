@@ -82,6 +82,7 @@ struct PlanStep {
   enum Kind { CONTRACT, DOT_ACCUMULATE, SCALAR_ACCUMULATE, PERMUTE };
   Kind kind = CONTRACT;
   int level = 0;  // number of cuts that precede this step in the ordering
+  int chain = -1; // flatten: world-line (grid site) this step belongs to
   qfx_contract_desc desc{};
   std::vector<VarTerm> var_a, var_b;
   // PERMUTE
@@ -119,6 +120,10 @@ struct Plan {
   std::vector<std::vector<SymTensor>> site;
   double flops_per_pass = 0, bytes_per_pass = 0;  // one execution of every step
   int precision = QFX_PREC_AUTO;
+  // flatten: every site has its own ping-pong buffers, so the world-line chains are
+  // independent and run as one qfx_contract_chains launch
+  bool flatten_parallel = false;
+  int n_chains = 0;
 };
 
 // Builds the full plan.  `final_qubits` = qubits with a terminal cut

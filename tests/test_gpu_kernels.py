@@ -186,3 +186,56 @@ def test_permute_involution_full_size(ctx):
     ctx.permute(0, n, p)
     ctx.permute(n, 2 * n, inv)
     assert np.array_equal(ctx.download(2 * n, n), src)
+
+
+def test_contract_chains_runs_independent_world_lines_in_one_launch():
+    """qfx_contract_chains: every chain multiplies small gate tensors one after the
+    other (ping-pong buffers), like one grid site of flatten_grid_of_tensors
+    (reference src/read_circuit.cpp:548-689); checked step by step against the oracle."""
+    from qflex_b200 import _device
+    from oracle import kernel_oracle as ko
+    rng = np.random.default_rng(2024)
+    ctx = _device.Context(0)
+    n_chains, steps, max_bits = 5, 9, 12
+    buf = 1 << max_bits
+    gates_off = 0
+    gate_elems = 16
+    work = n_chains * steps * gate_elems + 64
+    ctx.reserve(work + n_chains * 2 * buf + 64)
+    chains, expected = [], []
+    for c in range(n_chains):
+        ping, pong = work + c * 2 * buf, work + c * 2 * buf + buf
+        cur = (rng.uniform(-1, 1, 4) + 1j * rng.uniform(-1, 1, 4)).astype(np.complex64)
+        cur_bits = 2
+        ctx.upload(ping, cur)
+        src, dst = ping, pong
+        chain = []
+        for s in range(steps):
+            # gate [k | n]: contract the running tensor's bit `kp` (and sometimes 2 bits)
+            k = 1 if (s % 3) else min(2, cur_bits)
+            n = 1 + (s % 2)
+            if cur_bits - k + n > max_bits:
+                n = 1
+            g = (rng.uniform(-1, 1, 1 << (k + n)) + 1j * rng.uniform(-1, 1, 1 << (k + n))).astype(np.complex64)
+            goff = gates_off + (c * steps + s) * gate_elems
+            ctx.upload(goff, g)
+            pos = [int(x) for x in rng.permutation(cur_bits)]
+            a_k, a_m = pos[:k], pos[k:]
+            m = cur_bits - k
+            pc = [int(x) for x in rng.permutation(m + n)]
+            t = dict(a_m=a_m, a_k=a_k, b_n=list(range(n)), b_k=list(range(n, n + k)),
+                     c_m=pc[:m], c_n=pc[m:])
+            chain.append(_device.make_desc(src, goff, dst, t["a_m"], t["c_m"], t["b_n"], t["c_n"],
+                                           t["a_k"], t["b_k"]))
+            cur = ko.contract(cur, g, **t)
+            cur_bits = m + n
+            src, dst = dst, src
+        chains.append(chain)
+        expected.append((src, cur))
+    before = ctx.stats()["launches_total"]
+    ctx.contract_chains(chains)
+    assert ctx.stats()["launches_total"] == before + 1
+    for off, want in expected:
+        got = ctx.download(off, want.size)
+        assert support.rel_err(got, want) < 1e-5
+    ctx.close()
