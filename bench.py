@@ -42,7 +42,31 @@ WORKLOADS = {
               4: [[0, 1], [0, 1], [0, 1], [0, 1, 2, 3]],
               8: [[0, 1], [0, 1], [0, 1, 2, 3], [0, 1, 2, 3]]},
         reference_sample=[[0, 1], [0, 1], [0, 1], [0]], memory=8 << 30),
+    # BASELINE configs[4] stand-in (m=20 is not representable): Sycamore-53
+    # m=10, a low-fidelity batch of 64 of its 16384 slices, STRONG scaling (the same
+    # 64 slices whatever the GPU count)
+    "sycamore_53_10": dict(
+        circuit="sycamore_53_10_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+        scaling="strong", cuts={"all": [[0, 1, 2, 3], [0, 1, 2, 3], [0, 1, 2, 3]]},
+        reference_sample=[[0], [0], [0]], memory=100 << 30),
+    # BASELINE configs[2] at m=8: 64 slices x a batch of 64 output bitstrings, strong scaling
+    "sycamore_53_8_batch64": dict(
+        circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+        scaling="strong",
+        cuts={"all": [list(range(16)), [0, 1, 2, 3], [0]] + [[0, 1]] * 6},
+        reference_sample=[[0], [0], [0]] + [[0, 1]] * 6, memory=8 << 30),
+    # BASELINE configs[3]: 7x7 1-32-1 with the reference's ExampleOrdering schedule,
+    # 64 of its 256 slices x 64 output bitstrings, strong scaling
+    "rectangular_7x7_1-32-1": dict(
+        circuit="rectangular_7x7_1-32-1_0.txt", ordering="rectangular_7x7_v2.txt",
+        grid="rectangular_7x7.txt", scaling="strong",
+        cuts={"all": [list(range(16)), [0, 1, 2, 3]] + [[0, 1]] * 6},
+        reference_sample=[[0], [0]] + [[0, 1]] * 6, memory=16 << 30),
 }
+
+
+def workload_cuts(w, world):
+    return w["cuts"].get("all") or w["cuts"][world]
 
 
 def load_texts(w, cut_values):
@@ -155,13 +179,13 @@ def run_reference_arm(args, w, wname):
         secs, n_slices, _ = cpu_reference_run(w, sample, threads)
         if i >= args.warmup:
             times.append(secs)
-    flops_slice = plan_flops_per_slice(w)
     ms = 1e3 * sum(times) / len(times)
-    val = flops_slice * n_slices / (ms * 1e-3) / 1e12
+    val = plan_flops(w, sample) / (ms * 1e-3) / 1e12
     line = {
         "impl": "reference", "metric": "contraction_tflops", "value": val, "unit": "TFLOP/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "complex64",
+        "higher_is_better": True, "scaling": w.get("scaling", "weak"), "vs_baseline": None,
+        "dtype": "complex64",
         "data": "shipped circuit (config/circuits/%s), deterministic" % w["circuit"],
         "config": {"workload": wname, "slices_per_step": n_slices,
                    "note": "reference qflex EvaluateCircuit on host cores, OpenBLAS + OpenMP"},
@@ -179,23 +203,38 @@ def run_reference_arm(args, w, wname):
 _FLOPS_CACHE = {}
 
 
-def plan_flops_per_slice(w):
-    """Algorithmic flops of ONE slice = sum of 8*M*N*K over the schedule of a
-    plan whose cuts all carry a single value (planner's symbolic replay; the
-    plan is only described, not contracted)."""
-    key = w["circuit"]
+def plan_flops(w, cut_values):
+    """Algorithmic flops of one pass over the slices `cut_values` selects = sum over
+    the schedule of 8*M*N*K x (how often the step runs: the product of the value
+    counts of the cuts that precede it).  Planner's symbolic replay; the plan is only
+    described, not contracted."""
+    import re
+    key = (w["circuit"], json.dumps(cut_values))
     if key not in _FLOPS_CACHE:
         import qflex_b200
-        c, o, g = load_texts(w, [[v[0]] for v in w["reference_sample"]])
+        c, o, g = load_texts(w, cut_values)
+        fan = []
+        for line in o.splitlines():
+            m = re.match(r"\s*cut\s*\(([0-9,\s]*)\)", line)
+            if m:
+                vals = [v for v in m.group(1).split(",") if v.strip()]
+                if not vals:
+                    raise ValueError("bench workloads must give every cut an explicit value list")
+                fan.append(len(vals))
         try:
             p = qflex_b200.default_library().prepare(c, o, g, memory_limit=w["memory"])
         except qflex_b200.QflexError:
             from tests import support
             p = support.emulated_host_library().prepare(c, o, g, memory_limit=w["memory"])
-        _FLOPS_CACHE[key] = sum(
-            8.0 * 2.0 ** (r["m_bits"] + r["n_bits"] + r["k_bits"]) for r in p.describe()
-            if r["phase"] == "grid" and r["kind"] in ("contract", "dot"))
+        total = 0.0
+        for r in p.describe():
+            if r["phase"] == "grid" and r["kind"] in ("contract", "dot"):
+                times = 1
+                for f in fan[: r["level"]]:
+                    times *= f
+                total += times * 8.0 * 2.0 ** (r["m_bits"] + r["n_bits"] + r["k_bits"])
         p.close()
+        _FLOPS_CACHE[key] = total
     return _FLOPS_CACHE[key]
 
 
@@ -253,7 +292,7 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    cuts = w["cuts"][world]
+    cuts = workload_cuts(w, world)
     c, o, g = load_texts(w, cuts)
     lib = qflex_b200.default_library()
     prep = lib.prepare(c, o, g, memory_limit=w["memory"], device=local_rank,
@@ -370,9 +409,11 @@ def main():
     line = {
         "metric": "contraction_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "complex64",
+        "higher_is_better": True, "scaling": w.get("scaling", "weak"), "vs_baseline": None,
+        "dtype": "complex64",
         "data": "shipped circuit (config/circuits/%s), deterministic; synthetic = none needed" % w["circuit"],
-        "config": {"workload": args.workload, "slices_per_gpu": SLICES_PER_GPU,
+        "config": {"workload": args.workload,
+                   "slices_per_gpu": total_leaves / args.steps / world / max(1, n_amps),
                    "slices_per_step": int(total_leaves / args.steps), "cut_values": cuts,
                    "arena_gb": arena_bytes / 2 ** 30, "precision": args.precision,
                    "l2": "working set per contraction (>= 2 GB patches) exceeds the 126 MB L2",
@@ -396,7 +437,7 @@ def main():
         try:
             cores, threads = host_threads()
             secs, n_slices, ref_amps = cpu_reference_run(w, w["reference_sample"], threads)
-            fl = plan_flops_per_slice(w) * n_slices
+            fl = plan_flops(w, w["reference_sample"])
             line["cpu_baseline"] = {
                 "value": fl / secs / 1e12, "unit": "TFLOP/s", "cores": max(threads),
                 "kind": "reference", "seconds": secs,

@@ -345,6 +345,7 @@ struct DotArgs {
   double2* amp;   // amplitude slot (accumulated) or nullptr
   double2* ws;    // [outputs][splits] partials (splits > 1)
   int m_bits, n_bits, k_bits, ks_bits;
+  int vec;  // k bit 0 is address bit 0 of both operands and both bases are even
   int8_t a_m[QFX_MAX_BITS], c_m[QFX_MAX_BITS];
   int8_t b_n[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
   int8_t a_k[QFX_MAX_BITS], b_k[QFX_MAX_BITS];
@@ -364,39 +365,100 @@ __device__ __forceinline__ unsigned long long dot_out_offset(const DotArgs& g,
 
 __global__ void __launch_bounds__(kDotThreads)
     dotk(const __grid_constant__ DotArgs g) {
+  // K is enumerated lowest-A-address-bit first (host sorts the k tables): the
+  // optional vector bit (k bit 0 = address bit 0 of both operands: 16-byte loads),
+  // then up to 8 bits across the threads, then the remaining bits walked by every
+  // thread in Gray-code order, so that one step flips ONE address bit per operand
+  // (the summation order is free; accumulation is fp64).
   const unsigned out = blockIdx.x, split = blockIdx.y;
   const unsigned n = out & ((1u << g.n_bits) - 1u), m = out >> g.n_bits;
   unsigned long long baseA = 0, baseB = 0;
   for (int q = 0; q < g.m_bits; ++q) baseA |= (unsigned long long)((m >> q) & 1u) << g.a_m[q];
   for (int q = 0; q < g.n_bits; ++q) baseB |= (unsigned long long)((n >> q) & 1u) << g.b_n[q];
 
-  const int lo_bits = g.k_bits < kDotLoBits ? g.k_bits : kDotLoBits;
+  const int v = g.vec;
+  const int lo_bits = (g.k_bits - v) < kDotLoBits ? (g.k_bits - v) : kDotLoBits;
   const unsigned tid = threadIdx.x;
-  unsigned long long loA = 0, loB = 0;
+  unsigned long long offA = baseA, offB = baseB;
   for (int q = 0; q < lo_bits; ++q) {
     unsigned long long b = (tid >> q) & 1u;
-    loA |= b << g.a_k[q];
-    loB |= b << g.b_k[q];
+    offA |= b << g.a_k[v + q];
+    offB |= b << g.b_k[v + q];
   }
   const bool active = tid < (1u << lo_bits);
-  const int hi_bits = g.k_bits - lo_bits;
-  const unsigned nch = 1u << (hi_bits - g.ks_bits);
-  const unsigned c0 = split * nch;
-  const float2* __restrict__ A = g.A + baseA + loA;
-  const float2* __restrict__ B = g.B + baseB + loB;
+  const int h0 = v + lo_bits;                 // first walked k bit
+  const int hi_bits = g.k_bits - h0;
+  const int walk_bits = hi_bits - g.ks_bits;  // per block; the top ks bits select the split
+  for (int q = 0; q < g.ks_bits; ++q) {
+    unsigned long long b = (split >> q) & 1u;
+    offA |= b << g.a_k[h0 + walk_bits + q];
+    offB |= b << g.b_k[h0 + walk_bits + q];
+  }
+  const unsigned nch = 1u << walk_bits;
+  const float2* __restrict__ A = g.A;
+  const float2* __restrict__ B = g.B;
 
   double sx = 0.0, sy = 0.0;
   if (active) {
-    for (unsigned c = c0; c < c0 + nch; ++c) {
-      unsigned long long hA = 0, hB = 0;
-      for (int q = 0; q < hi_bits; ++q) {
-        unsigned long long b = (c >> q) & 1u;
-        hA |= b << g.a_k[lo_bits + q];
-        hB |= b << g.b_k[lo_bits + q];
+    for (unsigned c = 0; c < nch; c += 4) {
+      unsigned long long oa[4], ob[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        oa[u] = offA;
+        ob[u] = offB;
+        const unsigned nxt = c + u + 1;
+        if (nxt < nch) {
+          const int bit = __ffs(nxt) - 1;  // Gray code: step i flips bit ctz(i)
+          offA ^= 1ull << g.a_k[h0 + bit];
+          offB ^= 1ull << g.b_k[h0 + bit];
+        }
       }
-      const float2 a = __ldg(A + hA), b = __ldg(B + hB);
-      sx += (double)a.x * b.x - (double)a.y * b.y;
-      sy += (double)a.x * b.y + (double)a.y * b.x;
+      if (v) {
+        float4 a[4], b[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (c + u < nch) {
+            a[u] = __ldg(reinterpret_cast<const float4*>(A + oa[u]));
+            b[u] = __ldg(reinterpret_cast<const float4*>(B + ob[u]));
+          }
+        // fp32 products and a short fp32 sum (<= 8 terms, what cblas_cdotu does for
+        // the whole K), then fp64: fp32->fp64 conversions run at a few per clock per
+        // SM and bounded this kernel at 0.8 TB/s when every product was converted
+        float px = 0.f, py = 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (c + u < nch) {
+            px = fmaf(a[u].x, b[u].x, px);
+            px = fmaf(-a[u].y, b[u].y, px);
+            py = fmaf(a[u].x, b[u].y, py);
+            py = fmaf(a[u].y, b[u].x, py);
+            px = fmaf(a[u].z, b[u].z, px);
+            px = fmaf(-a[u].w, b[u].w, px);
+            py = fmaf(a[u].z, b[u].w, py);
+            py = fmaf(a[u].w, b[u].z, py);
+          }
+        sx += (double)px;
+        sy += (double)py;
+      } else {
+        float2 a[4], b[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (c + u < nch) {
+            a[u] = __ldg(A + oa[u]);
+            b[u] = __ldg(B + ob[u]);
+          }
+        float px = 0.f, py = 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (c + u < nch) {
+            px = fmaf(a[u].x, b[u].x, px);
+            px = fmaf(-a[u].y, b[u].y, px);
+            py = fmaf(a[u].x, b[u].y, py);
+            py = fmaf(a[u].y, b[u].x, py);
+          }
+        sx += (double)px;
+        sy += (double)py;
+      }
     }
   }
 #pragma unroll
@@ -427,17 +489,26 @@ __global__ void __launch_bounds__(kDotThreads)
   }
 }
 
+// One warp per output: lanes stride over the split partials, then a shuffle tree
+// (fixed order: deterministic).  A single thread walking 1024 partials took 140 us,
+// three times the dot product itself.
 __global__ void dotk_finish(const __grid_constant__ DotArgs g) {
   const unsigned outs = 1u << (g.m_bits + g.n_bits);
-  const unsigned out = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned out = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (out >= outs) return;
   double sx = 0.0, sy = 0.0;
   const unsigned splits = 1u << g.ks_bits;
-  for (unsigned s = 0; s < splits; ++s) {
+  for (unsigned s = lane; s < splits; s += 32) {
     const double2 v = g.ws[((unsigned long long)out << g.ks_bits) + s];
     sx += v.x;
     sy += v.y;
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sx += __shfl_xor_sync(0xffffffffu, sx, o);
+    sy += __shfl_xor_sync(0xffffffffu, sy, o);
+  }
+  if (lane != 0) return;
   if (g.amp != nullptr) {
     g.amp->x += sx;
     g.amp->y += sy;
@@ -629,11 +700,20 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
     memcpy(g.b_n, d.b_n, QFX_MAX_BITS);
     memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
-    memcpy(g.a_k, d.a_k, QFX_MAX_BITS);
-    memcpy(g.b_k, d.b_k, QFX_MAX_BITS);
+    {  // K enumeration is free: lowest A address bit first (contiguous runs per warp)
+      std::vector<int> idx(d.k_bits);
+      for (int i = 0; i < d.k_bits; ++i) idx[i] = i;
+      std::sort(idx.begin(), idx.end(), [&](int x, int y) { return d.a_k[x] < d.a_k[y]; });
+      for (int i = 0; i < d.k_bits; ++i) {
+        g.a_k[i] = d.a_k[idx[i]];
+        g.b_k[i] = d.b_k[idx[i]];
+      }
+    }
+    g.vec = (d.k_bits >= 1 && g.a_k[0] == 0 && g.b_k[0] == 0 && !(d.off_a & 1) && !(d.off_b & 1))
+                ? 1 : 0;
     const int outs_bits = d.m_bits + d.n_bits;
-    const int lo_bits = std::min(d.k_bits, kDotLoBits);
-    const int hi_bits = d.k_bits - lo_bits;
+    const int lo_bits = std::min(d.k_bits - g.vec, kDotLoBits);
+    const int hi_bits = d.k_bits - g.vec - lo_bits;
     // each block should stream at least 16 chunks of 256 elements
     int ks = 0;
     while (ks < hi_bits - 4 && ((1 << (outs_bits + ks)) < 4 * ctx->sm_count)) ++ks;
@@ -651,7 +731,7 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     ctx->stats.launches_total++;
     if (ks > 0) {
       const unsigned outs = 1u << outs_bits;
-      dotk_finish<<<(outs + 63) / 64, 64, 0, ctx->stream>>>(g);
+      dotk_finish<<<(outs * 32 + 127) / 128, 128, 0, ctx->stream>>>(g);
       QFX_CUDA(cudaGetLastError());
       ctx->stats.launches_reduce++;
       ctx->stats.launches_total++;

@@ -47,11 +47,12 @@ def main():
                     ctx.upload(off + o, blk[: min(1 << 16, size - o)])
                 if size > (1 << 22):
                     break  # big A: first 2^16 random, rest whatever the arena holds (finite)
-            d = _device.make_desc(0, sa + 32, sa + sb + 64, a_m, c_m, b_n, c_n, a_k, b_k)
+            d = _device.make_desc(0, sa + 32, sa + sb + 64, a_m, c_m, b_n, c_n, a_k, b_k,
+                                  precision=int(os.environ.get("QFLEX_KB_PREC", "0")))
             for _ in range(2):
                 ctx.contract(d)
             ctx.sync()
-            reps = 5
+            reps = 20 if m + n + k < 26 else 5
             ctx.timer_start()
             for _ in range(reps):
                 ctx.contract(d)
