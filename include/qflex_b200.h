@@ -57,6 +57,10 @@ int qfx_destroy(qfx_ctx* ctx);
  * allocates its scratch once per EvaluateCircuit, src/contraction_utils.cpp:
  * 16-221; parking removes the per-call cudaMalloc/cudaFree of the arena.) */
 int qfx_trim_cache(int device);
+/* Makes the context's device current for the calling host thread.  A context may
+ * be driven from any ONE thread at a time; a thread other than its creator calls
+ * this first (the host layer runs one thread per lane, see Session in plan.h). */
+int qfx_bind_thread(qfx_ctx* ctx);
 int qfx_sync(qfx_ctx* ctx);
 
 /* Arena of n_elems complex64.  Replaces the scratch arena that

@@ -53,6 +53,7 @@ int qfx_destroy(qfx_ctx* c) {
   return QFX_OK;
 }
 int qfx_trim_cache(int) { return QFX_OK; }
+int qfx_bind_thread(qfx_ctx*) { return QFX_OK; }
 int qfx_sync(qfx_ctx*) { return QFX_OK; }
 int qfx_arena_reserve(qfx_ctx* c, uint64_t n) {
   if (n > c->arena.size()) c->arena.assign(n, {0.f, 0.f});

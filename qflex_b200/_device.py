@@ -68,6 +68,7 @@ def load(path=DEFAULT_DEVICE_LIB):
     c.qfx_contract_chains.argtypes = [vp, ctypes.POINTER(ContractDesc),
                                       ctypes.POINTER(ctypes.c_int32), i32]
     c.qfx_trim_cache.argtypes = [ctypes.c_int]
+    c.qfx_bind_thread.argtypes = [vp]
     c.qfx_scalar_accumulate.argtypes = [vp, u64, u64]
     c.qfx_amps_reserve.argtypes = [vp, u64]
     c.qfx_amps_download.argtypes = [vp, vp, u64]

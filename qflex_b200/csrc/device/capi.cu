@@ -251,6 +251,15 @@ int qfx_destroy(qfx_ctx* ctx) {
   return QFX_OK;
 }
 
+int qfx_bind_thread(qfx_ctx* ctx) {
+  if (ctx == nullptr) {
+    qfx_set_error("qfx_bind_thread: null context");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaSetDevice(ctx->device));
+  return QFX_OK;
+}
+
 int qfx_sync(qfx_ctx* ctx) {
   if (ctx == nullptr) {
     qfx_set_error("qfx_sync: null context");

@@ -5,7 +5,10 @@
 // amplitude, a terminal cut selects amplitude output_index*|values|+i.
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
+#include <map>
+#include <thread>
 
 #include "errors.h"
 #include "plan.h"
@@ -111,26 +114,50 @@ class Runner {
 
 }  // namespace
 
-Session::Session(Plan plan, int device) : plan_(std::move(plan)) {
+namespace {
+int choose_lanes(const Plan& plan) {
+  if (const char* e = getenv("QFLEX_LANES")) return std::max(1, std::min(16, atoi(e)));
+  uint64_t slices = 1;
+  for (const auto& c : plan.cuts) slices *= std::max<uint64_t>(1, c.values.size());
+  const double arena_bytes = (double)plan.arena_elems * 8.0;
+  // lanes only for networks whose arena is small next to the GPU (<= 256 MB each)
+  int lanes = (int)std::min<double>(8.0, (2048.0 * 1048576.0) / std::max(arena_bytes, 1.0));
+  if (arena_bytes > 256.0 * 1048576.0) lanes = 1;
+  lanes = (int)std::min<uint64_t>((uint64_t)std::max(lanes, 1), std::max<uint64_t>(1, slices / 2));
+  return std::max(lanes, 1);
+}
+}  // namespace
+
+Session::Session(Plan plan, int device) : plan_(std::move(plan)), device_(device) {
   check(qfx_create(device, &ctx_), "qfx_create");
+  lanes_.push_back(ctx_);
   try {
     const double t0 = now_s();
-    check(qfx_arena_reserve(ctx_, plan_.arena_elems), "qfx_arena_reserve");
-    check(qfx_amps_reserve(ctx_, plan_.n_amplitudes), "qfx_amps_reserve");
+    const int n_lanes = choose_lanes(plan_);
+    for (int l = 1; l < n_lanes; ++l) {
+      qfx_ctx* c = nullptr;
+      check(qfx_create(device, &c), "qfx_create");
+      lanes_.push_back(c);
+    }
+    for (qfx_ctx* c : lanes_) {
+      check(qfx_arena_reserve(c, plan_.arena_elems), "qfx_arena_reserve");
+      check(qfx_amps_reserve(c, plan_.n_amplitudes), "qfx_amps_reserve");
+    }
     Upload();
     const double t1 = now_s();
     stats_.seconds_upload = t1 - t0;
     Flatten();
     stats_.seconds_flatten = now_s() - t1;
   } catch (...) {
-    qfx_destroy(ctx_);
+    for (qfx_ctx* c : lanes_) qfx_destroy(c);
+    lanes_.clear();
     ctx_ = nullptr;
     throw;
   }
 }
 
 Session::~Session() {
-  if (ctx_) qfx_destroy(ctx_);
+  for (qfx_ctx* c : lanes_) qfx_destroy(c);
 }
 
 void Session::Upload() {
@@ -144,26 +171,33 @@ void Session::Upload() {
     hi = std::max<uint64_t>(hi, up.off + up.data.size());
   }
   if (hi - lo > (uint64_t(1) << 24)) {  // scattered uploads: keep them separate
-    for (const auto& up : plan_.uploads)
-      check(qfx_upload(ctx_, up.off, reinterpret_cast<const float*>(up.data.data()),
-                       up.data.size()),
-            "qfx_upload");
+    for (qfx_ctx* c : lanes_)
+      for (const auto& up : plan_.uploads)
+        check(qfx_upload(c, up.off, reinterpret_cast<const float*>(up.data.data()),
+                         up.data.size()),
+              "qfx_upload");
     return;
   }
   std::vector<s_type> staged(hi - lo, s_type(0.f, 0.f));
   for (const auto& up : plan_.uploads)
     std::copy(up.data.begin(), up.data.end(), staged.begin() + (up.off - lo));
-  check(qfx_upload(ctx_, lo, reinterpret_cast<const float*>(staged.data()), staged.size()),
-        "qfx_upload");
+  for (qfx_ctx* c : lanes_)
+    check(qfx_upload(c, lo, reinterpret_cast<const float*>(staged.data()), staged.size()),
+          "qfx_upload");
 }
 
 void Session::Flatten() {
-  // replicated on every rank: site tensors are MB-scale
+  // replicated on every rank and lane: site tensors are MB-scale.  Launches are
+  // asynchronous, so the lanes' flattens overlap on the device.
+  for (qfx_ctx* c : lanes_) PrepareLane(c);
+  for (qfx_ctx* c : lanes_) check(qfx_sync(c), "qfx_sync");
+}
+
+void Session::PrepareLane(qfx_ctx* ctx) {
   Plan no_cuts;
-  Runner r(no_cuts, ctx_, 0, 1);
+  Runner r(no_cuts, ctx, 0, 1);
   if (!plan_.flatten_parallel) {
     r.run(plan_.flatten_steps);
-    check(qfx_sync(ctx_), "qfx_sync");
     return;
   }
   // every world-line product of every site in one launch, then the layout permutes
@@ -180,10 +214,34 @@ void Session::Flatten() {
     }
   }
   for (int c = 0; c < plan_.n_chains; ++c) first[c + 1] = std::max(first[c + 1], first[c]);
-  check(qfx_contract_chains(ctx_, descs.data(), first.data(), plan_.n_chains),
+  check(qfx_contract_chains(ctx, descs.data(), first.data(), plan_.n_chains),
         "qfx_contract_chains");
   r.run(permutes);
-  check(qfx_sync(ctx_), "qfx_sync");
+}
+
+void Session::ContractLane(int lane, int rank, int world, std::vector<double>* amps,
+                           ExecStats* stats, std::vector<qfx_profile_row>* rows) {
+  qfx_ctx* ctx = lanes_[lane];
+  check(qfx_bind_thread(ctx), "qfx_bind_thread");
+  check(qfx_amps_reserve(ctx, plan_.n_amplitudes), "qfx_amps_reserve");
+  check(qfx_stats_reset(ctx), "qfx_stats_reset");
+  if (profile_) check(qfx_profile_begin(ctx), "qfx_profile_begin");
+  check(qfx_timer_start(ctx), "qfx_timer_start");
+  Runner runner(plan_, ctx, rank, world);
+  runner.run(plan_.steps);
+  float ms = 0.f;
+  check(qfx_timer_stop_ms(ctx, &ms), "qfx_timer_stop_ms");
+  if (profile_) {
+    int32_t n = 0;
+    rows->assign(256, qfx_profile_row{});
+    check(qfx_profile_end(ctx, rows->data(), 256, &n), "qfx_profile_end");
+    rows->resize(std::min<int32_t>(n, 256));
+  }
+  stats->device_ms_contract = ms;
+  stats->leaves = runner.leaves();
+  check(qfx_stats_get(ctx, &stats->device), "qfx_stats_get");
+  amps->assign(2 * plan_.n_amplitudes, 0.0);
+  check(qfx_amps_download(ctx, amps->data(), plan_.n_amplitudes), "qfx_amps_download");
 }
 
 void Session::Contract(int rank, int world,
@@ -192,28 +250,65 @@ void Session::Contract(int rank, int world,
   if (world < 1 || rank < 0 || rank >= world)
     throw ERROR_MSG("Invalid rank ", rank, " of ", world, ".");
   const double t0 = now_s();
-  check(qfx_amps_reserve(ctx_, plan_.n_amplitudes), "qfx_amps_reserve");
-  check(qfx_stats_reset(ctx_), "qfx_stats_reset");
-  if (profile_) check(qfx_profile_begin(ctx_), "qfx_profile_begin");
-  check(qfx_timer_start(ctx_), "qfx_timer_start");
-  Runner runner(plan_, ctx_, rank, world);
-  runner.run(plan_.steps);
-  float ms = 0.f;
-  check(qfx_timer_stop_ms(ctx_, &ms), "qfx_timer_stop_ms");
-  if (profile_) {
-    int32_t n = 0;
-    profile_rows_.assign(256, qfx_profile_row{});
-    check(qfx_profile_end(ctx_, profile_rows_.data(), 256, &n), "qfx_profile_end");
-    profile_rows_.resize(std::min<int32_t>(n, 256));
+  const int L = (int)lanes_.size();
+  std::vector<std::vector<double>> amps(L);
+  std::vector<ExecStats> st(L);
+  std::vector<std::vector<qfx_profile_row>> rows(L);
+  std::vector<std::string> errors(L);
+  if (L == 1) {
+    ContractLane(0, rank, world, &amps[0], &st[0], &rows[0]);
+  } else {
+    std::vector<std::thread> threads;
+    for (int l = 0; l < L; ++l)
+      threads.emplace_back([&, l]() {
+        try {
+          ContractLane(l, rank * L + l, world * L, &amps[l], &st[l], &rows[l]);
+        } catch (const std::string& msg) {
+          errors[l] = msg.empty() ? std::string("unknown error") : msg;
+        } catch (const std::exception& ex) {
+          errors[l] = ex.what();
+        }
+      });
+    for (auto& t : threads) t.join();
+    for (const auto& e : errors)
+      if (!e.empty()) throw e;
   }
-  stats_.device_ms_contract = ms;
-  stats_.leaves = runner.leaves();
-  check(qfx_stats_get(ctx_, &stats_.device), "qfx_stats_get");
-  std::vector<double> host(2 * plan_.n_amplitudes);
-  check(qfx_amps_download(ctx_, host.data(), plan_.n_amplitudes), "qfx_amps_download");
+  // lanes summed in lane order (deterministic)
   amplitudes->assign(plan_.n_amplitudes, {0.0, 0.0});
-  for (uint64_t a = 0; a < plan_.n_amplitudes; ++a)
-    (*amplitudes)[a] = {host[2 * a], host[2 * a + 1]};
+  const double up = stats_.seconds_upload, fl = stats_.seconds_flatten;
+  stats_ = ExecStats{};
+  stats_.seconds_upload = up;
+  stats_.seconds_flatten = fl;
+  std::map<std::vector<int>, qfx_profile_row> merged;
+  for (int l = 0; l < L; ++l) {
+    for (uint64_t a = 0; a < plan_.n_amplitudes; ++a)
+      (*amplitudes)[a] += std::complex<double>(amps[l][2 * a], amps[l][2 * a + 1]);
+    stats_.device_ms_contract = std::max(stats_.device_ms_contract, st[l].device_ms_contract);
+    stats_.leaves += st[l].leaves;
+    const qfx_stats& d = st[l].device;
+    stats_.device.launches_total += d.launches_total;
+    stats_.device.launches_gemm_ffma += d.launches_gemm_ffma;
+    stats_.device.launches_gemm_tc += d.launches_gemm_tc;
+    stats_.device.launches_reduce += d.launches_reduce;
+    stats_.device.launches_permute += d.launches_permute;
+    stats_.device.launches_copy += d.launches_copy;
+    stats_.device.launches_gemm_tc_fused += d.launches_gemm_tc_fused;
+    stats_.device.launches_gemm_tc_pair += d.launches_gemm_tc_pair;
+    stats_.device.flops += d.flops;
+    stats_.device.bytes += d.bytes;
+    for (const auto& r : rows[l]) {
+      auto& m = merged[{r.kind, r.m_bits, r.n_bits, r.k_bits}];
+      if (m.launches == 0) m = r;
+      else {
+        m.launches += r.launches;
+        m.ms += r.ms;
+        m.flops += r.flops;
+        m.bytes += r.bytes;
+      }
+    }
+  }
+  profile_rows_.clear();
+  for (const auto& kv : merged) profile_rows_.push_back(kv.second);
   stats_.seconds_contract = now_s() - t0;
 }
 

@@ -164,8 +164,21 @@ class Session {
   const std::vector<qfx_profile_row>& profile_rows() const { return profile_rows_; }
 
  private:
+  // Upload + flatten into one lane's arena; one lane's share of Contract().
+  void PrepareLane(qfx_ctx* ctx);
+  void ContractLane(int lane, int rank, int world, std::vector<double>* amps,
+                    ExecStats* stats, std::vector<qfx_profile_row>* rows);
+
   Plan plan_;
-  qfx_ctx* ctx_ = nullptr;
+  qfx_ctx* ctx_ = nullptr;          // lane 0
+  // Lanes: extra contexts (own arena + stream) on the SAME device.  Small networks
+  // (arena of MBs, contractions of microseconds) leave most SMs idle and are bound
+  // by launch latency; their cut slices are independent, so the slices of this rank
+  // are dealt once more over the lanes (lane l acts as rank rank*L+l of world*L),
+  // each driven by its own host thread, and kernels of different slices overlap on
+  // the GPU.  One lane when the arena is large (the kernels fill the GPU).
+  std::vector<qfx_ctx*> lanes_;
+  int device_ = 0;
   ExecStats stats_;
   bool profile_ = false;
   std::vector<qfx_profile_row> profile_rows_;
