@@ -60,6 +60,8 @@ struct FusedArgs {
   uint32_t cv_ok0, cv_ok1;  // source byte offsets of k bit 0 / k bit 1
   int cv_vec;         // k0, k1 are the two lowest smem element bits: 16-byte loads
   int8_t row_perm[7]; // tile row bit i is m bit row_perm[i]
+  int n_group;        // tc_fused rasterisation: n tiles per group (power of two, divides tiles_n);
+                      // tiles run group by group, m-major inside, so a group's B' slab stays in L2
   int ksplit;         // tc_fused split-K: work items = tiles * ksplit, kblocks = k blocks per item
   float2* part;       // split-K partial results [ksplit][M][N] (natural layout)
   int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads (timing experiments)
@@ -232,6 +234,76 @@ __device__ __forceinline__ void quad_transpose(float (&x)[16], float (&y)[16], i
     if (hi) x[e] = r;
     else y[e] = r;
   }
+}
+
+// Transposed C (the rows of the tile are the FAST dimension of C in memory: what a
+// role swap produces).  A thread holds 8 complex columns of its row in v; the four
+// lanes that differ in lane bits xm0 / xm1 hold the four rows that are adjacent in
+// memory (C address bits 0 and 1).  A 4x4 transpose of complex elements inside that
+// lane group leaves every lane with ONE column of the four rows = 32 contiguous
+// bytes: one 256-bit store instead of four 8-byte stores to four 2 MB-strided lines.
+// dst0 / dst1: address of (first of the 4 rows, this lane's column) for columns 0..3
+// and 4..7 of the piece.
+__device__ __forceinline__ void tstore_piece(float (&v)[16], float2* dst0, float2* dst1,
+                                             unsigned xm0, unsigned xm1, unsigned lane) {
+  const bool P = (lane & xm0) != 0, H = (lane & xm1) != 0;
+#pragma unroll
+  for (int g4 = 0; g4 < 2; ++g4) {
+    float* e = &v[8 * g4];  // e[2i], e[2i+1] = complex column i of this group
+#pragma unroll
+    for (int b = 0; b < 4; b += 2) {
+      const float sx = P ? e[2 * b] : e[2 * b + 2], sy = P ? e[2 * b + 1] : e[2 * b + 3];
+      const float rx = __shfl_xor_sync(0xffffffffu, sx, xm0);
+      const float ry = __shfl_xor_sync(0xffffffffu, sy, xm0);
+      if (P) {
+        e[2 * b] = rx;
+        e[2 * b + 1] = ry;
+      } else {
+        e[2 * b + 2] = rx;
+        e[2 * b + 3] = ry;
+      }
+    }
+#pragma unroll
+    for (int s0 = 0; s0 < 2; ++s0) {
+      const float sx = H ? e[2 * s0] : e[2 * s0 + 4], sy = H ? e[2 * s0 + 1] : e[2 * s0 + 5];
+      const float rx = __shfl_xor_sync(0xffffffffu, sx, xm1);
+      const float ry = __shfl_xor_sync(0xffffffffu, sy, xm1);
+      if (H) {
+        e[2 * s0] = rx;
+        e[2 * s0 + 1] = ry;
+      } else {
+        e[2 * s0 + 4] = rx;
+        e[2 * s0 + 5] = ry;
+      }
+    }
+    stg256(reinterpret_cast<float*>(g4 == 0 ? dst0 : dst1), e);
+  }
+}
+
+// Setup of the transposed-store path: finds the tile-row bits that are C address
+// bits 0 and 1.  Returns false when they are not both lane bits (rows = 32 *
+// lane_group + lane) or C is not 32-byte aligned.
+struct TStore {
+  unsigned xm0, xm1;       // lane masks of the two row bits
+  unsigned long long coj;  // column offset of this lane's column (n bits 0, 1)
+  int rowb;                // this lane's row with the two bits cleared
+};
+__device__ __forceinline__ bool tstore_setup(const FusedArgs& g, const float2* C, int row, int lane,
+                                             TStore* t) {
+  if (g.c_natural || g.n_bits < 3) return false;
+  if ((reinterpret_cast<uintptr_t>(C) & 31) != 0) return false;
+  int r0 = -1, r1 = -1;
+  for (int i = 0; i < 7; ++i) {
+    if (g.c_m[g.row_perm[i]] == 0) r0 = i;
+    if (g.c_m[g.row_perm[i]] == 1) r1 = i;
+  }
+  if (r0 < 0 || r1 < 0 || r0 > 4 || r1 > 4) return false;
+  t->xm0 = 1u << r0;
+  t->xm1 = 1u << r1;
+  const int j = ((lane >> r0) & 1) | (((lane >> r1) & 1) << 1);
+  t->coj = ((j & 1) ? (1ull << g.c_n[0]) : 0ull) | ((j & 2) ? (1ull << g.c_n[1]) : 0ull);
+  t->rowb = row & ~(int)(t->xm0 | t->xm1);
+  return true;
 }
 
 // one lane of a converged warp (the same lane every time)

@@ -25,6 +25,14 @@
 
 namespace {
 
+// tile index -> (m tile, n tile): groups of n_group n tiles, m-major inside a group
+__device__ __forceinline__ void decode_tile(const FusedArgs& g, int t, int* mt, int* nt) {
+  const int per_group = (g.tiles / g.tiles_n) * g.n_group;
+  const int grp = t / per_group, r = t - grp * per_group;
+  *mt = r / g.n_group;
+  *nt = grp * g.n_group + (r - *mt * g.n_group);
+}
+
 __global__ void __launch_bounds__(FUSED_THREADS, 1)
     tc_fused_bf16x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                     const __grid_constant__ CUtensorMap tmBm, const __grid_constant__ FusedArgs g) {
@@ -96,7 +104,9 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
         const int t = w % g.tiles, kb0 = (w / g.tiles) * g.kblocks;
-        const unsigned mt = (unsigned)(t / g.tiles_n);
+        int mt_, nt_;
+        decode_tile(g, t, &mt_, &nt_);
+        const unsigned mt = (unsigned)mt_;
         const unsigned row_base =
             __reduce_or_sync(0xffffffffu, (m_sh >= 0 && ((mt >> lane) & 1u)) ? (1u << m_sh) : 0u);
         for (int kb = 0; kb < g.kblocks; ++kb) {
@@ -122,7 +132,8 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
         const int t = w % g.tiles, kb0 = (w / g.tiles) * g.kblocks;
-        const int nt = t % g.tiles_n;
+        int mt, nt;
+        decode_tile(g, t, &mt, &nt);
         if (g.b_resident && w != (int)blockIdx.x) break;
         for (int kb = kb0; kb < kb0 + g.kblocks; ++kb) {
 #pragma unroll
@@ -315,9 +326,17 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       for (int b = 0; b < 7; ++b) mq[i] |= (unsigned)((r >> b) & 1) << g.row_perm[b];
     }
     const bool quad_stores = g.c_natural && npieces >= 4 && !(g.dbg & 32);
+    TStore ts;
+    const bool t_stores = !(g.dbg & 32) && tstore_setup(g, g.C, row, lane, &ts);
+    unsigned m_local_b = 0;  // first of the 4 memory-adjacent rows of this lane's group
+    if (t_stores) {
+#pragma unroll
+      for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
+    }
     for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
       const int t = w % g.tiles;
-      const int nt = t % g.tiles_n, mt = t / g.tiles_n;
+      int mt, nt;
+      decode_tile(g, t, &mt, &nt);
       // split-K: this item's partial sums go to its own [M][N] slab (summed in a
       // fixed order by tc_splitk_finish)
       float2* const Cout =
@@ -356,6 +375,27 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
         row_off = m * N;
       } else {
         for (int q = 0; q < g.m_bits; ++q) row_off |= ((m >> q) & 1ull) << g.c_m[q];
+      }
+      if (t_stores) {
+        const unsigned long long mb = (unsigned long long)mt * BM + m_local_b;
+        unsigned long long rb = 0;
+        for (int q = 0; q < g.m_bits; ++q) rb |= ((mb >> q) & 1ull) << g.c_m[q];
+        const unsigned long long n_base =
+            ((unsigned long long)nt * bn + half * half_cols) >> 1;
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          if (p < npieces && !(g.dbg & 2)) {
+            unsigned long long co[2];
+#pragma unroll
+            for (int g4 = 0; g4 < 2; ++g4) {
+              const unsigned long long n = n_base + p * 8 + g4 * 4;
+              co[g4] = ts.coj;
+              for (int q = 2; q < g.n_bits; ++q) co[g4] |= ((n >> q) & 1ull) << g.c_n[q];
+            }
+            tstore_piece(sum[p], Cout + rb + co[0], Cout + rb + co[1], ts.xm0, ts.xm1, lane);
+          }
+        }
+        continue;
       }
       if (quad_stores) {
         float* tile_c = reinterpret_cast<float*>(Cout + (unsigned long long)mt * BM * N);
@@ -517,6 +557,19 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   g.bn = (int)std::min<uint64_t>(2 * N, MAX_BN);
   g.tiles_n = (int)((2 * N) / g.bn);
   g.tiles = (int)((M / BM) * g.tiles_n);
+  // n tiles per rasterisation group: the group's B' slab (hi + mid) should stay in L2
+  // while the m tiles sweep past it (wide N: 2^18 x 2^12 x 2^10 streamed all 67 MB of
+  // B' against every few m tiles and ran at 156 TFLOP/s)
+  {
+    const double slab_per_ntile = (double)g.bn * (double)(2 * K) * 2.0 * 2.0;
+    int G = 1;
+    while (G * 2 <= g.tiles_n && (G * 2) * slab_per_ntile <= 16.0 * 1048576.0) G *= 2;
+    if (const char* e = getenv("QFLEX_TC_NGROUP")) {
+      G = std::max(1, atoi(e));
+      while (g.tiles_n % G) --G;
+    }
+    g.n_group = G;
+  }
   g.c_natural = 1;
   for (int i = 0; i < d.n_bits; ++i)
     if (d.c_n[i] != i) g.c_natural = 0;

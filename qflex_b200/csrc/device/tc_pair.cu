@@ -382,6 +382,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       for (int b = 0; b < 7; ++b) mq[i] |= (unsigned)((r >> b) & 1) << g.row_perm[b];
     }
     const bool quad_stores = g.c_natural && npieces >= 4 && !(g.dbg & 32);
+    TStore ts;
+    const bool t_stores = !(g.dbg & 32) && tstore_setup(g, g.C, row, lane, &ts);
+    unsigned m_local_b = 0;  // first of the 4 memory-adjacent rows of this lane's group
+    if (t_stores) {
+#pragma unroll
+      for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
+    }
     for (int t = pair0; t < g.tiles; t += pair_step) {
       const unsigned long long m = (2ull * (unsigned long long)t + rank) * BM + m_local;
       unsigned long long row_off = 0;
@@ -409,6 +416,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+        if (t_stores) {
+          const unsigned long long mb = (2ull * (unsigned long long)t + rank) * BM + m_local_b;
+          unsigned long long rb = 0;
+          for (int q = 0; q < g.m_bits; ++q) rb |= ((mb >> q) & 1ull) << g.c_m[q];
+          const unsigned long long n_base =
+              ((unsigned long long)nt * bn + half * half_cols) >> 1;
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            if (p < npieces && !(g.dbg & 2)) {
+              unsigned long long co[2];
+#pragma unroll
+              for (int g4 = 0; g4 < 2; ++g4) {
+                const unsigned long long n = n_base + p * 8 + g4 * 4;
+                co[g4] = ts.coj;
+                for (int q = 2; q < g.n_bits; ++q) co[g4] |= ((n >> q) & 1ull) << g.c_n[q];
+              }
+              tstore_piece(sum[p], g.C + rb + co[0], g.C + rb + co[1], ts.xm0, ts.xm1, lane);
+            }
+          }
+          continue;
+        }
         if (quad_stores) {
           float* tile_c = reinterpret_cast<float*>(
               g.C + (2ull * (unsigned long long)t + rank) * BM * N);

@@ -120,9 +120,10 @@ int choose_lanes(const Plan& plan) {
   uint64_t slices = 1;
   for (const auto& c : plan.cuts) slices *= std::max<uint64_t>(1, c.values.size());
   const double arena_bytes = (double)plan.arena_elems * 8.0;
-  // lanes only for networks whose arena is small next to the GPU (<= 256 MB each)
-  int lanes = (int)std::min<double>(8.0, (2048.0 * 1048576.0) / std::max(arena_bytes, 1.0));
-  if (arena_bytes > 256.0 * 1048576.0) lanes = 1;
+  // lanes only for networks whose arena is small next to the GPU (<= 2 GB each, 4 GB
+  // in all): their kernels run for microseconds and do not fill the SMs
+  int lanes = (int)std::min<double>(8.0, (4096.0 * 1048576.0) / std::max(arena_bytes, 1.0));
+  if (arena_bytes > 2048.0 * 1048576.0) lanes = 1;
   lanes = (int)std::min<uint64_t>((uint64_t)std::max(lanes, 1), std::max<uint64_t>(1, slices / 2));
   return std::max(lanes, 1);
 }

@@ -194,3 +194,25 @@ def test_fused_split_k(ctx, m, n, k, scatter):
     assert e1 < TOL_TC and e1 == e2          # fixed-order slab sum: deterministic
     assert used["launches_gemm_tc_fused"] == 1, used
     assert after["launches_reduce"] - before["launches_reduce"] == 2  # one finish per run
+
+
+# ---- transposed C (rows of the tile are C's fast dimension: what a role swap gives)
+@pytest.mark.parametrize("m,n,k,groups", [
+    (12, 8, 8, None), (13, 6, 9, None), (14, 8, 8, (1, 4)), (13, 5, 8, None),
+    (15, 8, 8, None), (16, 7, 8, (0, 2)), (17, 5, 5, None), (17, 4, 4, (1,)),
+])
+def test_transposed_c_layout(ctx, m, n, k, groups):
+    rng = np.random.default_rng(31000 + 100 * m + 10 * n + k)
+    t = _natural(m, n, k) if groups is None else _grouped(m, n, k, groups)
+    t["c_m"], t["c_n"] = list(range(m)), list(range(m, m + n))
+    err, used = _run(ctx, t, rng)
+    assert err < TOL_TC
+    assert used["launches_gemm_tc_fused"] == 1, used
+
+
+def test_role_swap_produces_transposed_c_and_matches(ctx):
+    # n_bits > m_bits with natural C: the launcher swaps the operands, C becomes transposed
+    rng = np.random.default_rng(41)
+    err, used = _run(ctx, _natural(8, 14, 8), rng)
+    assert err < TOL_TC
+    assert used["launches_gemm_tc"] == 1, used

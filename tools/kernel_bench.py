@@ -25,6 +25,8 @@ def layout(m, n, k, mode):
         a_m = [p for p in pos if p not in a_k]
     b_n = list(range(n)); b_k = list(range(n, n + k))
     c_n = list(range(n)); c_m = list(range(n, n + m))
+    if os.environ.get("QFLEX_KB_CT"):  # C transposed: m lowest (what a role swap produces)
+        c_m = list(range(m)); c_n = list(range(m, m + n))
     return a_m, c_m, b_n, c_n, a_k, b_k
 
 
