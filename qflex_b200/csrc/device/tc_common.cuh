@@ -511,4 +511,18 @@ bool make_map_a(CUtensorMap* map, const float2* A, const qfx_contract_desc& d, i
   return true;
 }
 
+// Host mirror of the epilogue's store-path choice (template parameter STORE).
+inline int pick_store_mode(const FusedArgs& g, const float2* C) {
+  if (g.dbg & 32) return 0;
+  const int npieces = (g.bn >> 1) >> 4;
+  if (g.c_natural) return npieces >= 4 ? 1 : 0;
+  if (g.n_bits < 3 || (reinterpret_cast<uintptr_t>(C) & 31) != 0) return 0;
+  int r0 = -1, r1 = -1;
+  for (int i = 0; i < 7; ++i) {
+    if (g.c_m[g.row_perm[i]] == 0) r0 = i;
+    if (g.c_m[g.row_perm[i]] == 1) r1 = i;
+  }
+  return (r0 >= 0 && r1 >= 0 && r0 <= 4 && r1 <= 4) ? 2 : 0;
+}
+
 }  // namespace

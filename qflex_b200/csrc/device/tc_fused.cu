@@ -33,6 +33,9 @@ __device__ __forceinline__ void decode_tile(const FusedArgs& g, int t, int* mt, 
   *nt = grp * g.n_group + (r - *mt * g.n_group);
 }
 
+// STORE: 0 row-per-thread stores (any C layout), 1 quad-transposed (natural C, wide
+// rows), 2 transposed C; see tc_pair.cu.
+template <int STORE>
 __global__ void __launch_bounds__(FUSED_THREADS, 1)
     tc_fused_bf16x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                     const __grid_constant__ CUtensorMap tmBm, const __grid_constant__ FusedArgs g) {
@@ -325,11 +328,11 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
       for (int b = 0; b < 7; ++b) mq[i] |= (unsigned)((r >> b) & 1) << g.row_perm[b];
     }
-    const bool quad_stores = g.c_natural && npieces >= 4 && !(g.dbg & 32);
-    TStore ts;
-    const bool t_stores = !(g.dbg & 32) && tstore_setup(g, g.C, row, lane, &ts);
+    const bool quad_stores = STORE == 1;
+    TStore ts{};
+    const bool t_stores = STORE == 2 && tstore_setup(g, g.C, row, lane, &ts);
     unsigned m_local_b = 0;  // first of the 4 memory-adjacent rows of this lane's group
-    if (t_stores) {
+    if (STORE == 2 && t_stores) {
 #pragma unroll
       for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
     }
@@ -376,7 +379,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       } else {
         for (int q = 0; q < g.m_bits; ++q) row_off |= ((m >> q) & 1ull) << g.c_m[q];
       }
-      if (t_stores) {
+      if (STORE == 2 && t_stores) {
         const unsigned long long mb = (unsigned long long)mt * BM + m_local_b;
         unsigned long long rb = 0;
         for (int q = 0; q < g.m_bits; ++q) rb |= ((mb >> q) & 1ull) << g.c_m[q];
@@ -397,7 +400,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
         }
         continue;
       }
-      if (quad_stores) {
+      if (STORE == 1 && quad_stores) {
         float* tile_c = reinterpret_cast<float*>(Cout + (unsigned long long)mt * BM * N);
         const int col0 = nt * bn + half * half_cols + 8 * (lane & 3);  // float column
 #pragma unroll
@@ -616,12 +619,20 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   }
   static bool attr = false;
   if (!attr) {
-    QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  SMEM_LIMIT));
+    QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  SMEM_LIMIT));
+    QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
     attr = true;
   }
   const int grid = std::min(g.tiles * g.ksplit, ctx->sm_count);
-  tc_fused_bf16x3<<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  switch (pick_store_mode(g, C)) {
+    case 1: tc_fused_bf16x3<1><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
+    case 2: tc_fused_bf16x3<2><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
+    default: tc_fused_bf16x3<0><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  }
   QFX_CUDA(cudaGetLastError());
   if (ksplit > 1) {
     FinishArgs f{};

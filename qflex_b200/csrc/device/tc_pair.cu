@@ -97,6 +97,11 @@ __device__ __forceinline__ void umma2_commit(uint32_t bar) {
 // FusedArgs fields as in tc_fused.cu, except: tiles = number of 256-row pair
 // tiles, b_slot_bytes = bn/2 * 128 (this CTA's half), acc_stages = number of
 // accumulator SETS (one set = tiles_n accumulators of bn columns).
+// STORE: 0 row-per-thread stores (any C layout), 1 quad-transposed (natural C, wide
+// rows), 2 transposed C.  A template parameter so that an instantiation carries the
+// registers of one store path only (the d = 16 classes lost 35 % when all three
+// paths lived in one epilogue).
+template <int STORE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
     tc_pair_bf16x3(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh,
                    const __grid_constant__ CUtensorMap tmBm, const __grid_constant__ FusedArgs g) {
@@ -381,11 +386,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
       for (int b = 0; b < 7; ++b) mq[i] |= (unsigned)((r >> b) & 1) << g.row_perm[b];
     }
-    const bool quad_stores = g.c_natural && npieces >= 4 && !(g.dbg & 32);
-    TStore ts;
-    const bool t_stores = !(g.dbg & 32) && tstore_setup(g, g.C, row, lane, &ts);
+    const bool quad_stores = STORE == 1;
+    TStore ts{};
+    const bool t_stores = STORE == 2 && tstore_setup(g, g.C, row, lane, &ts);
     unsigned m_local_b = 0;  // first of the 4 memory-adjacent rows of this lane's group
-    if (t_stores) {
+    if (STORE == 2 && t_stores) {
 #pragma unroll
       for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
     }
@@ -416,7 +421,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
-        if (t_stores) {
+        if (STORE == 2 && t_stores) {
           const unsigned long long mb = (2ull * (unsigned long long)t + rank) * BM + m_local_b;
           unsigned long long rb = 0;
           for (int q = 0; q < g.m_bits; ++q) rb |= ((mb >> q) & 1ull) << g.c_m[q];
@@ -437,7 +442,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
           }
           continue;
         }
-        if (quad_stores) {
+        if (STORE == 1 && quad_stores) {
           float* tile_c = reinterpret_cast<float*>(
               g.C + (2ull * (unsigned long long)t + rank) * BM * N);
           const int col0 = nt * bn + half * half_cols + 8 * (lane & 3);  // float column
@@ -605,12 +610,20 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   }
   static bool attr = false;
   if (!attr) {
-    QFX_CUDA(cudaFuncSetAttribute(tc_pair_bf16x3, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    QFX_CUDA(cudaFuncSetAttribute(tc_pair_bf16x3<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  SMEM_LIMIT));
+    QFX_CUDA(cudaFuncSetAttribute(tc_pair_bf16x3<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  SMEM_LIMIT));
+    QFX_CUDA(cudaFuncSetAttribute(tc_pair_bf16x3<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
     attr = true;
   }
   const int grid = 2 * std::min(g.tiles, n_pairs);
-  tc_pair_bf16x3<<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  switch (pick_store_mode(g, C)) {
+    case 1: tc_pair_bf16x3<1><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
+    case 2: tc_pair_bf16x3<2><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
+    default: tc_pair_bf16x3<0><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  }
   QFX_CUDA(cudaGetLastError());
   ctx->stats.launches_gemm_tc++;
   ctx->stats.launches_gemm_tc_fused++;
