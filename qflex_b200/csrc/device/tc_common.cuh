@@ -62,6 +62,7 @@ struct FusedArgs {
   int8_t row_perm[7]; // tile row bit i is m bit row_perm[i]
   int n_group;        // tc_fused rasterisation: n tiles per group (power of two, divides tiles_n);
                       // tiles run group by group, m-major inside, so a group's B' slab stays in L2
+  int blocked;        // tc_pair: each pair owns a contiguous range of tiles (else interleaved)
   int ksplit;         // tc_fused split-K: work items = tiles * ksplit, kblocks = k blocks per item
   float2* part;       // split-K partial results [ksplit][M][N] (natural layout)
   int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads (timing experiments)

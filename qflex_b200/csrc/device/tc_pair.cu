@@ -135,6 +135,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
   const int n_acc = g.acc_stages * g.tiles_n;
   const uint32_t tmem_cols = (uint32_t)max(32, n_acc * bn);
   const int pair0 = (int)(blockIdx.x >> 1), pair_step = (int)(gridDim.x >> 1);
+  // tile -> pair assignment: interleaved (tile t to pair t mod P) or blocked (each pair
+  // a contiguous range of tiles)
+  int t_begin = pair0, t_end = g.tiles, t_step = pair_step;
+  if (g.blocked) {
+    const int per = (g.tiles + pair_step - 1) / pair_step;
+    t_begin = pair0 * per;
+    t_end = min(g.tiles, t_begin + per);
+    t_step = 1;
+  }
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < MAX_SA; ++s) {
@@ -175,7 +184,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       const int k_sh = lane < g.n_k_hi ? g.a_k_hi[lane] - 1 : -1;
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = pair0; t < g.tiles; t += pair_step) {
+      for (int t = t_begin; t < t_end; t += t_step) {
         const unsigned mt = 2u * (unsigned)t + rank;
         const unsigned row_base =
             __reduce_or_sync(0xffffffffu, (m_sh >= 0 && ((mt >> lane) & 1u)) ? (1u << m_sh) : 0u);
@@ -202,8 +211,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       int slot = 0;
       uint32_t phase = 0;
       const int half_rows = bn >> 1;
-      for (int t = pair0; t < g.tiles; t += pair_step) {
-        if (g.b_resident && t != pair0) break;
+      for (int t = t_begin; t < t_end; t += t_step) {
+        if (g.b_resident && t != t_begin) break;
         for (int kb = 0; kb < g.kblocks; ++kb) {
           for (int nt = 0; nt < g.tiles_n; ++nt) {
 #pragma unroll
@@ -230,7 +239,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       int cs = 0, bs = 0, set = 0;
       uint32_t cph = 0, bph = 0, set_phase = 0;
       const int nkk = (g.dbg & 4) ? 0 : g.nkk;
-      for (int t = pair0; t < g.tiles; t += pair_step) {
+      for (int t = t_begin; t < t_end; t += t_step) {
         for (int kb = 0; kb < g.kblocks; ++kb) {
           const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE);
           const uint64_t dAm = dAh + (uint64_t)(A16_TILE >> 4);
@@ -312,7 +321,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
     const uint32_t flip = (vec && ((ctid >> 2) & 1u)) ? ok1 : 0u;
     int as = 0, cs = 0;
     uint32_t aph = 0, cph = 0;
-    for (int t = pair0; t < g.tiles; t += pair_step) {
+    for (int t = t_begin; t < t_end; t += t_step) {
       for (int kb = 0; kb < g.kblocks; ++kb) {
         mbar_wait_spin(a_full(as), aph);
         mbar_wait_spin(c_empty(cs), cph ^ 1u);
@@ -394,7 +403,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
       for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
     }
-    for (int t = pair0; t < g.tiles; t += pair_step) {
+    for (int t = t_begin; t < t_end; t += t_step) {
       const unsigned long long m = (2ull * (unsigned long long)t + rank) * BM + m_local;
       unsigned long long row_off = 0;
       if (g.c_natural) {
@@ -591,6 +600,10 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
     if (g.sa < MAX_SA && total() + a32 <= SMEM_LIMIT) { ++g.sa; grew = true; }
     if (g.sc < MAX_SC && g.sc < g.sa && total() + a16 <= SMEM_LIMIT) { ++g.sc; grew = true; }
   }
+  if (const char* e = getenv("QFLEX_PAIR_BLOCKED")) g.blocked = atoi(e);
+  if (const char* e = getenv("QFLEX_PAIR_SA")) g.sa = std::max(1, std::min(g.sa, atoi(e)));
+  if (const char* e = getenv("QFLEX_PAIR_SC")) g.sc = std::max(1, std::min(g.sc, atoi(e)));
+  if (const char* e = getenv("QFLEX_PAIR_ACC")) g.acc_stages = std::max(1, std::min(g.acc_stages, atoi(e)));
   const int smem_bytes = total();
   if (const char* e = getenv("QFLEX_FUSED_DBG")) g.dbg = atoi(e);
 

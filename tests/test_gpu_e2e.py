@@ -87,3 +87,26 @@ def test_linearity_over_cut_values_full_size(gpu_lib):
     one = run([[2], [9], [4], [0]])
     other = run([[2], [9], [4], [15]])
     assert abs(both - (one + other)) < 1e-5 * max(abs(one), abs(other))
+
+
+def test_statevector_cases_on_gpu(gpu_lib):
+    """The circuits the reference checks against cirq (tests/python/simulation_test.py),
+    against the independent numpy state-vector simulator of tests/statevector.py;
+    the reference's own bound, 1e-6 per amplitude."""
+    import json
+    import os
+    from tests import statevector
+    fix = json.load(open(os.path.join(support.ROOT, "tests", "golden", "simulation_fixtures.json")))
+    psi = statevector.final_state_vector(fix["circuit_test"])
+    rng = np.random.default_rng(3)
+    for x in [int(v) for v in rng.integers(0, 2 ** 16, 6)]:
+        final = bin(x)[2:].zfill(16)
+        for o in ("ordering_test", "ordering_with_cuts_test"):
+            res, _ = gpu_lib.evaluate(fix["circuit_test"], fix[o], fix["grid_test"], "", final)
+            assert res[0][0] == final and abs(res[0][1] - psi[x]) < 1e-6
+    psi4 = statevector.final_state_vector(fix["circuit_test_fsim"])
+    for x in range(16):
+        final = bin(x)[2:].zfill(4)
+        res, _ = gpu_lib.evaluate(fix["circuit_test_fsim"], fix["ordering_2x2_test"],
+                                  fix["grid_2x2_test"], "", final)
+        assert abs(res[0][1] - psi4[x]) < 1e-6
