@@ -27,7 +27,9 @@ constexpr int MAX_SC = 4;                    // bf16 A stages (hi + mid each)
 constexpr int CONV_WARP0 = 4, CONV_WARPS = 8, EPI_WARP0 = CONV_WARP0 + CONV_WARPS;
 constexpr int CONV_THREADS = CONV_WARPS * 32;
 constexpr int FUSED_THREADS = (EPI_WARP0 + 8) * 32;  // 640
-constexpr int MAX_SA = 6, MAX_SB = 8, MAX_ACC = 8;
+constexpr int MAX_SA = 6, MAX_SB = 16, MAX_ACC = 8;  // barrier slots (tc_fused uses <= 8 B slots)
+constexpr int FUSED_MAX_SB = 8;
+constexpr int SMEM_FIXED = 1024 + 640;       // alignment slack + barriers + TMEM slot
 constexpr int NUM_BARS = 2 * MAX_SA + 2 * MAX_SC + 2 * MAX_SB + 2 * MAX_ACC;
 constexpr int SMEM_LIMIT = 232448;           // 227 KB opt-in maximum per CTA
 constexpr int MAX_TILE_BITS = 12;

@@ -592,12 +592,12 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   g.a32_bytes = 8u << g.tile_bits;
   g.b_slot_bytes = (uint32_t)g.bn * 128u;
   g.acc_stages = std::min(MAX_ACC, 512 / g.bn);
-  const int fixed = 1024 + 512;
+  const int fixed = SMEM_FIXED;
   const int slot = (int)g.b_slot_bytes, a32 = (int)g.a32_bytes, a16 = 2 * A16_TILE;
   g.sc = 2;
   g.sb = 3;
   g.sa = 2;
-  g.b_resident = (ksplit == 1 && g.tiles_n == 1 && 2 * g.kblocks <= MAX_SB) ? 1 : 0;
+  g.b_resident = (ksplit == 1 && g.tiles_n == 1 && 2 * g.kblocks <= FUSED_MAX_SB) ? 1 : 0;
   if (g.b_resident) g.sb = 2 * g.kblocks;
   auto total = [&]() { return fixed + g.sc * a16 + g.sb * slot + g.sa * a32; };
   if (total() > SMEM_LIMIT) return QFX_OK;
@@ -605,7 +605,7 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   for (bool grew = true; grew;) {
     grew = false;
     if (g.sa < MAX_SA && total() + a32 <= SMEM_LIMIT) { ++g.sa; grew = true; }
-    if (!g.b_resident && g.sb < MAX_SB && total() + slot <= SMEM_LIMIT) { ++g.sb; grew = true; }
+    if (!g.b_resident && g.sb < FUSED_MAX_SB && total() + slot <= SMEM_LIMIT) { ++g.sb; grew = true; }
     if (g.sc < MAX_SC && g.sc < g.sa && total() + a16 <= SMEM_LIMIT) { ++g.sc; grew = true; }
   }
   const int smem_bytes = total();

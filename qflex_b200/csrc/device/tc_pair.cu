@@ -564,7 +564,13 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   g.nkk = (int)std::min<uint64_t>(4, (2 * K) / 16);
   g.chunk = g.kblocks;
   g.nchunks = 1;
-  g.bn = (int)std::min<uint64_t>(2 * N, MAX_BN);
+  // UMMA N per instruction: 256, except N' = 256 where two n tiles of 128 (two
+  // accumulators draining alternately) beat one of 256 (2^20 x 128 x 256: 0.61 ->
+  // 0.51 ms).  For N' = 512, 128-wide tiles (8-KB B' slots, twice as many) measured
+  // 2 % slower than 256.
+  int bn_max = (2 * N == 256) ? 128 : MAX_BN;
+  if (const char* e = getenv("QFLEX_PAIR_BN")) bn_max = std::max(32, std::min(MAX_BN, atoi(e)));
+  g.bn = (int)std::min<uint64_t>(2 * N, (uint64_t)bn_max);
   g.tiles_n = (int)((2 * N) / g.bn);
   g.tiles = (int)(M / (2 * BM));
   g.c_natural = 1;
@@ -584,7 +590,7 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   g.a32_bytes = 8u << g.tile_bits;
   g.b_slot_bytes = (uint32_t)(g.bn / 2) * 128u;
   g.acc_stages = std::max(1, std::min(MAX_ACC / g.tiles_n, 512 / (g.bn * g.tiles_n)));
-  const int fixed = 1024 + 512;
+  const int fixed = SMEM_FIXED;
   const int slot = (int)g.b_slot_bytes, a32 = (int)g.a32_bytes, a16 = 2 * A16_TILE;
   const int slots_per_kb = 2 * g.tiles_n;
   g.sc = 2;
@@ -601,8 +607,15 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
     if (g.sc < MAX_SC && g.sc < g.sa && total() + a16 <= SMEM_LIMIT) { ++g.sc; grew = true; }
   }
   if (const char* e = getenv("QFLEX_PAIR_BLOCKED")) g.blocked = atoi(e);
-  if (const char* e = getenv("QFLEX_PAIR_SA")) g.sa = std::max(1, std::min(g.sa, atoi(e)));
-  if (const char* e = getenv("QFLEX_PAIR_SC")) g.sc = std::max(1, std::min(g.sc, atoi(e)));
+  // tuning overrides (exact stage counts; rejected when they do not fit)
+  if (getenv("QFLEX_PAIR_SA") || getenv("QFLEX_PAIR_SB") || getenv("QFLEX_PAIR_SC")) {
+    const int sa0 = g.sa, sb0 = g.sb, sc0 = g.sc;
+    if (const char* e = getenv("QFLEX_PAIR_SA")) g.sa = std::max(1, std::min(MAX_SA, atoi(e)));
+    if (const char* e = getenv("QFLEX_PAIR_SC")) g.sc = std::max(1, std::min(MAX_SC, atoi(e)));
+    if (const char* e = getenv("QFLEX_PAIR_SB"))
+      if (!g.b_resident) g.sb = std::max(slots_per_kb, std::min(MAX_SB, atoi(e)));
+    if (total() > SMEM_LIMIT) { g.sa = sa0; g.sb = sb0; g.sc = sc0; }
+  }
   if (const char* e = getenv("QFLEX_PAIR_ACC")) g.acc_stages = std::max(1, std::min(g.acc_stages, atoi(e)));
   const int smem_bytes = total();
   if (const char* e = getenv("QFLEX_FUSED_DBG")) g.dbg = atoi(e);
