@@ -64,6 +64,7 @@ struct FusedArgs {
   int8_t row_perm[7]; // tile row bit i is m bit row_perm[i]
   int n_group;        // tc_fused rasterisation: n tiles per group (power of two, divides tiles_n);
                       // tiles run group by group, m-major inside, so a group's B' slab stays in L2
+  int stagger_ns;     // tc_pair: start delay per pair index (tuning experiment)
   int blocked;        // tc_pair: each pair owns a contiguous range of tiles (else interleaved)
   int ksplit;         // tc_fused split-K: work items = tiles * ksplit, kblocks = k blocks per item
   float2* part;       // split-K partial results [ksplit][M][N] (natural layout)
@@ -188,6 +189,31 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
       : "r"(taddr)
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Asynchronous form: issue several loads back to back, then ONE tmem_wait_ld() and a
+// tmem_reg_fence() per destination (keeps register uses behind the wait).  With a
+// wait after every x16 load, draining a 128-column accumulator cost ~8 load
+// latencies on the epilogue's critical path.
+__device__ __forceinline__ void tmem_ld16_async(uint32_t taddr, float (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]),
+        "=f"(r[7]), "=f"(r[8]), "=f"(r[9]), "=f"(r[10]), "=f"(r[11]), "=f"(r[12]), "=f"(r[13]),
+        "=f"(r[14]), "=f"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_reg_fence(float (&r)[16]) {
+  asm volatile("" : "+f"(r[0]), "+f"(r[1]), "+f"(r[2]), "+f"(r[3]), "+f"(r[4]), "+f"(r[5]),
+                    "+f"(r[6]), "+f"(r[7]), "+f"(r[8]), "+f"(r[9]), "+f"(r[10]), "+f"(r[11]),
+                    "+f"(r[12]), "+f"(r[13]), "+f"(r[14]), "+f"(r[15])
+               :
+               : "memory");
 }
 
 __device__ __forceinline__ float4 lds128(uint32_t addr) {

@@ -184,6 +184,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       const int k_sh = lane < g.n_k_hi ? g.a_k_hi[lane] - 1 : -1;
       int stage = 0;
       uint32_t phase = 0;
+      // optional start stagger (ns per pair): spreads the pairs' load / store bursts
+      if (g.stagger_ns > 0) {
+        const long long t0 = clock64();
+        const long long wait = (long long)g.stagger_ns * pair0 * 2;  // ~2 clocks per ns
+        while (clock64() - t0 < wait) {}
+      }
       for (int t = t_begin; t < t_end; t += t_step) {
         const unsigned mt = 2u * (unsigned)t + rank;
         const unsigned row_base =
@@ -419,14 +425,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) +
                                (uint32_t)(acc * bn + half * half_cols);
 #pragma unroll
-        for (int p = 0; p < 8; ++p) {
-          if (p < npieces && !(g.dbg & 8)) {
-            uint32_t r[16];
-            tmem_ld16(t_row + (uint32_t)(p * 16), r);
+        for (int p = 0; p < 8; ++p)
+          if (p < npieces && !(g.dbg & 8)) tmem_ld16_async(t_row + (uint32_t)(p * 16), sum[p]);
+        tmem_wait_ld();
 #pragma unroll
-            for (int j = 0; j < 16; ++j) sum[p][j] = __uint_as_float(r[j]);
-          }
-        }
+        for (int p = 0; p < 8; ++p)
+          if (p < npieces && !(g.dbg & 8)) tmem_reg_fence(sum[p]);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
@@ -607,6 +611,11 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
     if (g.sc < MAX_SC && g.sc < g.sa && total() + a16 <= SMEM_LIMIT) { ++g.sc; grew = true; }
   }
   if (const char* e = getenv("QFLEX_PAIR_BLOCKED")) g.blocked = atoi(e);
+  // start stagger: the pairs otherwise run in lockstep and hit HBM with synchronized
+  // load / store bursts (2^20 x 256 x 256: 0.947 -> 0.926 ms); only when a pair has
+  // enough tiles for the start delay (<= one tile time for the last pair) to pay off
+  g.stagger_ns = (g.kblocks >= 4 && g.tiles >= 16 * n_pairs) ? 120 : 0;
+  if (const char* e = getenv("QFLEX_PAIR_STAGGER")) g.stagger_ns = atoi(e);
   // tuning overrides (exact stage counts; rejected when they do not fit)
   if (getenv("QFLEX_PAIR_SA") || getenv("QFLEX_PAIR_SB") || getenv("QFLEX_PAIR_SC")) {
     const int sa0 = g.sa, sb0 = g.sb, sc0 = g.sc;
