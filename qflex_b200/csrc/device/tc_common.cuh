@@ -64,6 +64,8 @@ struct FusedArgs {
   int8_t row_perm[7]; // tile row bit i is m bit row_perm[i]
   int n_group;        // tc_fused rasterisation: n tiles per group (power of two, divides tiles_n);
                       // tiles run group by group, m-major inside, so a group's B' slab stays in L2
+  int dual;           // tc_pair, K = 16: a stage carries TWO m tiles (m bit 7 rides as a fifth k bit
+                      // of the A tile: columns 32..63 of the bf16 row); two accumulators per stage
   int stagger_ns;     // tc_pair: start delay per pair index (tuning experiment)
   int blocked;        // tc_pair: each pair owns a contiguous range of tiles (else interleaved)
   int ksplit;         // tc_fused split-K: work items = tiles * ksplit, kblocks = k blocks per item

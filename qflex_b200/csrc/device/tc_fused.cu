@@ -600,6 +600,10 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   g.b_resident = (ksplit == 1 && g.tiles_n == 1 && 2 * g.kblocks <= FUSED_MAX_SB) ? 1 : 0;
   if (g.b_resident) g.sb = 2 * g.kblocks;
   auto total = [&]() { return fixed + g.sc * a16 + g.sb * slot + g.sa * a32; };
+  if (g.b_resident && total() > SMEM_LIMIT) {  // all of B' does not fit: stream it
+    g.b_resident = 0;
+    g.sb = 3;
+  }
   if (total() > SMEM_LIMIT) return QFX_OK;
   // grow round-robin while it fits: fp32 stages (memory-level parallelism) first
   for (bool grew = true; grew;) {

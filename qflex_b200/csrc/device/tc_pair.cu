@@ -132,7 +132,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int bn = g.bn;
-  const int n_acc = g.acc_stages * g.tiles_n;
+  const int subs = g.dual ? 2 : g.tiles_n;  // accumulators per tile
+  const int n_acc = g.acc_stages * subs;
   const uint32_t tmem_cols = (uint32_t)max(32, n_acc * bn);
   const int pair0 = (int)(blockIdx.x >> 1), pair_step = (int)(gridDim.x >> 1);
   // tile -> pair assignment: interleaved (tile t to pair t mod P) or blocked (each pair
@@ -245,6 +246,43 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       int cs = 0, bs = 0, set = 0;
       uint32_t cph = 0, bph = 0, set_phase = 0;
       const int nkk = (g.dbg & 4) ? 0 : g.nkk;
+      if (g.dual) {
+        // K = 16: one stage = two m tiles side by side in the bf16 rows (columns 0..31
+        // and 32..63); B' (resident, slots 0 = mid, 1 = hi) is the same for both
+        const uint64_t dBm = smem_desc_sw128(b_base);
+        const uint64_t dBh = smem_desc_sw128(b_base + g.b_slot_bytes);
+        mbar_wait_cluster(b_full(0), 0u);
+        mbar_wait_cluster(b_full(1), 0u);
+        for (int t = t_begin; t < t_end; t += t_step) {
+          const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE);
+          const uint64_t dAm = dAh + (uint64_t)(A16_TILE >> 4);
+          mbar_wait_cluster(c_full(cs), cph);
+          for (int h = 0; h < 2; ++h) {
+            const int acc = set * 2 + h;
+            mbar_wait_cluster(tempty_bar(acc), set_phase ^ 1u);
+            const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
+            tc_fence_after();
+            if (leader) {
+              for (int kk = 0; kk < nkk; ++kk)
+                umma2_bf16(d_tmem, dAh + 2 * (2 * h + kk), dBm + 2 * kk, idesc, kk == 0 ? 0u : 1u);
+              for (int kk = 0; kk < nkk; ++kk)
+                umma2_bf16(d_tmem, dAm + 2 * (2 * h + kk), dBh + 2 * kk, idesc, 1u);
+              for (int kk = 0; kk < nkk; ++kk)
+                umma2_bf16(d_tmem, dAh + 2 * (2 * h + kk), dBh + 2 * kk, idesc, 1u);
+              if (h == 1) umma2_commit(c_empty(cs));
+              umma2_commit(tfull_bar(acc));
+            }
+          }
+          if (++cs == g.sc) {
+            cs = 0;
+            cph ^= 1u;
+          }
+          if (++set == g.acc_stages) {
+            set = 0;
+            set_phase ^= 1u;
+          }
+        }
+      } else
       for (int t = t_begin; t < t_end; t += t_step) {
         for (int kb = 0; kb < g.kblocks; ++kb) {
           const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE);
@@ -410,15 +448,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
     }
     for (int t = t_begin; t < t_end; t += t_step) {
-      const unsigned long long m = (2ull * (unsigned long long)t + rank) * BM + m_local;
-      unsigned long long row_off = 0;
-      if (g.c_natural) {
-        row_off = m * N;
-      } else {
-        for (int q = 0; q < g.m_bits; ++q) row_off |= ((m >> q) & 1ull) << g.c_m[q];
-      }
-      for (int nt = 0; nt < g.tiles_n; ++nt) {
-        const int acc = set * g.tiles_n + nt;
+      for (int sub = 0; sub < subs; ++sub) {
+        // dual: the two accumulators are two m tiles; else the n tiles of one m tile
+        const int nt = g.dual ? 0 : sub;
+        const unsigned long long mtile =
+            g.dual ? (2ull * (unsigned long long)t + rank) * 2 + sub
+                   : 2ull * (unsigned long long)t + rank;
+        const unsigned long long m = mtile * BM + m_local;
+        unsigned long long row_off = 0;
+        if (g.c_natural) {
+          row_off = m * N;
+        } else {
+          for (int q = 0; q < g.m_bits; ++q) row_off |= ((m >> q) & 1ull) << g.c_m[q];
+        }
+        const int acc = set * subs + sub;
         float sum[8][16];
         mbar_wait_spin(tfull_bar(acc), set_phase);
         tc_fence_after();
@@ -435,7 +478,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         __syncwarp();
         if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
         if (STORE == 2 && t_stores) {
-          const unsigned long long mb = (2ull * (unsigned long long)t + rank) * BM + m_local_b;
+          const unsigned long long mb = mtile * BM + m_local_b;
           unsigned long long rb = 0;
           for (int q = 0; q < g.m_bits; ++q) rb |= ((mb >> q) & 1ull) << g.c_m[q];
           const unsigned long long n_base =
@@ -456,8 +499,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
           continue;
         }
         if (STORE == 1 && quad_stores) {
-          float* tile_c = reinterpret_cast<float*>(
-              g.C + (2ull * (unsigned long long)t + rank) * BM * N);
+          float* tile_c = reinterpret_cast<float*>(g.C + mtile * BM * N);
           const int col0 = nt * bn + half * half_cols + 8 * (lane & 3);  // float column
 #pragma unroll
           for (int pp = 0; pp < 4; ++pp) {
@@ -552,14 +594,27 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
     memcpy(d.b_k, bk, d.k_bits);
   }
   FusedArgs g{};
-  g.kb_bits = std::min(5, (int)d.k_bits);
+  // K = 16 (d = 16 bonds, HBM-bound): a 128-row stage is only 16 KB and the per-stage
+  // handshakes, not HBM, bound the kernel (~1200 clocks per stage whatever its size).
+  // Dual mode doubles the stage: m bit 7 rides along as a fifth k bit of the A tile,
+  // so the bf16 rows hold two m tiles side by side, multiplied into two accumulators.
+  static const bool dual_off = [] {
+    const char* e = getenv("QFLEX_PAIR_DUAL");
+    return e != nullptr && atoi(e) == 0;
+  }();
+  g.dual = (!dual_off && d.k_bits == 4 && d.n_bits <= 6 && (int)(M / (4 * BM)) >= n_pairs) ? 1 : 0;
+  g.kb_bits = g.dual ? 5 : std::min(5, (int)d.k_bits);
   g.tile_bits = 7 + g.kb_bits;
   uint64_t span = 0;
   for (int i = 0; i < d.m_bits; ++i) span |= 1ull << d.a_m[i];
   for (int i = 0; i < d.k_bits; ++i) span |= 1ull << d.a_k[i];
   span += 1;
   CUtensorMap mA, mBh, mBm;
-  if (!make_map_a(&mA, A, d, g.kb_bits, span, &g)) return QFX_OK;
+  {
+    qfx_contract_desc dm = d;
+    if (g.dual) dm.a_k[4] = d.a_m[7];  // the tile's fifth "k" bit
+    if (!make_map_a(&mA, A, dm, g.kb_bits, span, &g)) return QFX_OK;
+  }
 
   g.C = C;
   g.m_bits = d.m_bits;
@@ -577,6 +632,11 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   g.bn = (int)std::min<uint64_t>(2 * N, (uint64_t)bn_max);
   g.tiles_n = (int)((2 * N) / g.bn);
   g.tiles = (int)(M / (2 * BM));
+  if (g.dual) {
+    g.tiles = (int)(M / (4 * BM));
+    g.kblocks = 1;
+    g.chunk = 1;
+  }
   g.c_natural = 1;
   for (int i = 0; i < d.n_bits; ++i)
     if (d.c_n[i] != i) g.c_natural = 0;
@@ -585,15 +645,17 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   if ((reinterpret_cast<uintptr_t>(C) & 31) != 0) g.c_natural = 0;
   memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
   memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
-  g.n_m_hi = d.m_bits - 7;
-  for (int i = 0; i < g.n_m_hi; ++i) g.a_m_hi[i] = d.a_m[7 + i];
-  g.n_k_hi = d.k_bits - g.kb_bits;
+  const int m_lo = g.dual ? 8 : 7;  // m bits inside a stage
+  g.n_m_hi = d.m_bits - m_lo;
+  for (int i = 0; i < g.n_m_hi; ++i) g.a_m_hi[i] = d.a_m[m_lo + i];
+  g.n_k_hi = g.dual ? 0 : d.k_bits - g.kb_bits;
   for (int i = 0; i < g.n_k_hi; ++i) g.a_k_hi[i] = d.a_k[g.kb_bits + i];
 
   // shared memory plan per CTA: bf16 A stages, half-tile B slots, fp32 A stages
   g.a32_bytes = 8u << g.tile_bits;
   g.b_slot_bytes = (uint32_t)(g.bn / 2) * 128u;
-  g.acc_stages = std::max(1, std::min(MAX_ACC / g.tiles_n, 512 / (g.bn * g.tiles_n)));
+  const int subs = g.dual ? 2 : g.tiles_n;  // accumulators per tile
+  g.acc_stages = std::max(1, std::min(MAX_ACC / subs, 512 / (g.bn * subs)));
   const int fixed = SMEM_FIXED;
   const int slot = (int)g.b_slot_bytes, a32 = (int)g.a32_bytes, a16 = 2 * A16_TILE;
   const int slots_per_kb = 2 * g.tiles_n;
@@ -603,6 +665,11 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   g.b_resident = (slots_per_kb * g.kblocks <= MAX_SB) ? 1 : 0;
   if (g.b_resident) g.sb = slots_per_kb * g.kblocks;
   auto total = [&]() { return fixed + g.sc * a16 + g.sb * slot + g.sa * a32; };
+  if (g.b_resident && total() > SMEM_LIMIT) {  // all of B' does not fit: stream it
+    g.b_resident = 0;
+    g.sb = slots_per_kb;
+  }
+  if (g.dual && !g.b_resident) return QFX_OK;  // (cannot happen: 2 slots of <= 8 KB)
   if (g.sb > MAX_SB || total() > SMEM_LIMIT) return QFX_OK;
   for (bool grew = true; grew;) {
     grew = false;

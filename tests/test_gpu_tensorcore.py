@@ -216,3 +216,13 @@ def test_role_swap_produces_transposed_c_and_matches(ctx):
     err, used = _run(ctx, _natural(8, 14, 8), rng)
     assert err < TOL_TC
     assert used["launches_gemm_tc"] == 1, used
+
+
+@pytest.mark.parametrize("m,n,k", [(16, 7, 7), (15, 7, 8), (13, 7, 7), (12, 8, 7)])
+def test_b_prime_too_large_to_stay_resident_is_streamed(ctx, m, n, k):
+    # N' = 256 / K' = 256..512: all of B' would need > 227 KB of shared memory; the
+    # in-kernel-conversion kernels must stream it, not hand over to the pre-split path
+    rng = np.random.default_rng(52000 + 100 * m + 10 * n + k)
+    err, used = _run(ctx, _natural(m, n, k), rng)
+    assert err < TOL_TC
+    assert used["launches_gemm_tc_fused"] == 1, used
