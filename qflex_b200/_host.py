@@ -243,14 +243,23 @@ def simulate(options, lib=None):
         lib = lib or default_library()
         initial = _load_state(options, "initial")
         final = _load_state(options, "final")
-        if len(initial) != 1 or len(final) != 1:
+        if len(initial) != 1:
             raise QflexError("Not yet supported")
-        result, _ = lib.evaluate(
-            _load_option(options, "circuit"), _load_option(options, "ordering"),
-            _load_option(options, "grid"), initial[0], final[0],
-            memory_limit=options.get("memory_limit"), device=options.get("device", 0),
-            rank=options.get("rank", 0), world=options.get("world", 1),
-            precision=options.get("precision", "auto"))
+        # Several final states in one call (the reference answers "Not yet supported",
+        # src/pybind_main.cpp:111-113, and qflexcirq calls simulate once per bitstring):
+        # the inputs are read once and the device buffers of one evaluation are reused
+        # by the next (parked arena), so a batch costs parse + plan + contract per state.
+        circuit = _load_option(options, "circuit")
+        ordering = _load_option(options, "ordering")
+        grid = _load_option(options, "grid")
+        result = []
+        for state in final:
+            part, _ = lib.evaluate(
+                circuit, ordering, grid, initial[0], state,
+                memory_limit=options.get("memory_limit"), device=options.get("device", 0),
+                rank=options.get("rank", 0), world=options.get("world", 1),
+                precision=options.get("precision", "auto"))
+            result.extend(part)
         return result
     except QflexError as e:
         print(e, file=sys.stderr)

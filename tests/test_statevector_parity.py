@@ -53,3 +53,16 @@ def test_terminal_cuts_give_the_whole_distribution_of_the_cut_qubits(emul):
 
 def test_norm_of_the_simulated_state_is_one(psi16):
     assert abs(np.vdot(psi16, psi16) - 1) < 1e-9
+
+
+def test_simulate_accepts_a_batch_of_final_states(emul):
+    import qflex_b200
+    psi = statevector.final_state_vector(FIX["circuit_test_fsim"])
+    states = ["0000", "0110", "1011", "1111"]
+    out = qflex_b200.simulate({"circuit": FIX["circuit_test_fsim"].split("\n"),
+                               "ordering": FIX["ordering_2x2_test"].split("\n"),
+                               "grid": FIX["grid_2x2_test"].split("\n"),
+                               "final_states": states}, lib=emul)
+    assert [s for s, _ in out] == states
+    for s, a in out:
+        assert abs(a - psi[int(s, 2)]) < 1e-6
