@@ -210,11 +210,30 @@ int qfx_create(int device, qfx_ctx** ctx_out) {
     return QFX_ERR_ARG;
   }
   QFX_CUDA(cudaSetDevice(device));
-  cudaDeviceProp prop;
-  QFX_CUDA(cudaGetDeviceProperties(&prop, device));
-  if (prop.major < 10) {
-    qfx_set_error(std::string("qfx_create: device '") + prop.name +
-                  "' is not sm_100-class; this library is built for sm_100a only");
+  // cudaGetDeviceProperties costs ~20 ms per call; two attributes are all we need,
+  // cached per device (a context is created per EvaluateCircuit call)
+  static std::mutex attr_mu;
+  static int attr_major[64], attr_sms[64];
+  static bool attr_known[64];
+  int major = 0, sms = 0;
+  {
+    std::lock_guard<std::mutex> lock(attr_mu);
+    if (device < 64 && attr_known[device]) {
+      major = attr_major[device];
+      sms = attr_sms[device];
+    } else {
+      QFX_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+      QFX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+      if (device < 64) {
+        attr_major[device] = major;
+        attr_sms[device] = sms;
+        attr_known[device] = true;
+      }
+    }
+  }
+  if (major < 10) {
+    qfx_set_error("qfx_create: the device is not sm_100-class; this library is built for "
+                  "sm_100a only");
     return QFX_ERR_ARG;
   }
   qfx_ctx* ctx = new (std::nothrow) qfx_ctx();
@@ -223,7 +242,7 @@ int qfx_create(int device, qfx_ctx** ctx_out) {
     return QFX_ERR_OOM;
   }
   ctx->device = device;
-  ctx->sm_count = prop.multiProcessorCount;
+  ctx->sm_count = sms;
   if (const char* e = getenv("QFLEX_TC_CHUNK")) ctx->tc_chunk = atoi(e);
   QFX_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   QFX_CUDA(cudaEventCreate(&ctx->ev0));
