@@ -152,8 +152,13 @@ void build_network(const QflexInput& input,
   const QflexCircuit& circuit = input.circuit;
   const std::size_t I = input.grid.I, J = input.grid.J;
   const auto& off = input.grid.qubits_off;
+  // (passing `off` to find_grid_coord_in_list would copy it into a std::optional on
+  // every call -- thousands of calls per plan)
+  std::vector<char> off_mask(I * J, 0);
+  for (const auto& c : off)
+    if (c.size() == 2 && c[0] < I && c[1] < J) off_mask[c[0] * J + c[1]] = 1;
   auto is_off = [&](std::size_t i, std::size_t j) {
-    return find_grid_coord_in_list(off, i, j);
+    return i < I && j < J && off_mask[i * J + j] != 0;
   };
   const std::size_t active = I * J - off.size();
   if (circuit.num_active_qubits != active)
@@ -347,8 +352,13 @@ Plan BuildPlan(const QflexInput& input,
   plan.steps.reserve(512);
   const std::size_t I = input.grid.I, J = input.grid.J;
   const auto& off = input.grid.qubits_off;
+  // (passing `off` to find_grid_coord_in_list would copy it into a std::optional on
+  // every call -- thousands of calls per plan)
+  std::vector<char> off_mask(I * J, 0);
+  for (const auto& c : off)
+    if (c.size() == 2 && c[0] < I && c[1] < J) off_mask[c[0] * J + c[1]] = 1;
   auto is_off = [&](std::size_t i, std::size_t j) {
-    return find_grid_coord_in_list(off, i, j);
+    return i < I && j < J && off_mask[i * J + j] != 0;
   };
 
   std::vector<std::vector<SiteNet>> net;
