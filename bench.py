@@ -34,34 +34,34 @@ WORKLOADS = {
         cuts={1: [[0, 1], [0, 1], [0, 1], [0]], 2: [[0, 1], [0, 1], [0, 1], [0, 1]],
               4: [[0, 1], [0, 1], [0, 1], [0, 1, 2, 3]],
               8: [[0, 1], [0, 1], [0, 1, 2, 3], [0, 1, 2, 3]]},
-        reference_sample=[[0], [0], [0], [0]], memory=64 << 30),
+        reference_sample=[[0], [0], [0], [0]], memory=64 << 30, total_slices=65536),
     "bristlecone_70_1-24-1": dict(
         circuit="bristlecone_70_1-24-1_0.txt", ordering="bristlecone_70.txt",
         grid="bristlecone_70.txt",
         cuts={1: [[0, 1], [0, 1], [0, 1], [0]], 2: [[0, 1], [0, 1], [0, 1], [0, 1]],
               4: [[0, 1], [0, 1], [0, 1], [0, 1, 2, 3]],
               8: [[0, 1], [0, 1], [0, 1, 2, 3], [0, 1, 2, 3]]},
-        reference_sample=[[0, 1], [0, 1], [0, 1], [0]], memory=8 << 30),
+        reference_sample=[[0, 1], [0, 1], [0, 1], [0]], memory=8 << 30, total_slices=4096),
     # BASELINE configs[4] stand-in (m=20 is not representable): Sycamore-53
     # m=10, a low-fidelity batch of 64 of its 16384 slices, STRONG scaling (the same
     # 64 slices whatever the GPU count)
     "sycamore_53_10": dict(
         circuit="sycamore_53_10_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1, 2, 3], [0, 1, 2, 3], [0, 1, 2, 3]]},
-        reference_sample=[[0], [0], [0]], memory=100 << 30),
+        reference_sample=[[0], [0], [0]], memory=100 << 30, total_slices=16384),
     # BASELINE configs[2] at m=8: 64 slices x a batch of 64 output bitstrings, strong scaling
     "sycamore_53_8_batch64": dict(
         circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         scaling="strong",
         cuts={"all": [list(range(16)), [0, 1, 2, 3], [0]] + [[0, 1]] * 6},
-        reference_sample=[[0], [0], [0]] + [[0, 1]] * 6, memory=8 << 30),
+        reference_sample=[[0], [0], [0]] + [[0, 1]] * 6, memory=8 << 30, total_slices=4096),
     # BASELINE configs[3]: 7x7 1-32-1 with the reference's ExampleOrdering schedule,
     # 64 of its 256 slices x 64 output bitstrings, strong scaling
     "rectangular_7x7_1-32-1": dict(
         circuit="rectangular_7x7_1-32-1_0.txt", ordering="rectangular_7x7_v2.txt",
         grid="rectangular_7x7.txt", scaling="strong",
         cuts={"all": [list(range(16)), [0, 1, 2, 3]] + [[0, 1]] * 6},
-        reference_sample=[[0], [0]] + [[0, 1]] * 6, memory=16 << 30),
+        reference_sample=[[0], [0]] + [[0, 1]] * 6, memory=16 << 30, total_slices=256),
 }
 
 
@@ -418,8 +418,11 @@ def main():
                    "arena_gb": arena_bytes / 2 ** 30, "precision": args.precision,
                    "l2": "working set per contraction (>= 2 GB patches) exceeds the 126 MB L2",
                    "collective": "one NCCL all-reduce(sum) of %d complex128 per step" % n_amps},
-        "slices_per_s": total_leaves / wall, "amplitudes_per_s_full_circuit": total_leaves / wall / 65536.0
-        if args.workload == "bristlecone_70_1-32-1" else None,
+        # leaves = (bond-cut slices) x (output bitstrings): one leaf = one scalar result
+        "slices_per_s": total_leaves / wall,
+        # amplitudes/s of the FULL circuit at this rate: every output bitstring needs all
+        # of the circuit's bond-cut slices
+        "amplitudes_per_s_full_circuit": total_leaves / wall / float(w["total_slices"]),
         "device_ms_per_step_rank0": dev_ms / args.steps,
         "e2e": {"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 16 * n_amps, "steps": e2e_steps,
