@@ -847,43 +847,82 @@ extern "C" int qfx_scalar_accumulate(qfx_ctx* ctx, uint64_t off, uint64_t slot) 
 // bristlecone_70 1-32-1) become one launch.
 namespace {
 
-__device__ __forceinline__ unsigned long long chain_deposit(unsigned long long v, int bits,
-                                                            const int8_t* pos) {
-  unsigned long long o = 0;
-  for (int q = 0; q < bits; ++q) o |= ((v >> q) & 1ull) << pos[q];
+__device__ __forceinline__ uint32_t chain_deposit(uint32_t v, int bits, const int8_t* pos) {
+  uint32_t o = 0;
+  for (int q = 0; q < bits; ++q) o |= ((v >> q) & 1u) << pos[q];
   return o;
 }
 
+__device__ __forceinline__ void chain_point(const float2* __restrict__ A,
+                                            const float2* __restrict__ B, float2* C, uint32_t ao,
+                                            uint32_t bo, uint32_t co, unsigned K,
+                                            const uint32_t* ka, const uint32_t* kb) {
+  float sx = 0.f, sy = 0.f;
+  for (unsigned k = 0; k < K; ++k) {
+    const float2 a = A[ao | ka[k]];
+    const float2 b = B[bo | kb[k]];
+    sx = fmaf(a.x, b.x, sx);
+    sx = fmaf(-a.y, b.y, sx);
+    sy = fmaf(a.x, b.y, sy);
+    sy = fmaf(a.y, b.x, sy);
+  }
+  C[co] = make_float2(sx, sy);
+}
+
+// One block = one chain.  Per step the bit tables of the descriptor become three
+// per-output-bit offset words (xa/xb/xc) and two per-k offset tables in shared
+// memory; a thread owns the outputs whose low 10 index bits are its thread id and
+// walks the remaining bits in Gray-code order (one XOR per operand per output),
+// four outputs per trip so that a late step's 2^16..2^20 outputs keep several loads
+// in flight per thread -- the block is alone on its SM and latency is all it pays.
 __global__ void __launch_bounds__(1024)
     contract_chains(float2* arena, const qfx_contract_desc* descs, const int32_t* chain_first) {
   __shared__ qfx_contract_desc d;
+  __shared__ uint32_t xa[32], xb[32], xc[32], ka[64], kb[64];
   const int first = chain_first[blockIdx.x], last = chain_first[blockIdx.x + 1];
+  const unsigned tid = threadIdx.x;
   for (int s = first; s < last; ++s) {
-    __syncthreads();  // previous step's results visible; `d` no longer in use
-    for (int i = threadIdx.x; i < (int)(sizeof(qfx_contract_desc) / 4); i += blockDim.x)
+    __syncthreads();  // previous step's results visible; tables no longer in use
+    for (int i = tid; i < (int)(sizeof(qfx_contract_desc) / 4); i += blockDim.x)
       reinterpret_cast<uint32_t*>(&d)[i] = reinterpret_cast<const uint32_t*>(descs + s)[i];
+    __syncthreads();
+    const int nb = d.n_bits, tb = d.m_bits + d.n_bits;
+    const unsigned K = 1u << d.k_bits;
+    if ((int)tid < tb) {
+      const int q = (int)tid - nb;
+      xa[tid] = q < 0 ? 0u : 1u << d.a_m[q];
+      xb[tid] = q < 0 ? 1u << d.b_n[tid] : 0u;
+      xc[tid] = q < 0 ? 1u << d.c_n[tid] : 1u << d.c_m[q];
+    } else if (tid >= 64 && tid < 64 + K) {
+      ka[tid - 64] = chain_deposit(tid - 64, d.k_bits, d.a_k);
+      kb[tid - 64] = chain_deposit(tid - 64, d.k_bits, d.b_k);
+    }
     __syncthreads();
     const float2* A = arena + d.off_a;
     const float2* B = arena + d.off_b;
     float2* C = arena + d.off_c;
-    const unsigned long long total = 1ull << (d.m_bits + d.n_bits);
-    const unsigned K = 1u << d.k_bits;
-    for (unsigned long long idx = threadIdx.x; idx < total; idx += blockDim.x) {
-      const unsigned long long n = idx & ((1ull << d.n_bits) - 1ull), m = idx >> d.n_bits;
-      const unsigned long long ao = chain_deposit(m, d.m_bits, d.a_m);
-      const unsigned long long bo = chain_deposit(n, d.n_bits, d.b_n);
-      const unsigned long long co =
-          chain_deposit(m, d.m_bits, d.c_m) | chain_deposit(n, d.n_bits, d.c_n);
-      float sx = 0.f, sy = 0.f;
-      for (unsigned k = 0; k < K; ++k) {
-        const float2 a = A[ao | chain_deposit(k, d.k_bits, d.a_k)];
-        const float2 b = B[bo | chain_deposit(k, d.k_bits, d.b_k)];
-        sx = fmaf(a.x, b.x, sx);
-        sx = fmaf(-a.y, b.y, sx);
-        sy = fmaf(a.x, b.y, sy);
-        sy = fmaf(a.y, b.x, sy);
-      }
-      C[co] = make_float2(sx, sy);
+    const int low = tb < 10 ? tb : 10;
+    if (tid >= (1u << low)) continue;  // fewer outputs than threads
+    uint32_t ao = 0, bo = 0, co = 0;
+    for (int b = 0; b < low; ++b)
+      if ((tid >> b) & 1u) ao |= xa[b], bo |= xb[b], co |= xc[b];
+    const int hi = tb - low;  // index bits walked by this thread
+    if (hi < 2) {
+      chain_point(A, B, C, ao, bo, co, K, ka, kb);
+      if (hi == 1) chain_point(A, B, C, ao ^ xa[low], bo ^ xb[low], co ^ xc[low], K, ka, kb);
+      continue;
+    }
+    const uint32_t a0 = xa[low], b0 = xb[low], c0 = xc[low];
+    const uint32_t a1 = xa[low + 1], b1 = xb[low + 1], c1 = xc[low + 1];
+    const unsigned trips = 1u << (hi - 2);
+    for (unsigned j = 0;;) {
+      chain_point(A, B, C, ao, bo, co, K, ka, kb);
+      chain_point(A, B, C, ao ^ a0, bo ^ b0, co ^ c0, K, ka, kb);
+      chain_point(A, B, C, ao ^ a1, bo ^ b1, co ^ c1, K, ka, kb);
+      chain_point(A, B, C, ao ^ a0 ^ a1, bo ^ b0 ^ b1, co ^ c0 ^ c1, K, ka, kb);
+      if (++j == trips) break;
+      const int f = low + 2 + __ffs(j) - 1;  // Gray code: trip j flips bit ctz(j)
+      ao ^= xa[f], bo ^= xb[f], co ^= xc[f];
     }
   }
 }
