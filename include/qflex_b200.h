@@ -129,6 +129,13 @@ int qfx_dot_accumulate(qfx_ctx* ctx, const qfx_contract_desc* desc,
                        uint64_t slot);
 /* amps[slot] += (complex128) arena[off]  (final tensor already a scalar). */
 int qfx_scalar_accumulate(qfx_ctx* ctx, uint64_t off, uint64_t slot);
+/* Open output indices: the final tensor holds 2^n_bits amplitudes at arena[off ..];
+ * element i is added (complex128) to amplitude slot
+ * `slot + sum_b ((i >> b) & 1) * slot_stride[b]`.  One call replaces the 2^k
+ * projected leaf contractions of the terminal cuts, i.e. the `for i in values`
+ * loop of src/contraction_utils.cpp:300-314 with output_index*|values|+i. */
+int qfx_tensor_accumulate(qfx_ctx* ctx, uint64_t off, int32_t n_bits,
+                          const uint32_t* slot_stride, uint64_t slot);
 
 /* Amplitude table (complex128), replaces std::vector<std::complex<double>>
  * amplitudes (src/evaluate_circuit.cpp:226). */

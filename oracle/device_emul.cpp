@@ -11,6 +11,7 @@
 //                   sum_c A[l,c]*B[c,r] in complex64 with fp32 accumulation;
 //   qfx_permute   = Tensor::reorder (src/tensor.cpp:866-911) as a bit permutation;
 //   qfx_dot_accumulate = _multiply_vv + amplitude += (src/contraction_utils.cpp:352).
+#include <algorithm>
 #include <complex>
 #include <cstring>
 #include <string>
@@ -153,6 +154,28 @@ int qfx_dot_accumulate(qfx_ctx* c, const qfx_contract_desc* d, uint64_t slot) {
 int qfx_scalar_accumulate(qfx_ctx* c, uint64_t off, uint64_t slot) {
   if (off >= c->arena.size() || slot >= c->amps.size()) return fail("qfx_scalar_accumulate: bad argument");
   c->amps[slot] += std::complex<double>(c->arena[off]);
+  c->stats.launches_total++;
+  return QFX_OK;
+}
+int qfx_tensor_accumulate(qfx_ctx* c, uint64_t off, int32_t nb, const uint32_t* stride,
+                          uint64_t slot) {
+  if (c == nullptr || nb < 0 || nb > QFX_MAX_BITS || (nb > 0 && stride == nullptr) ||
+      off + (1ull << nb) > c->arena.size())
+    return fail("qfx_tensor_accumulate: bad argument");
+  std::vector<uint64_t> st(stride, stride + nb);
+  std::sort(st.begin(), st.end());
+  uint64_t reach = 0;
+  for (uint64_t x : st) {
+    if (x == 0 || x <= reach) return fail("qfx_tensor_accumulate: slot strides overlap");
+    reach += x;
+  }
+  if (slot + reach >= c->amps.size())
+    return fail("qfx_tensor_accumulate: slot outside the amplitude table");
+  for (uint64_t i = 0; i < (1ull << nb); ++i) {
+    uint64_t s = slot;
+    for (int b = 0; b < nb; ++b) s += ((i >> b) & 1ull) * stride[b];
+    c->amps[s] += std::complex<double>(c->arena[off + i]);
+  }
   c->stats.launches_total++;
   return QFX_OK;
 }

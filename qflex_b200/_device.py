@@ -16,7 +16,8 @@ DEFAULT_DEVICE_LIB = os.path.join(_HERE, "libqflex_b200.so")
 EXPORTS = (
     "qfx_last_error", "qfx_device_count", "qfx_create", "qfx_destroy", "qfx_sync",
     "qfx_arena_reserve", "qfx_arena_size", "qfx_upload", "qfx_download", "qfx_copy",
-    "qfx_contract", "qfx_dot_accumulate", "qfx_scalar_accumulate", "qfx_amps_reserve",
+    "qfx_contract", "qfx_dot_accumulate", "qfx_scalar_accumulate", "qfx_tensor_accumulate",
+    "qfx_amps_reserve",
     "qfx_amps_download", "qfx_permute", "qfx_timer_start", "qfx_timer_stop_ms",
     "qfx_stats_get", "qfx_stats_reset", "qfx_profile_begin", "qfx_profile_end",
 )
@@ -70,6 +71,7 @@ def load(path=DEFAULT_DEVICE_LIB):
     c.qfx_trim_cache.argtypes = [ctypes.c_int]
     c.qfx_bind_thread.argtypes = [vp]
     c.qfx_scalar_accumulate.argtypes = [vp, u64, u64]
+    c.qfx_tensor_accumulate.argtypes = [vp, u64, i32, ctypes.POINTER(ctypes.c_uint32), u64]
     c.qfx_amps_reserve.argtypes = [vp, u64]
     c.qfx_amps_download.argtypes = [vp, vp, u64]
     c.qfx_permute.argtypes = [vp, u64, u64, i32, vp]
@@ -134,6 +136,13 @@ class Context:
 
     def dot_accumulate(self, desc, slot):
         self._ck(self.c.qfx_dot_accumulate(self.h, ctypes.byref(desc), slot))
+
+    def scalar_accumulate(self, off, slot):
+        self._ck(self.c.qfx_scalar_accumulate(self.h, off, slot))
+
+    def tensor_accumulate(self, off, slot_stride, slot=0):
+        st = (ctypes.c_uint32 * max(1, len(slot_stride)))(*slot_stride)
+        self._ck(self.c.qfx_tensor_accumulate(self.h, off, len(slot_stride), st, slot))
 
     def permute(self, src, dst, dst_pos):
         p = (ctypes.c_int8 * max(1, len(dst_pos)))(*dst_pos)

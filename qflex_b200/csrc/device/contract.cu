@@ -838,6 +838,68 @@ extern "C" int qfx_scalar_accumulate(qfx_ctx* ctx, uint64_t off, uint64_t slot) 
   return QFX_OK;
 }
 
+namespace {
+struct TensorAccArgs {
+  const float2* src;
+  double2* amps;
+  int n_bits;
+  uint32_t stride[QFX_MAX_BITS];
+};
+__global__ void tensor_accumulate_kernel(const __grid_constant__ TensorAccArgs g) {
+  const unsigned long long total = 1ull << g.n_bits;
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+       i < total; i += (unsigned long long)gridDim.x * blockDim.x) {
+    unsigned long long slot = 0;
+    for (int b = 0; b < g.n_bits; ++b) slot += ((i >> b) & 1ull) * g.stride[b];
+    const float2 v = g.src[i];
+    double2 a = g.amps[slot];  // slots of distinct i are distinct (host checks)
+    a.x += (double)v.x;
+    a.y += (double)v.y;
+    g.amps[slot] = a;
+  }
+}
+}  // namespace
+
+extern "C" int qfx_tensor_accumulate(qfx_ctx* ctx, uint64_t off, int32_t n_bits,
+                                     const uint32_t* slot_stride, uint64_t slot) {
+  if (ctx == nullptr || n_bits < 0 || n_bits > QFX_MAX_BITS ||
+      (n_bits > 0 && slot_stride == nullptr) || off + (1ull << n_bits) > ctx->arena_elems) {
+    qfx_set_error("qfx_tensor_accumulate: bad argument");
+    return QFX_ERR_ARG;
+  }
+  // distinct elements must land in distinct slots: with the strides sorted, each one
+  // has to exceed the sum of the smaller ones
+  uint64_t reach = 0;
+  {
+    std::vector<uint64_t> st(slot_stride, slot_stride + n_bits);
+    std::sort(st.begin(), st.end());
+    for (uint64_t x : st) {
+      if (x == 0 || x <= reach) {
+        qfx_set_error("qfx_tensor_accumulate: slot strides overlap");
+        return QFX_ERR_ARG;
+      }
+      reach += x;
+    }
+  }
+  if (slot + reach >= ctx->n_amps) {
+    qfx_set_error("qfx_tensor_accumulate: slot outside the amplitude table");
+    return QFX_ERR_ARG;
+  }
+  TensorAccArgs g{};
+  g.src = ctx->arena + off;
+  g.amps = ctx->amps + slot;
+  g.n_bits = n_bits;
+  for (int b = 0; b < n_bits; ++b) g.stride[b] = slot_stride[b];
+  const unsigned long long total = 1ull << n_bits;
+  const unsigned blocks =
+      (unsigned)std::min<unsigned long long>((total + 255) / 256, 8ull * ctx->sm_count);
+  tensor_accumulate_kernel<<<blocks, 256, 0, ctx->stream>>>(g);
+  QFX_CUDA(cudaGetLastError());
+  ctx->stats.launches_reduce++;
+  ctx->stats.launches_total++;
+  return QFX_OK;
+}
+
 // ---------------------------------------------------------------- chains
 // World-line flattening (reference flatten_grid_of_tensors, src/read_circuit.cpp:
 // 548-689): every grid site multiplies its gate tensors one after the other, a

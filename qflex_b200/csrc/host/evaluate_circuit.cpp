@@ -4,6 +4,8 @@
 // a device plan (plan.h) instead of Tensor::multiply/reorder calls.
 #include "evaluate_circuit.h"
 
+#include <cstdlib>
+
 #include <chrono>
 #include <iostream>
 
@@ -98,7 +100,22 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
     throw ERROR_MSG("Failed to call get_output_states(). Error:\n\t[", err_msg, "]");
   }
 
-  Plan plan = BuildPlan(*input, ordering, final_qubits);
+  // Terminal cuts stay open when that plan exists and fits the memory limit
+  // (QFLEX_OPEN_OUTPUTS=0 keeps the reference's projected leaves); otherwise the
+  // projected plan, whose errors are the ones reported.
+  Plan plan;
+  bool planned = false;
+  const char* open_env = getenv("QFLEX_OPEN_OUTPUTS");
+  if (!final_qubits.empty() && !(open_env && open_env[0] == '0')) {
+    try {
+      plan = BuildPlan(*input, ordering, final_qubits, true);
+      planned = plan.open_outputs > 0 &&
+                (double)plan.arena_elems * sizeof(s_type) <= (double)global::memory_limit;
+    } catch (const std::string&) {
+      planned = false;
+    }
+  }
+  if (!planned) plan = BuildPlan(*input, ordering, final_qubits);
   plan.precision = where.precision;
   for (auto& st : plan.steps) st.desc.precision = where.precision;
   lap("Time spent planning the contraction: ");

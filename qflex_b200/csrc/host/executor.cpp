@@ -2,7 +2,8 @@
 // The recursion mirrors ContractionData::ContractGrid
 // (reference src/contraction_utils.cpp:223-354): steps before a cut run once,
 // everything after it runs once per cut value; a bond cut adds into the same
-// amplitude, a terminal cut selects amplitude output_index*|values|+i.
+// amplitude, a terminal cut selects amplitude output_index*|values|+i (here: slot
+// += i * amp_stride, so that projected and open terminal cuts can mix).
 #include <algorithm>
 #include <chrono>
 #include <cstdlib>
@@ -77,6 +78,12 @@ class Runner {
               "qfx_scalar_accumulate");
         ++leaves_;
         break;
+      case PlanStep::TENSOR_ACCUMULATE:
+        check(qfx_tensor_accumulate(ctx_, resolve(st.scalar_off, st.var_scalar), st.n_bits,
+                                    st.slot_stride, amp_index),
+              "qfx_tensor_accumulate");
+        leaves_ += uint64_t(1) << st.n_bits;
+        break;
       case PlanStep::PERMUTE:
         check(qfx_permute(ctx_, st.src, st.dst, st.n_bits, st.dst_pos), "qfx_permute");
         break;
@@ -92,14 +99,13 @@ class Runner {
     for (; i < steps.size() && steps[i].level == level; ++i) issue(steps[i], amp_index);
     if (level == (int)plan_.cuts.size()) return;
     const PlanCut& cut = plan_.cuts[level];
-    if (cut.terminal) amp_index *= cut.values.size();
     for (std::size_t v = 0; v < cut.values.size(); ++v) {
       const uint64_t next_combo = combo * cut.values.size() + v;
       if (level + 1 == share_levels_ && world_ > 1 &&
           (int)(next_combo % (uint64_t)world_) != rank_)
         continue;
       values_[level] = cut.values[v];
-      walk(steps, i, level + 1, cut.terminal ? amp_index + v : amp_index,
+      walk(steps, i, level + 1, cut.terminal ? amp_index + v * cut.amp_stride : amp_index,
            level < share_levels_ ? next_combo : combo);
     }
   }

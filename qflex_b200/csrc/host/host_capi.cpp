@@ -63,6 +63,7 @@ const char* kind_name(qflex::PlanStep::Kind k) {
     case qflex::PlanStep::CONTRACT: return "contract";
     case qflex::PlanStep::DOT_ACCUMULATE: return "dot";
     case qflex::PlanStep::SCALAR_ACCUMULATE: return "scalar";
+    case qflex::PlanStep::TENSOR_ACCUMULATE: return "amps";
     case qflex::PlanStep::PERMUTE: return "permute";
   }
   return "?";

@@ -344,9 +344,22 @@ struct NeighbourOrder {
 
 }  // namespace
 
+namespace {
+// a terminal cut whose values are the whole range in natural order can stay open
+bool cut_stays_open(const ContractionOperation& op, bool open_outputs) {
+  if (!open_outputs || op.op_type != ContractionOperation::CUT || op.cut.tensors.size() != 1)
+    return false;
+  const auto& v = op.cut.values;
+  if (v.empty()) return true;
+  if (v.size() != 2) return false;  // output indices have dimension 2
+  return v[0] == 0 && v[1] == 1;
+}
+}  // namespace
+
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
-               const std::vector<std::vector<std::size_t>>& final_qubits) {
+               const std::vector<std::vector<std::size_t>>& final_qubits,
+               bool open_outputs) {
   Plan plan;
   plan.flatten_steps.reserve(4096);  // PlanStep is ~300 bytes: avoid regrowth copies
   plan.steps.reserve(512);
@@ -541,7 +554,7 @@ Plan BuildPlan(const QflexInput& input,
           patches[op.merge.target_id].need =
               std::max(patches[op.merge.target_id].need, cur[op.merge.target_id].size());
         }
-      } else {
+      } else if (!cut_stays_open(op, open_outputs)) {
         const std::string index = index_name(op.cut.tensors);
         for (const auto& pos : op.cut.tensors) {
           SymTensor& t = site[pos[0]][pos[1]];
@@ -570,6 +583,13 @@ Plan BuildPlan(const QflexInput& input,
   std::vector<std::vector<char>> site_used(I, std::vector<char>(J, 0));
   int level = 0;
   plan.n_amplitudes = 1;
+  // terminal cuts in ordering order: projected (cut id >= 0) or open (index name)
+  struct Terminal {
+    int cut_id;
+    std::string index;
+    uint64_t count;
+  };
+  std::vector<Terminal> terminals;
   bool last_was_contract = false;
   SymTensor last_tensor;
 
@@ -651,6 +671,7 @@ Plan BuildPlan(const QflexInput& input,
         cut.terminal = (op.cut.tensors.size() == 1);
         cut.values = op.cut.values;
         const int cut_id = (int)plan.cuts.size();
+        const bool stays_open = cut_stays_open(op, open_outputs);
         int width = -1;
         for (const auto& pos : op.cut.tensors) {
           SymTensor& t = site[pos[0]][pos[1]];
@@ -663,8 +684,15 @@ Plan BuildPlan(const QflexInput& input,
                             t.idx.empty() ? std::string("") : t.idx[0].name, "'.]");
           }
           width = t.idx[p].bits;
+          if (stays_open) continue;
           t.var.push_back(VarTerm{cut_id, t.idx[p].pos});
           t.idx.erase(t.idx.begin() + p);
+        }
+        if (stays_open) {
+          terminals.push_back(Terminal{-1, index, uint64_t(1) << width});
+          plan.n_amplitudes <<= width;
+          ++plan.open_outputs;
+          break;
         }
         if (cut.values.empty())
           for (std::size_t v = 0; v < (std::size_t(1) << width); ++v) cut.values.push_back(v);
@@ -672,7 +700,10 @@ Plan BuildPlan(const QflexInput& input,
           if (v >= (std::size_t(1) << width))
             throw ERROR_MSG("Failed to call project(). Error:\n\t[index_value: ", v,
                             " must be contained in [0, ", (std::size_t(1) << width), ").]");
-        if (cut.terminal) plan.n_amplitudes *= cut.values.size();
+        if (cut.terminal) {
+          plan.n_amplitudes *= cut.values.size();
+          terminals.push_back(Terminal{cut_id, index, (uint64_t)cut.values.size()});
+        }
         plan.cuts.push_back(std::move(cut));
         ++level;
         break;
@@ -683,10 +714,44 @@ Plan BuildPlan(const QflexInput& input,
   // the schedule must end in a scalar, which is accumulated into the amplitude
   // of the current output bitstring (src/contraction_utils.cpp:347-352)
   if (ordering.empty()) throw ERROR_MSG("Empty contraction ordering.");
-  if (last_tensor.rank_bits() != 0)
-    throw ERROR_MSG("Contraction did not complete; final tensor is: ",
-                    tensor_to_string(last_tensor));
-  if (last_was_contract) {
+  // amplitude slot = mixed radix over the terminal cuts, first = most significant
+  std::map<std::string, uint64_t> open_stride;
+  {
+    uint64_t stride = 1;
+    for (std::size_t t = terminals.size(); t--;) {
+      if (terminals[t].cut_id >= 0)
+        plan.cuts[terminals[t].cut_id].amp_stride = stride;
+      else
+        open_stride[terminals[t].index] = stride;
+      stride *= terminals[t].count;
+    }
+  }
+  for (const auto& ix : last_tensor.idx)
+    if (!open_stride.count(ix.name))
+      throw ERROR_MSG("Contraction did not complete; final tensor is: ",
+                      tensor_to_string(last_tensor));
+  if (last_tensor.rank_bits() != 0) {
+    // open outputs: the last contraction (if any) stays a CONTRACT that writes the
+    // tensor of amplitudes, one more step adds it into the table
+    if ((int)open_stride.size() * 1 != (int)last_tensor.idx.size() ||
+        last_tensor.rank_bits() > QFX_MAX_BITS)
+      throw ERROR_MSG("Contraction did not complete; final tensor is: ",
+                      tensor_to_string(last_tensor));
+    PlanStep st;
+    st.kind = PlanStep::TENSOR_ACCUMULATE;
+    st.level = level;
+    st.scalar_off = last_tensor.off;
+    st.var_scalar = last_tensor.var;
+    st.n_bits = last_tensor.span_bits;
+    st.label = "accumulate open outputs";
+    for (const auto& ix : last_tensor.idx)
+      for (int b = 0; b < ix.bits; ++b)
+        st.slot_stride[ix.pos + b] = (uint32_t)(open_stride.at(ix.name) << b);
+    if (last_tensor.span_bits != last_tensor.rank_bits())
+      throw ERROR_MSG("Final tensor of open outputs is not dense: ",
+                      tensor_to_string(last_tensor));
+    plan.steps.push_back(std::move(st));
+  } else if (last_was_contract) {
     plan.steps.back().kind = PlanStep::DOT_ACCUMULATE;
   } else {
     PlanStep st;

@@ -79,7 +79,7 @@ struct SymTensor {
 };
 
 struct PlanStep {
-  enum Kind { CONTRACT, DOT_ACCUMULATE, SCALAR_ACCUMULATE, PERMUTE };
+  enum Kind { CONTRACT, DOT_ACCUMULATE, SCALAR_ACCUMULATE, TENSOR_ACCUMULATE, PERMUTE };
   Kind kind = CONTRACT;
   int level = 0;  // number of cuts that precede this step in the ordering
   int chain = -1; // flatten: world-line (grid site) this step belongs to
@@ -89,9 +89,11 @@ struct PlanStep {
   uint64_t src = 0, dst = 0;
   int n_bits = 0;
   int8_t dst_pos[QFX_MAX_BITS] = {0};
-  // SCALAR_ACCUMULATE
+  // SCALAR_ACCUMULATE / TENSOR_ACCUMULATE (n_bits open output bits at scalar_off;
+  // bit b of the element index moves the amplitude slot by slot_stride[b])
   uint64_t scalar_off = 0;
   std::vector<VarTerm> var_scalar;
+  uint32_t slot_stride[QFX_MAX_BITS] = {0};
   // bookkeeping
   double flops = 0, bytes = 0;
   std::string label;
@@ -101,6 +103,10 @@ struct PlanCut {
   std::vector<std::size_t> values;
   bool terminal = false;
   std::string index;
+  // terminal: value number v of this cut moves the amplitude slot by v * amp_stride
+  // (mixed radix over the terminal cuts in ordering order, first = most significant:
+  // output_index * |values| + i of src/contraction_utils.cpp:300-314)
+  uint64_t amp_stride = 0;
 };
 
 struct PlanUpload {
@@ -124,13 +130,24 @@ struct Plan {
   // independent and run as one qfx_contract_chains launch
   bool flatten_parallel = false;
   int n_chains = 0;
+  // terminal cuts kept as open indices of the final tensor (see BuildPlan)
+  int open_outputs = 0;
 };
 
 // Builds the full plan.  `final_qubits` = qubits with a terminal cut
 // (EvaluateCircuit passes get_output_states' list).  Throws std::string.
+//
+// `open_outputs`: a terminal cut over the full value range is not projected value by
+// value (the reference's 2^k leaf contractions per slice, src/contraction_utils.cpp:
+// 300-314); its output index stays open, rides through the remaining expands and
+// merges as one more free bit, and the schedule ends in a tensor of 2^k amplitudes
+// that one TENSOR_ACCUMULATE step adds into the table.  Same amplitudes, same flops,
+// 2^k times fewer launches after the cut, 2^k times larger patches after it -- the
+// caller falls back to the projected plan when that does not fit the memory limit.
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
-               const std::vector<std::vector<std::size_t>>& final_qubits);
+               const std::vector<std::vector<std::size_t>>& final_qubits,
+               bool open_outputs = false);
 
 struct ExecStats {
   double seconds_upload = 0, seconds_flatten = 0, seconds_contract = 0;

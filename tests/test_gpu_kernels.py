@@ -134,6 +134,38 @@ def test_dot_accumulate_complex128(ctx, k):
     assert abs(amps[1] - 2 * want) <= 1e-6 * max(1.0, np.sqrt(n))
 
 
+@pytest.mark.parametrize("nbits", [0, 1, 6, 10, 14])
+def test_tensor_accumulate_open_outputs(ctx, nbits):
+    """qfx_tensor_accumulate: 2^k amplitudes of a final tensor added (complex128) into
+    mixed-radix slots -- bit-exact: every slot receives (double) of one fp32 value."""
+    from qflex_b200 import _device
+    rng = np.random.default_rng(nbits)
+    n = 1 << nbits
+    t = _rand(n, rng)
+    ctx.reserve(n + 64)
+    ctx.upload(7, t)
+    # slot strides: a bit permutation spread over a table 3x as large (gaps = slots of
+    # projected terminal cuts), starting at slot 2
+    perm = [int(x) for x in rng.permutation(nbits)]
+    strides = [3 << p for p in perm]
+    total = 2 + 3 * n + 1
+    ctx.amps_reserve(total)
+    ctx.tensor_accumulate(7, strides, 2)
+    ctx.tensor_accumulate(7, strides, 2)  # accumulates
+    got = ctx.amps(total)
+    want = np.zeros(total, dtype=np.complex128)
+    for i in range(n):
+        slot = 2 + sum(strides[b] for b in range(nbits) if (i >> b) & 1)
+        want[slot] += 2 * np.complex128(t[i])
+    assert np.array_equal(got, want)
+    if nbits >= 2:
+        with pytest.raises(_device.DeviceError, match="overlap"):
+            ctx.tensor_accumulate(7, [1, 2, 3] + [8 << b for b in range(nbits - 3)][:nbits - 3]
+                                  if nbits >= 3 else [1, 1], 0)
+    with pytest.raises(_device.DeviceError, match="outside the amplitude table"):
+        ctx.tensor_accumulate(7, strides, total)
+
+
 @pytest.mark.parametrize("nbits,seed", [(0, 0), (1, 0), (3, 1), (5, 2), (9, 3), (10, 4), (12, 5),
                                         (12, 6), (16, 7), (20, 8), (22, 9)])
 def test_permute_bit_exact(ctx, nbits, seed):

@@ -60,6 +60,38 @@ def test_slices_dealt_to_ranks_sum_to_full_result(emul, golden, world):
     p.close()
 
 
+def test_projected_leaves_match_open_outputs(emul, golden, monkeypatch):
+    """QFLEX_OPEN_OUTPUTS=0 plans the reference's projected leaves (one dot per output
+    bitstring and slice); the default keeps the output indices open.  Same amplitudes."""
+    case = support.CASES["bristlecone_48_1-16-1"]
+    texts = support.case_texts(case)
+    res_open, st_open = emul.evaluate(*texts, memory_limit=8 << 30)
+    monkeypatch.setenv("QFLEX_OPEN_OUTPUTS", "0")
+    p = emul.prepare(*texts, memory_limit=8 << 30)
+    assert [r for r in p.describe() if r["phase"] == "grid"][-1]["kind"] == "dot"
+    p.close()
+    res_proj, st_proj = emul.evaluate(*texts, memory_limit=8 << 30)
+    assert [s for s, _ in res_open] == [s for s, _ in res_proj]
+    a = np.array([v for _, v in res_open]); b = np.array([v for _, v in res_proj])
+    assert support.rel_err(a, b) < 1e-6
+    assert st_open["leaves"] == st_proj["leaves"] == 8
+    assert st_open["launches"] < st_proj["launches"]
+
+
+def test_open_outputs_fall_back_when_memory_is_short(emul):
+    # bristlecone_48 1-24-1: the open plan needs 41.2 MB, the projected one 39.7 MB
+    texts = support.case_texts(support.CASES["bristlecone_48_1-24-1"])
+    last = lambda p: [r for r in p.describe() if r["phase"] == "grid"][-1]["kind"]
+    p = emul.prepare(*texts, memory_limit=64 << 20)
+    assert last(p) == "amps"
+    p.close()
+    p = emul.prepare(*texts, memory_limit=40 * 10 ** 6)
+    assert last(p) == "dot"
+    p.close()
+    with pytest.raises(Exception, match="exceeds memory limit"):
+        emul.prepare(*texts, memory_limit=39 * 10 ** 6)
+
+
 def test_restricting_cut_values_matches_reference_subset(emul, golden):
     # the mechanism bench.py uses to time a fixed subset of slices
     o = support.restrict_cuts("cut () 1 3\ncut (0,1) 5\n", [[1], None])
@@ -71,7 +103,9 @@ def test_plan_describe_and_flop_model(emul):
     p = emul.prepare(*support.case_texts(case), memory_limit=8 << 30)
     rows = p.describe()
     grid = [r for r in rows if r["phase"] == "grid"]
-    assert grid[-1]["kind"] == "dot"
+    # the two terminal cuts stay open: the schedule ends in a 4-amplitude tensor
+    assert grid[-1]["kind"] == "amps" and grid[-2]["kind"] == "contract"
+    grid = grid[:-1]
     assert all(r["kind"] in ("contract", "dot", "scalar") for r in grid)
     # every grid tensor ends in one layout permute or a direct write
     assert any(r["kind"] == "permute" for r in rows if r["phase"] == "flatten")
