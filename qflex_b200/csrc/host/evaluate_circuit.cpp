@@ -4,6 +4,7 @@
 // a device plan (plan.h) instead of Tensor::multiply/reorder calls.
 #include "evaluate_circuit.h"
 
+#include <algorithm>
 #include <cstdlib>
 
 #include <chrono>
@@ -100,19 +101,37 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
     throw ERROR_MSG("Failed to call get_output_states(). Error:\n\t[", err_msg, "]");
   }
 
-  // Terminal cuts stay open when that plan exists and fits the memory limit
-  // (QFLEX_OPEN_OUTPUTS=0 keeps the reference's projected leaves); otherwise the
-  // projected plan, whose errors are the ones reported.
+  // As many terminal cuts as fit the memory limit stay open (counted from the end of
+  // the ordering; the arena grows monotonically with that count, so bisect).
+  // QFLEX_OPEN_OUTPUTS=<n> caps the count, 0 = the reference's projected leaves, whose
+  // plan is also the one whose errors are reported.
   Plan plan;
   bool planned = false;
-  const char* open_env = getenv("QFLEX_OPEN_OUTPUTS");
-  if (!final_qubits.empty() && !(open_env && open_env[0] == '0')) {
+  int max_open = (int)final_qubits.size();
+  if (const char* e = getenv("QFLEX_OPEN_OUTPUTS")) max_open = std::min(max_open, std::max(0, atoi(e)));
+  auto try_open = [&](int n, Plan* out) {
     try {
-      plan = BuildPlan(*input, ordering, final_qubits, true);
-      planned = plan.open_outputs > 0 &&
-                (double)plan.arena_elems * sizeof(s_type) <= (double)global::memory_limit;
+      Plan p = BuildPlan(*input, ordering, final_qubits, n);
+      if (p.open_outputs == 0 ||
+          (double)p.arena_elems * sizeof(s_type) > (double)global::memory_limit)
+        return false;
+      *out = std::move(p);
+      return true;
     } catch (const std::string&) {
-      planned = false;
+      return false;
+    }
+  };
+  if (max_open > 0) {
+    planned = try_open(max_open, &plan);
+    if (!planned) {
+      int lo = 0, hi = max_open;  // lo fits (0 = projected), hi does not
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) / 2;
+        if (try_open(mid, &plan)) lo = mid, planned = true;
+        else hi = mid;
+      }
+      // `plan` holds the last fitting try only if that was `lo`
+      if (planned && plan.open_outputs != lo) planned = try_open(lo, &plan);
     }
   }
   if (!planned) plan = BuildPlan(*input, ordering, final_qubits);

@@ -346,9 +346,8 @@ struct NeighbourOrder {
 
 namespace {
 // a terminal cut whose values are the whole range in natural order can stay open
-bool cut_stays_open(const ContractionOperation& op, bool open_outputs) {
-  if (!open_outputs || op.op_type != ContractionOperation::CUT || op.cut.tensors.size() != 1)
-    return false;
+bool cut_can_open(const ContractionOperation& op) {
+  if (op.op_type != ContractionOperation::CUT || op.cut.tensors.size() != 1) return false;
   const auto& v = op.cut.values;
   if (v.empty()) return true;
   if (v.size() != 2) return false;  // output indices have dimension 2
@@ -359,8 +358,21 @@ bool cut_stays_open(const ContractionOperation& op, bool open_outputs) {
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               bool open_outputs) {
+               int open_outputs) {
   Plan plan;
+  // the LAST `open_outputs` openable terminal cuts of the ordering stay open (a later
+  // cut enlarges fewer of the remaining patches)
+  std::vector<const ContractionOperation*> open_ops;
+  {
+    std::vector<const ContractionOperation*> can;
+    for (const auto& op : ordering)
+      if (cut_can_open(op)) can.push_back(&op);
+    const std::size_t n = std::min<std::size_t>(can.size(), (std::size_t)std::max(open_outputs, 0));
+    open_ops.assign(can.end() - n, can.end());
+  }
+  auto cut_stays_open = [&](const ContractionOperation& op, int) {
+    return std::find(open_ops.begin(), open_ops.end(), &op) != open_ops.end();
+  };
   plan.flatten_steps.reserve(4096);  // PlanStep is ~300 bytes: avoid regrowth copies
   plan.steps.reserve(512);
   const std::size_t I = input.grid.I, J = input.grid.J;

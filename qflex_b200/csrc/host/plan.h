@@ -137,17 +137,19 @@ struct Plan {
 // Builds the full plan.  `final_qubits` = qubits with a terminal cut
 // (EvaluateCircuit passes get_output_states' list).  Throws std::string.
 //
-// `open_outputs`: a terminal cut over the full value range is not projected value by
+// `open_outputs` = how many terminal cuts (counted from the end of the ordering) stay
+// open: such a cut, when it runs over the full value range, is not projected value by
 // value (the reference's 2^k leaf contractions per slice, src/contraction_utils.cpp:
 // 300-314); its output index stays open, rides through the remaining expands and
 // merges as one more free bit, and the schedule ends in a tensor of 2^k amplitudes
 // that one TENSOR_ACCUMULATE step adds into the table.  Same amplitudes, same flops,
 // 2^k times fewer launches after the cut, 2^k times larger patches after it -- the
-// caller falls back to the projected plan when that does not fit the memory limit.
+// caller opens fewer cuts (down to none: the reference's plan) when that does not fit
+// the memory limit.
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               bool open_outputs = false);
+               int open_outputs = 0);
 
 struct ExecStats {
   double seconds_upload = 0, seconds_flatten = 0, seconds_contract = 0;
