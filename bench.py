@@ -204,8 +204,8 @@ _FLOPS_CACHE = {}
 
 
 def plan_flops(w, cut_values):
-    """Algorithmic flops of one pass over the slices `cut_values` selects = sum over
-    the schedule of 8*M*N*K x (how often the step runs: the product of the value
+    """Algorithmic flops of one pass of the REFERENCE's schedule over the slices
+    `cut_values` selects = sum over the schedule of 8*M*N*K x (how often the step runs: the product of the value
     counts of the cuts that precede it).  Planner's symbolic replay; the plan is only
     described, not contracted."""
     import re
@@ -221,11 +221,21 @@ def plan_flops(w, cut_values):
                 if not vals:
                     raise ValueError("bench workloads must give every cut an explicit value list")
                 fan.append(len(vals))
+        # the reference contracts projected leaves (one per output bitstring): count
+        # the flops of THAT plan, not of the open-output plan the engine itself runs
+        saved = os.environ.get("QFLEX_OPEN_OUTPUTS")
+        os.environ["QFLEX_OPEN_OUTPUTS"] = "0"
         try:
-            p = qflex_b200.default_library().prepare(c, o, g, memory_limit=w["memory"])
-        except qflex_b200.QflexError:
-            from tests import support
-            p = support.emulated_host_library().prepare(c, o, g, memory_limit=w["memory"])
+            try:
+                p = qflex_b200.default_library().prepare(c, o, g, memory_limit=w["memory"])
+            except qflex_b200.QflexError:
+                from tests import support
+                p = support.emulated_host_library().prepare(c, o, g, memory_limit=w["memory"])
+        finally:
+            if saved is None:
+                del os.environ["QFLEX_OPEN_OUTPUTS"]
+            else:
+                os.environ["QFLEX_OPEN_OUTPUTS"] = saved
         total = 0.0
         for r in p.describe():
             if r["phase"] == "grid" and r["kind"] in ("contract", "dot"):
