@@ -489,6 +489,130 @@ __global__ void __launch_bounds__(kDotThreads)
   }
 }
 
+// ---------------------------------------------------------------- gemv_rows
+// out[m] = sum_k A[m,k] * B[k] with 2..64 outputs and a long K, A dense: the tail of a
+// schedule whose output indices stayed open (the last merge yields all 2^k amplitudes).
+// dotk runs one block per output and walks A with the output bits fixed -- when those
+// bits sit low in A's address every block touches 8 bytes out of each 32-byte sector.
+// Here A is read ONCE, linearly, with 16-byte loads: address bit 0 = the two halves of a
+// load, bits 1..8 = the thread, higher bits = the block (bits that are output bits, and
+// the K split) or walked in Gray-code order; a (thread, half) pair therefore always
+// feeds the same output and needs one accumulator.  B (2^k elements) comes from L1/L2.
+struct GemvArgs {
+  const float2* A;
+  const float2* B;
+  double2* ws;                   // [outputs][splits]
+  int m_bits, ks_bits;
+  int n_hm, n_hk;                // output / k bits at A address positions >= kGemvLow
+  int8_t kind[16];               // A address bit p < kGemvLow: k index, or -(m index) - 1
+  int8_t hm_pos[8], hm_idx[8];   // high output bits: A address position, m index
+  int8_t hk_pos[32], hk_bk[32];  // high k bits, ascending A position: A / B position
+  int8_t b_k[QFX_MAX_BITS];
+};
+constexpr int kGemvLow = 9;
+
+__global__ void __launch_bounds__(256) gemv_rows(const __grid_constant__ GemvArgs g) {
+  __shared__ double2 part[512];
+  __shared__ uint8_t part_m[512];
+  const unsigned tid = threadIdx.x;
+  unsigned mlow[2] = {0u, 0u};
+  unsigned long long offB[2] = {0ull, 0ull};
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    const unsigned j = (tid << 1) | e;
+    for (int p = 0; p < kGemvLow; ++p)
+      if ((j >> p) & 1u) {
+        const int kd = g.kind[p];
+        if (kd >= 0) offB[e] |= 1ull << g.b_k[kd];
+        else mlow[e] |= 1u << (-kd - 1);
+      }
+  }
+  unsigned long long offA = (unsigned long long)tid << 1, offBc = 0;
+  unsigned mhigh = 0;
+  for (int q = 0; q < g.n_hm; ++q)
+    if ((blockIdx.x >> q) & 1u) {
+      offA |= 1ull << g.hm_pos[q];
+      mhigh |= 1u << g.hm_idx[q];
+    }
+  const int walk_bits = g.n_hk - g.ks_bits;
+  for (int q = 0; q < g.ks_bits; ++q)
+    if ((blockIdx.y >> q) & 1u) {
+      offA |= 1ull << g.hk_pos[walk_bits + q];
+      offBc |= 1ull << g.hk_bk[walk_bits + q];
+    }
+  const unsigned nch = 1u << walk_bits;
+  const float2* __restrict__ A = g.A;
+  const float2* __restrict__ B = g.B;
+  double s0x = 0.0, s0y = 0.0, s1x = 0.0, s1y = 0.0;
+  for (unsigned c = 0; c < nch; c += 4) {
+    unsigned long long oa[4], ob[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      oa[u] = offA;
+      ob[u] = offBc;
+      const unsigned nxt = c + u + 1;
+      if (nxt < nch) {
+        const int bit = __ffs(nxt) - 1;  // Gray code: step i flips bit ctz(i)
+        offA ^= 1ull << g.hk_pos[bit];
+        offBc ^= 1ull << g.hk_bk[bit];
+      }
+    }
+    float4 a[4];
+    float2 b0[4], b1[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (c + u < nch) {
+        a[u] = __ldg(reinterpret_cast<const float4*>(A + oa[u]));
+        b0[u] = __ldg(B + (ob[u] | offB[0]));
+        b1[u] = __ldg(B + (ob[u] | offB[1]));
+      }
+    float p0x = 0.f, p0y = 0.f, p1x = 0.f, p1y = 0.f;  // short fp32 sums, then fp64
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (c + u < nch) {
+        p0x = fmaf(a[u].x, b0[u].x, p0x);
+        p0x = fmaf(-a[u].y, b0[u].y, p0x);
+        p0y = fmaf(a[u].x, b0[u].y, p0y);
+        p0y = fmaf(a[u].y, b0[u].x, p0y);
+        p1x = fmaf(a[u].z, b1[u].x, p1x);
+        p1x = fmaf(-a[u].w, b1[u].y, p1x);
+        p1y = fmaf(a[u].z, b1[u].y, p1y);
+        p1y = fmaf(a[u].w, b1[u].x, p1y);
+      }
+    s0x += (double)p0x;
+    s0y += (double)p0y;
+    s1x += (double)p1x;
+    s1y += (double)p1y;
+  }
+  part[(tid << 1)] = make_double2(s0x, s0y);
+  part[(tid << 1) | 1] = make_double2(s1x, s1y);
+  part_m[(tid << 1)] = (uint8_t)mlow[0];
+  part_m[(tid << 1) | 1] = (uint8_t)mlow[1];
+  __syncthreads();
+  // outputs of this block: every value of the low output bits; one warp per output,
+  // lanes stride over the 512 partials in a fixed order (deterministic)
+  unsigned low_mask = 0;
+  for (int p = 0; p < kGemvLow; ++p)
+    if (g.kind[p] < 0) low_mask |= 1u << (-g.kind[p] - 1);
+  const unsigned warp = tid >> 5, lane = tid & 31;
+  for (unsigned m = warp; m < (1u << g.m_bits); m += 8) {
+    if ((m & ~low_mask) != 0) continue;  // enumerate the subsets of low_mask only
+    double sx = 0.0, sy = 0.0;
+    for (unsigned j = lane; j < 512; j += 32)
+      if (part_m[j] == m) {
+        sx += part[j].x;
+        sy += part[j].y;
+      }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      sx += __shfl_xor_sync(0xffffffffu, sx, o);
+      sy += __shfl_xor_sync(0xffffffffu, sy, o);
+    }
+    if (lane == 0)
+      g.ws[((unsigned long long)(m | mhigh) << g.ks_bits) + blockIdx.y] = make_double2(sx, sy);
+  }
+}
+
 // One warp per output: lanes stride over the split partials, then a shuffle tree
 // (fixed order: deterministic).  A single thread walking 1024 partials took 140 us,
 // three times the dot product itself.
@@ -582,6 +706,15 @@ uint64_t operand_mask(const int8_t* p1, int n1, const int8_t* p2, int n2) {
     seen |= 1ull << p2[i];
   }
   return seen;
+}
+
+// the streamed operand of the GEMV path: its m and k bits fill 0 .. m+k-1
+bool mask_a_dense(const qfx_contract_desc& d) {
+  uint64_t seen = 0;
+  for (int i = 0; i < d.m_bits; ++i) seen |= 1ull << d.a_m[i];
+  for (int i = 0; i < d.k_bits; ++i) seen |= 1ull << d.a_k[i];
+  const int bits = d.m_bits + d.k_bits;
+  return bits <= 32 && seen == (bits == 64 ? ~0ull : (1ull << bits) - 1ull);
 }
 
 }  // namespace
@@ -684,6 +817,53 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     rc = qfx_launch_contract_tc_fused(ctx, d, A, B, C, &done);
     if (rc || done) return rc;
     if (d.n_bits >= 5 && d.k_bits >= 5) return qfx_launch_contract_tc(ctx, d, A, B, C);
+  }
+
+  // ---------------- a few outputs on one side, long K, dense big operand: linear GEMV
+  if (!accumulate_amp && d.n_bits == 0 && d.m_bits >= 1 && d.m_bits <= 6 && d.k_bits >= 10 &&
+      mask_a_dense(d) && !(d.off_a & 1) && getenv("QFLEX_NO_GEMV") == nullptr) {
+    GemvArgs g{};
+    g.A = A;
+    g.B = B;
+    g.m_bits = d.m_bits;
+    memcpy(g.b_k, d.b_k, QFX_MAX_BITS);
+    const int bits = d.m_bits + d.k_bits;
+    std::vector<int> owner(bits, 0);  // per A address bit: k index or -(m index) - 1
+    for (int i = 0; i < d.k_bits; ++i) owner[d.a_k[i]] = i;
+    for (int i = 0; i < d.m_bits; ++i) owner[d.a_m[i]] = -i - 1;
+    for (int p = 0; p < kGemvLow; ++p) g.kind[p] = (int8_t)owner[p];
+    for (int p = kGemvLow; p < bits; ++p) {
+      if (owner[p] >= 0) {
+        g.hk_pos[g.n_hk] = (int8_t)p;
+        g.hk_bk[g.n_hk] = d.b_k[owner[p]];
+        ++g.n_hk;
+      } else {
+        g.hm_pos[g.n_hm] = (int8_t)p;
+        g.hm_idx[g.n_hm] = (int8_t)(-owner[p] - 1);
+        ++g.n_hm;
+      }
+    }
+    int ks = 0;
+    while (ks < g.n_hk - 4 && (1ll << (g.n_hm + ks)) < 8ll * ctx->sm_count) ++ks;
+    g.ks_bits = ks;
+    int rc = qfx_ensure_ws(ctx, sizeof(double2) << (d.m_bits + ks));
+    if (rc) return rc;
+    g.ws = reinterpret_cast<double2*>(ctx->ws);
+    dim3 grid(1u << g.n_hm, 1u << ks);
+    gemv_rows<<<grid, 256, 0, ctx->stream>>>(g);
+    QFX_CUDA(cudaGetLastError());
+    DotArgs f{};
+    f.C = C;
+    f.ws = g.ws;
+    f.m_bits = d.m_bits;
+    f.ks_bits = ks;
+    memcpy(f.c_m, d.c_m, QFX_MAX_BITS);
+    const unsigned outs = 1u << d.m_bits;
+    dotk_finish<<<(outs * 32 + 127) / 128, 128, 0, ctx->stream>>>(f);
+    QFX_CUDA(cudaGetLastError());
+    ctx->stats.launches_reduce += 2;
+    ctx->stats.launches_total += 2;
+    return QFX_OK;
   }
 
   // ---------------- tiny outputs: block reduction over K

@@ -30,6 +30,27 @@ def test_amplitudes_match_reference_golden(gpu_lib, golden, name):
     assert stats["launches"] > 0
 
 
+@pytest.mark.parametrize("name,n_open", [("bristlecone_48_1-24-1", 0), ("sycamore_53_8_64amps", 0),
+                                         ("sycamore_53_8_2slices_64amps", 3),
+                                         ("rect7x7_1-32-1_4amps", 1)])
+def test_projected_and_partly_open_outputs_match_golden(gpu_lib, golden, monkeypatch, name, n_open):
+    """The default keeps every terminal cut open; QFLEX_OPEN_OUTPUTS=0 is the
+    reference's schedule (one projected leaf per bitstring), n > 0 a mix of both."""
+    monkeypatch.setenv("QFLEX_OPEN_OUTPUTS", str(n_open))
+    case = support.CASES[name]
+    c, o, g = support.case_texts(case)
+    res, stats = gpu_lib.evaluate(c, o, g, case.get("initial", ""), case.get("final", ""),
+                                  memory_limit=64 << 30)
+    states, want = _amps(golden, name)
+    assert [s for s, _ in res] == states
+    assert support.rel_err([a for _, a in res], want) < TOL
+    monkeypatch.delenv("QFLEX_OPEN_OUTPUTS")
+    res2, stats2 = gpu_lib.evaluate(c, o, g, case.get("initial", ""), case.get("final", ""),
+                                    memory_limit=64 << 30)
+    assert stats2["launches"] < stats["launches"] and stats2["leaves"] == stats["leaves"]
+    assert support.rel_err([a for _, a in res2], [a for _, a in res]) < TOL
+
+
 @pytest.mark.parametrize("precision", ["ffma"])
 def test_precision_modes_agree(gpu_lib, golden, precision):
     case = support.CASES["bristlecone_48_1-24-1"]

@@ -66,6 +66,24 @@ def test_contract_random_bit_placement(ctx, m, n, k):
     assert _run_contract(ctx, t, rng) < TOL
 
 
+@pytest.mark.parametrize("outs,k,seed", [(1, 10, 0), (1, 17, 1), (2, 12, 2), (3, 15, 3), (5, 14, 4),
+                                         (6, 16, 5), (6, 10, 6), (4, 20, 7), (5, 13, 8)])
+@pytest.mark.parametrize("side", ["a", "b"])
+def test_contract_few_outputs_long_k_gemv(ctx, outs, k, seed, side):
+    """The tail of an open-output schedule: 2..64 outputs all on one operand, long K,
+    output bits anywhere inside the big operand (gemv_rows reads it once, linearly)."""
+    rng = np.random.default_rng(4000 + seed)
+    t = _random_tables(rng, outs, 0, k) if side == "a" else _random_tables(rng, 0, outs, k)
+    assert _run_contract(ctx, t, rng) < TOL
+    # output bits lowest / highest in the big operand's address
+    big, free = ("a_m", "a_k") if side == "a" else ("b_n", "b_k")
+    for lowest in (True, False):
+        t2 = dict(t)
+        t2[big] = list(range(outs)) if lowest else list(range(k, k + outs))
+        t2[free] = list(range(outs, outs + k)) if lowest else list(range(k))
+        assert _run_contract(ctx, t2, rng) < TOL
+
+
 @pytest.mark.parametrize("m,n,k", [(8, 6, 6), (12, 3, 3), (9, 7, 5), (0, 0, 10)])
 def test_contract_odd_base_offsets(ctx, m, n, k):
     # cut projections shift operand bases; odd bases disable 16-byte accesses

@@ -76,6 +76,14 @@ def test_projected_leaves_match_open_outputs(emul, golden, monkeypatch):
     assert support.rel_err(a, b) < 1e-6
     assert st_open["leaves"] == st_proj["leaves"] == 8
     assert st_open["launches"] < st_proj["launches"]
+    # one of the two terminal cuts open, the other projected: slots still line up
+    monkeypatch.setenv("QFLEX_OPEN_OUTPUTS", "1")
+    res_mix, st_mix = emul.evaluate(*texts, memory_limit=8 << 30)
+    assert [s for s, _ in res_mix] == [s for s, _ in res_proj]
+    assert support.rel_err(np.array([v for _, v in res_mix]), b) < 1e-6
+    assert st_open["launches"] < st_mix["launches"] < st_proj["launches"]
+    _, want = _amps(golden, "bristlecone_48_1-16-1")
+    assert support.rel_err(np.array([v for _, v in res_mix]), want) < TOL
 
 
 def test_open_outputs_fall_back_when_memory_is_short(emul):

@@ -23,6 +23,10 @@ def layout(m, n, k, mode):
         hi = pos[min(4, m) + h + mid - h: min(4, m) + h + mid - h + (k - h)]
         a_k = lo + hi
         a_m = [p for p in pos if p not in a_k]
+    if os.environ.get("QFLEX_KB_MLOW"):  # output bits lowest in A (open-output tails)
+        a_m = list(range(m)); a_k = list(range(m, m + k))
+    elif os.environ.get("QFLEX_KB_MMID"):  # output bits in the middle of A's address
+        a_m = list(range(6, 6 + m)); a_k = list(range(6)) + list(range(6 + m, m + k))
     b_n = list(range(n)); b_k = list(range(n, n + k))
     c_n = list(range(n)); c_m = list(range(n, n + m))
     if os.environ.get("QFLEX_KB_CT"):  # C transposed: m lowest (what a role swap produces)
@@ -39,7 +43,7 @@ def main():
     rng = np.random.default_rng(0)
     out = []
     for (m, n, k) in shapes:
-        for mode in ("gemm", "mixed"):
+        for mode in (("gemm",) if (n == 0 or m == 0) else ("gemm", "mixed")):
             a_m, c_m, b_n, c_n, a_k, b_k = layout(m, n, k, mode)
             sa, sb, sc = 1 << (m + k), 1 << (n + k), 1 << (m + n)
             ctx.reserve(sa + sb + sc + 128)
