@@ -131,3 +131,23 @@ def test_statevector_cases_on_gpu(gpu_lib):
         res, _ = gpu_lib.evaluate(fix["circuit_test_fsim"], fix["ordering_2x2_test"],
                                   fix["grid_2x2_test"], "", final)
         assert abs(res[0][1] - psi4[x]) < 1e-6
+
+
+def test_7x7_depth_40_tensor_core_and_ffma_paths_agree(gpu_lib):
+    """BASELINE configs[3] as named (7x7, depth 1-40-1): 64 GB arena, 2^15 x 2^15 x 2^15
+    complex merges.  The reference needs 72 GB of host memory and hours per slice, so
+    there is no golden; the split-bf16 tensor-core path is checked against the
+    independent FFMA kernels on one slice and two output bitstrings (same tolerance)."""
+    import torch
+    if torch.cuda.mem_get_info(0)[0] < (80 << 30):
+        pytest.skip("needs 80 GB of free device memory")
+    texts = support.case_texts(dict(
+        circuit="rectangular_7x7_1-40-1_0.txt", ordering="rectangular_7x7_v2.txt",
+        grid="rectangular_7x7.txt", cut_values=[[0], [0]] + [[0]] * 5 + [[0, 1]]))
+    tc, st_tc = gpu_lib.evaluate(*texts, memory_limit=70 << 30)
+    ff, st_ff = gpu_lib.evaluate(*texts, memory_limit=70 << 30, precision="ffma")
+    assert [s for s, _ in tc] == [s for s, _ in ff] and len(tc) == 2
+    assert st_tc["launches_gemm_tc"] > 0 and st_ff["launches_gemm_tc"] == 0
+    a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
+    assert np.linalg.norm(b) > 0
+    assert support.rel_err(a, b) < TOL
