@@ -49,6 +49,13 @@ WORKLOADS = {
         circuit="sycamore_53_10_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1, 2, 3], [0, 1, 2, 3], [0, 1, 2, 3]]},
         reference_sample=[[0], [0], [0]], memory=100 << 30, total_slices=16384),
+    # one step up from the m=10 stand-in: Sycamore-53 m=12 (29.6 GB arena here, 7.1e14
+    # flop per slice; the reference cannot hold its patches in this host's memory), 8
+    # of its slices, strong scaling
+    "sycamore_53_12": dict(
+        circuit="sycamore_53_12_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+        scaling="strong", cuts={"all": [[0, 1], [0, 1], [0, 1]]},
+        reference_sample=None, memory=100 << 30, total_slices=None),
     # BASELINE configs[2] at m=8: 64 slices x a batch of 64 output bitstrings, strong scaling
     "sycamore_53_8_batch64": dict(
         circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
@@ -447,7 +454,8 @@ def main():
         "slices_per_s": total_leaves / wall,
         # amplitudes/s of the FULL circuit at this rate: every output bitstring needs all
         # of the circuit's bond-cut slices
-        "amplitudes_per_s_full_circuit": total_leaves / wall / float(w["total_slices"]),
+        "amplitudes_per_s_full_circuit": (total_leaves / wall / float(w["total_slices"])
+                                          if w.get("total_slices") else None),
         "device_ms_per_step_rank0": dev_ms / args.steps,
         "e2e": {"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 16 * n_amps, "steps": e2e_steps,

@@ -151,3 +151,21 @@ def test_7x7_depth_40_tensor_core_and_ffma_paths_agree(gpu_lib):
     a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
     assert np.linalg.norm(b) > 0
     assert support.rel_err(a, b) < TOL
+
+
+def test_sycamore_m12_tensor_core_and_ffma_paths_agree(gpu_lib):
+    """Sycamore-53 m=12, one slice (29.6 GB arena, 7.1e14 flop): beyond what the
+    reference can hold on this host, so the tensor-core path is checked against the
+    FFMA kernels."""
+    import torch
+    if torch.cuda.mem_get_info(0)[0] < (40 << 30):
+        pytest.skip("needs 40 GB of free device memory")
+    texts = support.case_texts(dict(
+        circuit="sycamore_53_12_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+        cut_values=[[0], [0], [0]] + [[0]] * 5 + [[0, 1]]))
+    tc, st_tc = gpu_lib.evaluate(*texts, memory_limit=60 << 30)
+    ff, st_ff = gpu_lib.evaluate(*texts, memory_limit=60 << 30, precision="ffma")
+    assert len(tc) == 2 and st_tc["launches_gemm_tc"] > 0 and st_ff["launches_gemm_tc"] == 0
+    a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
+    assert np.linalg.norm(b) > 0
+    assert support.rel_err(a, b) < TOL
