@@ -56,6 +56,15 @@ WORKLOADS = {
         circuit="sycamore_53_12_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1], [0, 1], [0, 1]]},
         reference_sample=None, memory=100 << 30, total_slices=None),
+    # BASELINE configs[2] as named: Sycamore-53 m=14.  The shipped 3-cut ordering needs
+    # a 2^44-element patch; config/ordering/sycamore_53_m14.txt = that ordering plus the
+    # six bond cuts tools/augment_ordering.py adds for a 2^30 limit (largest tensor
+    # 2^28, 2.45e14 flop per slice, 2^58 slices, 81 GB arena: the flattened grid
+    # tensors).  8 slices x 64 output bitstrings, strong scaling.
+    "sycamore_53_14": dict(
+        circuit="sycamore_53_14_0.txt", ordering="sycamore_53_m14.txt", grid="sycamore_53.txt",
+        scaling="strong", cuts={"all": [[0, 1]] * 3 + [[0]] * 6 + [[0, 1]] * 6},
+        reference_sample=None, memory=160 << 30, total_slices=2.0 ** 58),
     # BASELINE configs[2] at m=8: 64 slices x a batch of 64 output bitstrings, strong scaling
     "sycamore_53_8_batch64": dict(
         circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",

@@ -169,3 +169,20 @@ def test_sycamore_m12_tensor_core_and_ffma_paths_agree(gpu_lib):
     a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
     assert np.linalg.norm(b) > 0
     assert support.rel_err(a, b) < TOL
+
+
+def test_sycamore_m14_with_augmented_ordering(gpu_lib):
+    """BASELINE configs[2] as named (m=14): runs with the cut-augmented ordering
+    (tools/augment_ordering.py); tensor-core path against FFMA on one slice."""
+    import torch
+    if torch.cuda.mem_get_info(0)[0] < (100 << 30):
+        pytest.skip("needs 100 GB of free device memory")
+    texts = support.case_texts(dict(
+        circuit="sycamore_53_14_0.txt", ordering="sycamore_53_m14.txt", grid="sycamore_53.txt",
+        cut_values=[[0]] * 9 + [[0]] * 5 + [[0, 1]]))
+    tc, st_tc = gpu_lib.evaluate(*texts, memory_limit=120 << 30)
+    ff, st_ff = gpu_lib.evaluate(*texts, memory_limit=120 << 30, precision="ffma")
+    assert len(tc) == 2 and st_tc["launches_gemm_tc"] > 0 and st_ff["launches_gemm_tc"] == 0
+    a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
+    assert np.linalg.norm(b) > 0
+    assert support.rel_err(a, b) < TOL

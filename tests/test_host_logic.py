@@ -199,3 +199,32 @@ def test_kernels_are_sm100a_sass():
     if out.returncode != 0:
         pytest.skip("cuobjdump unavailable")
     assert "sm_100a" in out.stdout
+
+
+def test_augmented_ordering_keeps_the_amplitudes(emul, golden):
+    """tools/augment_ordering.py: bond cuts added until every intermediate fits; the
+    planner's sizes agree with the tool's graph replay and the amplitudes (sums over
+    the extra slices) do not move."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "augment_ordering", os.path.join(support.ROOT, "tools", "augment_ordering.py"))
+    tool = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(tool)
+    case = support.CASES["bristlecone_48_1-16-1"]
+    c, o, g = support.case_texts(case)
+    same, info0 = tool.augment(c, g, o, 60)
+    assert info0["added"] == [] and info0["max_log2"] == 14
+    assert [l for l in same.splitlines() if l.strip()] == [l for l in o.splitlines() if l.strip()]
+    o2, info = tool.augment(c, g, o, 12)
+    assert info["added"] and info["max_log2"] <= 12
+    res, st = emul.evaluate(c, o2, g, memory_limit=8 << 30)
+    states, want = _amps(golden, "bristlecone_48_1-16-1")
+    assert [s for s, _ in res] == states
+    assert support.rel_err(np.array([v for _, v in res]), want) < TOL
+    res0, st0 = emul.evaluate(c, o, g, memory_limit=8 << 30)
+    assert st["leaves"] == 4 * st0["leaves"]  # the cut bond has dimension 4
+    # the tool's flop count per slice is the planner's
+    p = emul.prepare(c, o, g, memory_limit=8 << 30)
+    p.contract()
+    assert abs(p.stats["flops_per_pass"] - info0["flops_per_slice"]) < 0.05 * info0["flops_per_slice"]  # the tool ignores output indices
+    p.close()
