@@ -65,6 +65,16 @@ WORKLOADS = {
         circuit="sycamore_53_14_0.txt", ordering="sycamore_53_m14.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1]] * 3 + [[0]] * 6 + [[0, 1]] * 6},
         reference_sample=None, memory=160 << 30, total_slices=2.0 ** 58),
+    # BASELINE configs[4] as named: Sycamore-53 m=20, heavily sliced.  Its grid tensors
+    # (four bonds of 2^10) are not representable; config/ordering/sycamore_53_m20.txt =
+    # the shipped ordering + 36 bond cuts (tools/augment_ordering.py --max-log2 30
+    # --extra 14: largest tensor 2^30, 2^390 slices) and the planner's cut-aware
+    # flatten projects them in the gate tensors (120 GB arena).  8 of the slices x 64
+    # output bitstrings, strong scaling.
+    "sycamore_53_20": dict(
+        circuit="sycamore_53_20_0.txt", ordering="sycamore_53_m20.txt", grid="sycamore_53.txt",
+        scaling="strong", cuts={"all": [[0, 1]] * 3 + [[0]] * 36 + [[0, 1]] * 6},
+        reference_sample=None, memory=170 << 30, total_slices=2.0 ** 390),
     # BASELINE configs[2] at m=8: 64 slices x a batch of 64 output bitstrings, strong scaling
     "sycamore_53_8_batch64": dict(
         circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",

@@ -105,36 +105,66 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
   // the ordering; the arena grows monotonically with that count, so bisect).
   // QFLEX_OPEN_OUTPUTS=<n> caps the count, 0 = the reference's projected leaves, whose
   // plan is also the one whose errors are reported.
+  // When that plan cannot be built or does not fit (grid tensors next to cut bonds too
+  // large), the same once more with the cut-aware flatten (BuildPlan, plan.h);
+  // QFLEX_CUT_AWARE_FLATTEN=1 forces it, =0 forbids it.
   Plan plan;
-  bool planned = false;
   int max_open = (int)final_qubits.size();
   if (const char* e = getenv("QFLEX_OPEN_OUTPUTS")) max_open = std::min(max_open, std::max(0, atoi(e)));
-  auto try_open = [&](int n, Plan* out) {
-    try {
-      Plan p = BuildPlan(*input, ordering, final_qubits, n);
-      if (p.open_outputs == 0 ||
-          (double)p.arena_elems * sizeof(s_type) > (double)global::memory_limit)
-        return false;
-      *out = std::move(p);
-      return true;
-    } catch (const std::string&) {
-      return false;
-    }
+  const auto fits = [&](const Plan& p) {
+    return (double)p.arena_elems * sizeof(s_type) <= (double)global::memory_limit;
   };
-  if (max_open > 0) {
-    planned = try_open(max_open, &plan);
-    if (!planned) {
-      int lo = 0, hi = max_open;  // lo fits (0 = projected), hi does not
-      while (hi - lo > 1) {
-        const int mid = (lo + hi) / 2;
-        if (try_open(mid, &plan)) lo = mid, planned = true;
-        else hi = mid;
+  auto plan_with = [&](bool cut_aware, Plan* result) {
+    bool planned = false;
+    auto try_open = [&](int n) {
+      try {
+        Plan p = BuildPlan(*input, ordering, final_qubits, n, cut_aware);
+        if (p.open_outputs == 0 || !fits(p)) return false;
+        *result = std::move(p);
+        return true;
+      } catch (const std::string&) {
+        return false;
       }
-      // `plan` holds the last fitting try only if that was `lo`
-      if (planned && plan.open_outputs != lo) planned = try_open(lo, &plan);
+    };
+    if (max_open > 0) {
+      planned = try_open(max_open);
+      if (!planned) {
+        int lo = 0, hi = max_open;  // lo fits (0 = projected), hi does not
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) / 2;
+          if (try_open(mid)) lo = mid, planned = true;
+          else hi = mid;
+        }
+      }
     }
+    if (!planned) *result = BuildPlan(*input, ordering, final_qubits, 0, cut_aware);
+  };
+  const char* ca_env = getenv("QFLEX_CUT_AWARE_FLATTEN");
+  const bool ca_forced = ca_env && ca_env[0] == '1', ca_forbidden = ca_env && ca_env[0] == '0';
+  if (ca_forced) {
+    plan_with(true, &plan);
+  } else {
+    std::string first_error;
+    bool ok = false;
+    try {
+      plan_with(false, &plan);
+      ok = fits(plan);
+    } catch (const std::string& err_msg) {
+      first_error = err_msg;
+    }
+    if (!ok && !ca_forbidden) {
+      try {
+        Plan second;
+        plan_with(true, &second);
+        if (first_error.empty() && !fits(second)) throw std::string("does not fit either");
+        plan = std::move(second);
+        ok = true;
+      } catch (const std::string&) {
+        // report the plain plan's outcome
+      }
+    }
+    if (!ok && !first_error.empty()) throw first_error;
   }
-  if (!planned) plan = BuildPlan(*input, ordering, final_qubits);
   plan.precision = where.precision;
   for (auto& st : plan.steps) st.desc.precision = where.precision;
   lap("Time spent planning the contraction: ");

@@ -6,6 +6,7 @@
 // += i * amp_stride, so that projected and open terminal cuts can mix).
 #include <algorithm>
 #include <chrono>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -51,7 +52,11 @@ class Runner {
 
  private:
   uint64_t resolve(uint64_t base, const std::vector<VarTerm>& var) const {
-    for (const auto& v : var) base += (uint64_t)values_[v.cut] << v.shift;
+    for (const auto& v : var) {
+      uint64_t x = (uint64_t)values_[v.cut] >> v.from;
+      if (v.width < 64) x &= (uint64_t(1) << v.width) - 1;
+      base += x << v.shift;
+    }
     return base;
   }
 
@@ -287,9 +292,14 @@ void Session::Contract(int rank, int world,
   stats_.seconds_upload = up;
   stats_.seconds_flatten = fl;
   std::map<std::vector<int>, qfx_profile_row> merged;
+  // cut-aware flatten scales projected gate halves by powers of two (plan.cpp) so that
+  // partial amplitudes of heavily sliced circuits stay inside fp32's range; undone
+  // here, exactly, in fp64
+  const double unscale = std::ldexp(1.0, -plan_.amp_scale_log2);
   for (int l = 0; l < L; ++l) {
     for (uint64_t a = 0; a < plan_.n_amplitudes; ++a)
-      (*amplitudes)[a] += std::complex<double>(amps[l][2 * a], amps[l][2 * a + 1]);
+      (*amplitudes)[a] +=
+          std::complex<double>(amps[l][2 * a] * unscale, amps[l][2 * a + 1] * unscale);
     stats_.device_ms_contract = std::max(stats_.device_ms_contract, st[l].device_ms_contract);
     stats_.leaves += st[l].leaves;
     const qfx_stats& d = st[l].device;

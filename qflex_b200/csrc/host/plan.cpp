@@ -358,7 +358,7 @@ bool cut_can_open(const ContractionOperation& op) {
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               int open_outputs) {
+               int open_outputs, bool cut_aware_flatten) {
   Plan plan;
   // the LAST `open_outputs` openable terminal cuts of the ordering stay open (a later
   // cut enlarges fewer of the remaining patches)
@@ -389,6 +389,67 @@ Plan BuildPlan(const QflexInput& input,
   std::vector<std::vector<SiteNet>> net;
   build_network(input, final_qubits, &net);
 
+  // ------------------------------------------ cut-aware flatten: project the gates
+  // bond cuts that open the ordering -> id of the cut (position among the kept cuts)
+  std::map<std::string, int> pre_bond, pre_width;
+  std::vector<std::vector<char>> dynamic(I, std::vector<char>(J, 0));
+  if (cut_aware_flatten) {
+    int id = 0;
+    for (const auto& op : ordering) {
+      if (op.op_type != ContractionOperation::CUT) break;
+      if (cut_stays_open(op, 0)) continue;
+      if (op.cut.tensors.size() == 2) pre_bond[index_name(op.cut.tensors)] = id;
+      ++id;
+    }
+    for (std::size_t i = 0; i < I; ++i)
+      for (std::size_t j = 0; j < J; ++j) {
+        // virtual legs of every pre-cut bond, in chain (= chronological) order
+        std::map<std::string, std::vector<std::pair<std::size_t, std::string>>> legs;
+        auto& chain = net[i][j].chain;
+        for (std::size_t k = 0; k < chain.size(); ++k)
+          for (const auto& ix : chain[k].sym.idx) {
+            auto it = net[i][j].virt_to_bond.find(ix.name);
+            if (it != net[i][j].virt_to_bond.end() && pre_bond.count(it->second))
+              legs[it->second].push_back({k, ix.name});
+          }
+        for (const auto& kv : legs) {
+          int total = 0;
+          for (const auto& leg : kv.second) {
+            const SymTensor& t = chain[leg.first].sym;
+            total += t.idx[t.find(leg.second)].bits;
+          }
+          pre_width[kv.first] = total;
+          // A slice of a bond of w bits carries ~2^(-w/2) of the amplitude: with
+          // hundreds of cut bits the partial amplitudes leave fp32's range (Sycamore
+          // m=20: 2^-220).  One side of the bond (its first site) takes a factor 2 per
+          // two projected bits -- exact in floating point -- undone in fp64 at the end.
+          const bool scale_here = kv.first.rfind(utils::concat("(", i, ",", j, "),"), 0) == 0;
+          int carry = 0;
+          int seen = 0;  // the first leg is the most significant field of the bond value
+          for (const auto& leg : kv.second) {
+            SymTensor& t = chain[leg.first].sym;
+            const int p = t.find(leg.second);
+            seen += t.idx[p].bits;
+            if (scale_here) {
+              carry += t.idx[p].bits;
+              for (; carry >= 2; carry -= 2) {
+                for (auto& x : chain[leg.first].data) x *= 2.0f;
+                ++plan.amp_scale_log2;
+              }
+            }
+            VarTerm term;
+            term.cut = pre_bond.at(kv.first);
+            term.shift = t.idx[p].pos;
+            term.from = total - seen;
+            term.width = t.idx[p].bits;
+            t.var.push_back(term);
+            t.idx.erase(t.idx.begin() + p);
+          }
+          dynamic[i][j] = 1;
+        }
+      }
+  }
+
   // ---------------------------------------------------------- arena: gates
   uint64_t cursor = 0;
   for (std::size_t i = 0; i < I; ++i)
@@ -404,7 +465,7 @@ Plan BuildPlan(const QflexInput& input,
 
   // ------------------------------------------------- flatten: sizes first
   plan.site.assign(I, std::vector<SymTensor>(J));
-  uint64_t max_chain = 1;
+  uint64_t max_chain = 1, max_dyn_chain = 0;
   for (std::size_t i = 0; i < I; ++i)
     for (std::size_t j = 0; j < J; ++j) {
       if (is_off(i, j)) continue;
@@ -413,7 +474,8 @@ Plan BuildPlan(const QflexInput& input,
       for (std::size_t k = 1; k < net[i][j].chain.size(); ++k) {
         PlanStep dummy;
         a = make_contract(a, net[i][j].chain[k].sym, 0, &dummy);
-        max_chain = std::max(max_chain, a.size());
+        if (dynamic[i][j]) max_dyn_chain = std::max(max_dyn_chain, a.size());
+        else max_chain = std::max(max_chain, a.size());
       }
       // final layout: [(o)] ++ bonds ordered by consumption
       SymTensor& site = plan.site[i][j];
@@ -438,6 +500,7 @@ Plan BuildPlan(const QflexInput& input,
           auto it = net[i][j].virt_to_bond.find(ix.name);
           if (it != net[i][j].virt_to_bond.end() && it->second == b.name) b.bits += ix.bits;
         }
+        if (b.bits == 0 && pre_bond.count(b.name)) continue;  // projected in the gates
         site.idx.push_back(b);
       }
       site.make_dense();
@@ -448,6 +511,11 @@ Plan BuildPlan(const QflexInput& input,
       site.off = cursor;
       cursor = align_up(cursor + site.size());
     }
+  // sites flattened inside the slice loop share one ping-pong pair of their own (the
+  // work region below belongs to the patches by then)
+  const uint64_t dyn_ping = cursor, dyn_pong = cursor + align_up(max_dyn_chain);
+  if (max_dyn_chain > 0) cursor = dyn_pong + align_up(max_dyn_chain);
+  std::vector<PlanStep> dyn_steps;
   const uint64_t work_base = cursor;
   // Ping-pong buffers of the world-line products.  One pair PER SITE when that is
   // affordable (<= 2^26 elements = 512 MB in all): the chains are then independent
@@ -456,7 +524,7 @@ Plan BuildPlan(const QflexInput& input,
   uint64_t n_sites = 0;
   for (std::size_t i = 0; i < I; ++i)
     for (std::size_t j = 0; j < J; ++j)
-      if (!is_off(i, j)) ++n_sites;
+      if (!is_off(i, j) && !dynamic[i][j]) ++n_sites;
   const uint64_t pair_elems = 2 * align_up(max_chain);
   plan.flatten_parallel = n_sites * pair_elems <= (uint64_t(1) << 26);
   uint64_t work_flatten = plan.flatten_parallel ? n_sites * pair_elems : pair_elems;
@@ -466,10 +534,14 @@ Plan BuildPlan(const QflexInput& input,
     for (std::size_t j = 0; j < J; ++j) {
       if (is_off(i, j)) continue;
       const auto& chain = net[i][j].chain;
-      const int chain_id = plan.n_chains++;
+      const bool dyn = dynamic[i][j] != 0;
+      std::vector<PlanStep>& out_steps = dyn ? dyn_steps : plan.flatten_steps;
+      const std::size_t first_step = out_steps.size();
+      const int chain_id = dyn ? -1 : plan.n_chains++;
       const uint64_t ping =
-          work_base + (plan.flatten_parallel ? (uint64_t)chain_id * pair_elems : 0);
-      const uint64_t pong = ping + align_up(max_chain);
+          dyn ? dyn_ping
+              : work_base + (plan.flatten_parallel ? (uint64_t)chain_id * pair_elems : 0);
+      const uint64_t pong = dyn ? dyn_pong : ping + align_up(max_chain);
       SymTensor a = chain[0].sym;
       bool in_ping = false;
       for (std::size_t k = 1; k < chain.size(); ++k) {
@@ -481,7 +553,7 @@ Plan BuildPlan(const QflexInput& input,
         a = make_contract(a, chain[k].sym, dst, &st);
         st.desc.precision = QFX_PREC_FFMA;
         in_ping = !in_ping;
-        plan.flatten_steps.push_back(std::move(st));
+        out_steps.push_back(std::move(st));
       }
       // one permute into the final layout
       const SymTensor& site = plan.site[i][j];
@@ -517,12 +589,12 @@ Plan BuildPlan(const QflexInput& input,
           if (ix.pos + b != dpos + b) identity = false;
         }
       }
-      if (identity && !plan.flatten_steps.empty() && chain.size() > 1) {
+      if (identity && out_steps.size() > first_step && chain.size() > 1) {
         // last world-line product can write the grid tensor directly
-        plan.flatten_steps.back().desc.off_c = site.off;
+        out_steps.back().desc.off_c = site.off;
       } else {
         pm.bytes = 16.0 * (double)(1ull << pm.n_bits);
-        plan.flatten_steps.push_back(std::move(pm));
+        out_steps.push_back(std::move(pm));
       }
     }
 
@@ -633,7 +705,16 @@ Plan BuildPlan(const QflexInput& input,
     last_tensor = p.cur;
   };
 
+  bool dyn_placed = dyn_steps.empty();
   for (const auto& op : ordering) {
+    if (!dyn_placed && op.op_type != ContractionOperation::CUT) {
+      // the leading cuts are fixed from here on: flatten the sites next to them
+      for (auto& st : dyn_steps) {
+        st.level = level;
+        plan.steps.push_back(std::move(st));
+      }
+      dyn_placed = true;
+    }
     switch (op.op_type) {
       case ContractionOperation::EXPAND: {
         const std::size_t i = op.expand.tensor[0], j = op.expand.tensor[1];
@@ -685,7 +766,10 @@ Plan BuildPlan(const QflexInput& input,
         const int cut_id = (int)plan.cuts.size();
         const bool stays_open = cut_stays_open(op, open_outputs);
         int width = -1;
+        const bool pre = pre_bond.count(index) != 0;  // already projected in the gates
+        if (pre) width = pre_width.count(index) ? pre_width.at(index) : 0;
         for (const auto& pos : op.cut.tensors) {
+          if (pre) break;
           SymTensor& t = site[pos[0]][pos[1]];
           const int p = t.find(index);
           if (p < 0 || site_used[pos[0]][pos[1]]) {

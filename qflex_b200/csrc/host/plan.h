@@ -40,9 +40,12 @@ struct SymIndex {
 };
 
 // Slice-dependent part of an operand's base: value(cut) << shift.
+// offset += ((value of cut `cut` >> from) & (2^width - 1)) << shift
 struct VarTerm {
   int cut = 0;
   int shift = 0;
+  int from = 0;    // cut-aware flatten: one virtual leg is a bit field of its bond's value
+  int width = 64;
 };
 
 struct SymTensor {
@@ -132,6 +135,8 @@ struct Plan {
   int n_chains = 0;
   // terminal cuts kept as open indices of the final tensor (see BuildPlan)
   int open_outputs = 0;
+  // cut-aware flatten: the device computes amplitudes * 2^amp_scale_log2
+  int amp_scale_log2 = 0;
 };
 
 // Builds the full plan.  `final_qubits` = qubits with a terminal cut
@@ -146,10 +151,17 @@ struct Plan {
 // 2^k times fewer launches after the cut, 2^k times larger patches after it -- the
 // caller opens fewer cuts (down to none: the reference's plan) when that does not fit
 // the memory limit.
+//
+// `cut_aware_flatten`: the bond cuts that open the ordering are applied
+// to the GATE tensors -- every virtual leg of a cut bond is projected on its bit
+// field of the cut value -- so a grid tensor next to a cut never carries that bond.
+// Such sites are flattened inside the slice loop (their world-line products become
+// ordinary steps after the leading cuts) instead of once; grid tensors that would
+// not fit (Sycamore m >= 16: four bonds of 2^8..2^10) become representable.
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               int open_outputs = 0);
+               int open_outputs = 0, bool cut_aware_flatten = false);
 
 struct ExecStats {
   double seconds_upload = 0, seconds_flatten = 0, seconds_contract = 0;

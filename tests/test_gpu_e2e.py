@@ -12,6 +12,13 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-4  # BASELINE.json: per-run normwise relative error of the amplitude vector
 
 
+def _trim_parked_buffers():
+    """Arena / workspace of the previous evaluation stay parked for reuse; the large
+    cases below need that memory back before asking how much is free."""
+    from qflex_b200 import _device
+    _device.load().qfx_trim_cache(0)
+
+
 def _amps(golden, name):
     g = golden[name]
     return g["states"], np.array(g["re"]) + 1j * np.array(g["im"])
@@ -139,6 +146,7 @@ def test_7x7_depth_40_tensor_core_and_ffma_paths_agree(gpu_lib):
     there is no golden; the split-bf16 tensor-core path is checked against the
     independent FFMA kernels on one slice and two output bitstrings (same tolerance)."""
     import torch
+    _trim_parked_buffers()
     if torch.cuda.mem_get_info(0)[0] < (80 << 30):
         pytest.skip("needs 80 GB of free device memory")
     texts = support.case_texts(dict(
@@ -158,6 +166,7 @@ def test_sycamore_m12_tensor_core_and_ffma_paths_agree(gpu_lib):
     reference can hold on this host, so the tensor-core path is checked against the
     FFMA kernels."""
     import torch
+    _trim_parked_buffers()
     if torch.cuda.mem_get_info(0)[0] < (40 << 30):
         pytest.skip("needs 40 GB of free device memory")
     texts = support.case_texts(dict(
@@ -175,6 +184,7 @@ def test_sycamore_m14_with_augmented_ordering(gpu_lib):
     """BASELINE configs[2] as named (m=14): runs with the cut-augmented ordering
     (tools/augment_ordering.py); tensor-core path against FFMA on one slice."""
     import torch
+    _trim_parked_buffers()
     if torch.cuda.mem_get_info(0)[0] < (100 << 30):
         pytest.skip("needs 100 GB of free device memory")
     texts = support.case_texts(dict(
@@ -186,3 +196,24 @@ def test_sycamore_m14_with_augmented_ordering(gpu_lib):
     a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
     assert np.linalg.norm(b) > 0
     assert support.rel_err(a, b) < TOL
+
+
+def test_sycamore_m20_heavily_sliced_with_cut_aware_flatten(gpu_lib):
+    """BASELINE configs[4] as named (m=20).  Grid tensors with four 2^10 bonds do not
+    exist; the ordering carries 36 extra bond cuts (tools/augment_ordering.py) and the
+    planner projects them in the gate tensors (cut-aware flatten, exact power-of-two
+    range scaling).  One slice: a non-zero partial amplitude far below fp32's range
+    (~1e-65), the same from the tensor-core and the FFMA paths."""
+    import torch
+    _trim_parked_buffers()
+    if torch.cuda.mem_get_info(0)[0] < (140 << 30):
+        pytest.skip("needs 140 GB of free device memory")
+    texts = support.case_texts(dict(
+        circuit="sycamore_53_20_0.txt", ordering="sycamore_53_m20.txt", grid="sycamore_53.txt",
+        cut_values=[[0]] * 39 + [[0]] * 5 + [[0, 1]]))
+    tc, st_tc = gpu_lib.evaluate(*texts, memory_limit=170 << 30)
+    ff, st_ff = gpu_lib.evaluate(*texts, memory_limit=170 << 30, precision="ffma")
+    a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
+    assert len(tc) == 2 and 0 < np.linalg.norm(b) < 1e-50
+    assert support.rel_err(a, b) < TOL
+    _trim_parked_buffers()

@@ -228,3 +228,23 @@ def test_augmented_ordering_keeps_the_amplitudes(emul, golden):
     p.contract()
     assert abs(p.stats["flops_per_pass"] - info0["flops_per_slice"]) < 0.05 * info0["flops_per_slice"]  # the tool ignores output indices
     p.close()
+
+
+@pytest.mark.parametrize("name", ["test", "bristlecone_48_1-16-1", "sycamore_53_4",
+                                  "bristlecone_70_1-12-1", "rect2x2_0000"])
+def test_cut_aware_flatten_is_bit_identical(emul, monkeypatch, name):
+    """QFLEX_CUT_AWARE_FLATTEN=1: the leading bond cuts are applied to the gate tensors
+    and the sites next to them are flattened inside the slice loop.  Projecting a leg
+    before or after the world-line products selects the same numbers, and the range
+    scaling is by powers of two, so the amplitudes are the same bits."""
+    case = support.CASES[name]
+    texts = support.case_texts(case)
+    args = (case.get("initial", ""), case.get("final", ""))
+    r0, s0 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
+    monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", "1")
+    r1, s1 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
+    assert r0 == r1
+    has_bond_cut = any(l.split("#")[0].strip().startswith("cut") and len(l.split(")")[1].split()) == 2
+                       for l in texts[1].splitlines() if l.split("#")[0].strip())
+    if has_bond_cut:
+        assert s1["launches"] > s0["launches"] and s1["arena_bytes"] < s0["arena_bytes"]

@@ -83,6 +83,7 @@ def replay(ops, bits, cut):
                 out.append((boundary(new), 0, new))
                 continue
             merged = cur | new
+            out.append((boundary(new), 0, new))  # the grid tensor itself (cut-aware flatten)
             out.append((boundary(merged), boundary(merged) + between(cur, new), merged))
             patches[op[1]] = merged
         elif op[0] == "merge":
@@ -100,7 +101,7 @@ def cost(steps):
     return max(s[0] for s in steps), sum(2.0 ** s[1] for s in steps)
 
 
-def augment(circuit_text, grid_text, ordering_text, max_log2):
+def augment(circuit_text, grid_text, ordering_text, max_log2, extra=0):
     bits = bond_bits(circuit_text)
     ops = parse_ordering(ordering_text)
     cut = {op[1] for op in ops if op[0] == "cut" and len(op[1]) == 2}
@@ -109,7 +110,9 @@ def augment(circuit_text, grid_text, ordering_text, max_log2):
         steps = replay(ops, bits, cut)
         worst, _ = cost(steps)
         if worst <= max_log2:
-            break
+            if extra <= 0:
+                break
+            extra -= 1  # keep going: `extra` more cuts on the largest tensor (arena size)
         big = max(steps, key=lambda s: s[0])[2]
         cands = [k for k in bits if k not in cut and ((k[0] in big) != (k[1] in big))]
         if not cands:
@@ -139,10 +142,11 @@ def main():
     ap.add_argument("grid")
     ap.add_argument("ordering")
     ap.add_argument("--max-log2", type=int, default=30)
+    ap.add_argument("--extra", type=int, default=0, help="more cuts after the limit is met")
     ap.add_argument("-o", "--output")
     a = ap.parse_args()
     text, info = augment(open(a.circuit).read(), open(a.grid).read(), open(a.ordering).read(),
-                         a.max_log2)
+                         a.max_log2, a.extra)
     print("largest tensor 2^%d elements, %.3g flop per slice, 2^%d slices, cuts added: %s"
           % (info["max_log2"], info["flops_per_slice"], info["log2_slices"],
              " ".join("%d-%d" % k for k in info["added"]) or "none"), file=sys.stderr)
