@@ -489,6 +489,71 @@ __global__ void __launch_bounds__(kDotThreads)
   }
 }
 
+// ---------------------------------------------------------------- stream_small
+// C[m, n] = sum_k A[m, k] * B[k, n] with N, K <= 4 and a long M: one world-line step
+// of a large grid tensor (cut-aware flatten of Sycamore m >= 14: 2^28..2^30 elements
+// times a 1- or 2-qubit gate).  Pure streaming, AI < 1 flop/B: the tiled GEMM spent
+// its time on per-tile bookkeeping (0.95 TB/s).  One thread per m, m enumerated in
+// A-address order; the m bits are grouped into runs that are contiguous in both A and
+// C so that an address is a few shift-mask-or steps; B lives in shared memory.
+struct StreamSeg {
+  int start, len, a_shift, c_shift;
+};
+struct StreamArgs {
+  const float2* A;
+  const float2* B;
+  float2* C;
+  int m_bits, n_bits, k_bits, n_seg;
+  StreamSeg seg[8];
+  int8_t a_k[2], b_k[2], b_n[2], c_n[2];
+};
+
+__global__ void __launch_bounds__(256) stream_small(const __grid_constant__ StreamArgs g) {
+  __shared__ float2 Bs[16];
+  __shared__ unsigned long long ka[4], cn[4];
+  const int K = 1 << g.k_bits, N = 1 << g.n_bits;
+  if ((int)threadIdx.x < K * N) {
+    const int k = threadIdx.x / N, n = threadIdx.x % N;
+    unsigned long long o = 0;
+    for (int q = 0; q < g.k_bits; ++q) o |= (unsigned long long)((k >> q) & 1) << g.b_k[q];
+    for (int q = 0; q < g.n_bits; ++q) o |= (unsigned long long)((n >> q) & 1) << g.b_n[q];
+    Bs[threadIdx.x] = g.B[o];
+  }
+  if (threadIdx.x < 4) {
+    unsigned long long oa = 0, oc = 0;
+    for (int q = 0; q < g.k_bits; ++q) oa |= (unsigned long long)((threadIdx.x >> q) & 1) << g.a_k[q];
+    for (int q = 0; q < g.n_bits; ++q) oc |= (unsigned long long)((threadIdx.x >> q) & 1) << g.c_n[q];
+    ka[threadIdx.x] = oa;
+    cn[threadIdx.x] = oc;
+  }
+  __syncthreads();
+  const unsigned long long M = 1ull << g.m_bits;
+  const float2* __restrict__ A = g.A;
+  float2* __restrict__ C = g.C;
+  for (unsigned long long m = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; m < M;
+       m += (unsigned long long)gridDim.x * blockDim.x) {
+    unsigned long long ao = 0, co = 0;
+    for (int s = 0; s < g.n_seg; ++s) {
+      const unsigned long long f = (m >> g.seg[s].start) & ((1ull << g.seg[s].len) - 1ull);
+      ao |= f << g.seg[s].a_shift;
+      co |= f << g.seg[s].c_shift;
+    }
+    float2 a[4];
+    for (int k = 0; k < K; ++k) a[k & 3] = __ldg(A + (ao | ka[k]));
+    for (int n = 0; n < N; ++n) {
+      float sx = 0.f, sy = 0.f;
+      for (int k = 0; k < K; ++k) {
+        const float2 b = Bs[k * N + n];
+        sx = fmaf(a[k & 3].x, b.x, sx);
+        sx = fmaf(-a[k & 3].y, b.y, sx);
+        sy = fmaf(a[k & 3].x, b.y, sy);
+        sy = fmaf(a[k & 3].y, b.x, sy);
+      }
+      C[co | cn[n]] = make_float2(sx, sy);
+    }
+  }
+}
+
 // ---------------------------------------------------------------- gemv_rows
 // out[m] = sum_k A[m,k] * B[k] with 2..64 outputs and a long K, A dense: the tail of a
 // schedule whose output indices stayed open (the last merge yields all 2^k amplitudes).
@@ -817,6 +882,48 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     rc = qfx_launch_contract_tc_fused(ctx, d, A, B, C, &done);
     if (rc || done) return rc;
     if (d.n_bits >= 5 && d.k_bits >= 5) return qfx_launch_contract_tc(ctx, d, A, B, C);
+  }
+
+  // ---------------- tiny N and K, long M: streaming kernel
+  if (!accumulate_amp && d.m_bits >= 16 && d.n_bits <= 2 && d.k_bits <= 2 &&
+      getenv("QFLEX_NO_STREAM") == nullptr) {
+    StreamArgs g{};
+    g.A = A;
+    g.B = B;
+    g.C = C;
+    g.m_bits = d.m_bits;
+    g.n_bits = d.n_bits;
+    g.k_bits = d.k_bits;
+    for (int q = 0; q < d.k_bits; ++q) g.a_k[q] = d.a_k[q], g.b_k[q] = d.b_k[q];
+    for (int q = 0; q < d.n_bits; ++q) g.b_n[q] = d.b_n[q], g.c_n[q] = d.c_n[q];
+    // m bits in A-address order (which m bit is which is free as long as a_m and c_m
+    // move together), then runs contiguous in both operands
+    std::vector<int> idx(d.m_bits);
+    for (int i = 0; i < d.m_bits; ++i) idx[i] = i;
+    std::sort(idx.begin(), idx.end(), [&](int x, int y) { return d.a_m[x] < d.a_m[y]; });
+    bool ok = true;
+    for (int i = 0; i < d.m_bits;) {
+      int j = i + 1;
+      while (j < d.m_bits && d.a_m[idx[j]] == d.a_m[idx[j - 1]] + 1 &&
+             d.c_m[idx[j]] == d.c_m[idx[j - 1]] + 1)
+        ++j;
+      if (g.n_seg == 8) {
+        ok = false;
+        break;
+      }
+      g.seg[g.n_seg++] = StreamSeg{i, j - i, d.a_m[idx[i]], d.c_m[idx[i]]};
+      i = j;
+    }
+    if (ok) {
+      const unsigned long long M = 1ull << d.m_bits;
+      const unsigned blocks =
+          (unsigned)std::min<unsigned long long>(M / 256, 16ull * ctx->sm_count);
+      stream_small<<<blocks, 256, 0, ctx->stream>>>(g);
+      QFX_CUDA(cudaGetLastError());
+      ctx->stats.launches_gemm_ffma++;
+      ctx->stats.launches_total++;
+      return QFX_OK;
+    }
   }
 
   // ---------------- a few outputs on one side, long K, dense big operand: linear GEMV

@@ -84,6 +84,26 @@ def test_contract_few_outputs_long_k_gemv(ctx, outs, k, seed, side):
         assert _run_contract(ctx, t2, rng) < TOL
 
 
+@pytest.mark.parametrize("m,n,k", [(16, 1, 1), (18, 2, 1), (17, 0, 2), (20, 2, 2), (16, 0, 0),
+                                   (19, 1, 2), (21, 1, 0), (1, 17, 1), (2, 18, 2)])
+def test_contract_long_m_tiny_n_k_streaming(ctx, m, n, k):
+    """World-line steps on large grid tensors (cut-aware flatten): N, K <= 4, long M."""
+    rng = np.random.default_rng(77 * m + 10 * n + k)
+    assert _run_contract(ctx, _random_tables(rng, m, n, k), rng) < TOL
+    # the layout a flatten step produces: A = [m_hi | k | m_lo], C = [m_hi, m_lo | n]
+    lo = min(m, n) if False else 5
+    big, small = (m, n) if m >= n else (n, m)
+    a_free = list(range(lo)) + list(range(lo + k, big + k))
+    a_k = list(range(lo, lo + k))
+    c_big = list(range(small, small + big))
+    t = dict(a_m=a_free, a_k=a_k, b_k=list(range(small, small + k)), b_n=list(range(small)),
+             c_m=c_big, c_n=list(range(small)))
+    if m < n:  # same contraction with the roles of the operands exchanged
+        t = dict(a_m=t["b_n"], a_k=t["b_k"], b_k=t["a_k"], b_n=t["a_m"], c_m=t["c_n"], c_n=t["c_m"])
+    assert _run_contract(ctx, t, rng) < TOL
+    assert _run_contract(ctx, t, rng, off_jitter=1) < TOL
+
+
 @pytest.mark.parametrize("m,n,k", [(8, 6, 6), (12, 3, 3), (9, 7, 5), (0, 0, 10)])
 def test_contract_odd_base_offsets(ctx, m, n, k):
     # cut projections shift operand bases; odd bases disable 16-byte accesses
