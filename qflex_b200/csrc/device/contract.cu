@@ -504,6 +504,7 @@ struct StreamArgs {
   const float2* B;
   float2* C;
   int m_bits, n_bits, k_bits, n_seg;
+  int c_vec;  // the n bits are C's lowest address bits and C's base is even: 16-byte stores
   StreamSeg seg[8];
   int8_t a_k[2], b_k[2], b_n[2], c_n[2];
 };
@@ -540,6 +541,7 @@ __global__ void __launch_bounds__(256) stream_small(const __grid_constant__ Stre
     }
     float2 a[4];
     for (int k = 0; k < K; ++k) a[k & 3] = __ldg(A + (ao | ka[k]));
+    float2 prev = make_float2(0.f, 0.f);
     for (int n = 0; n < N; ++n) {
       float sx = 0.f, sy = 0.f;
       for (int k = 0; k < K; ++k) {
@@ -549,7 +551,13 @@ __global__ void __launch_bounds__(256) stream_small(const __grid_constant__ Stre
         sy = fmaf(a[k & 3].x, b.y, sy);
         sy = fmaf(a[k & 3].y, b.x, sy);
       }
-      C[co | cn[n]] = make_float2(sx, sy);
+      if (!g.c_vec) {
+        C[co | cn[n]] = make_float2(sx, sy);
+      } else if (n & 1) {
+        *reinterpret_cast<float4*>(C + co + n - 1) = make_float4(prev.x, prev.y, sx, sy);
+      } else {
+        prev = make_float2(sx, sy);
+      }
     }
   }
 }
@@ -901,6 +909,9 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     std::vector<int> idx(d.m_bits);
     for (int i = 0; i < d.m_bits; ++i) idx[i] = i;
     std::sort(idx.begin(), idx.end(), [&](int x, int y) { return d.a_m[x] < d.a_m[y]; });
+    g.c_vec = (d.n_bits >= 1 && !(d.off_c & 1)) ? 1 : 0;
+    for (int q = 0; q < d.n_bits; ++q)
+      if (d.c_n[q] != q) g.c_vec = 0;
     bool ok = true;
     for (int i = 0; i < d.m_bits;) {
       int j = i + 1;
