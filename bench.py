@@ -65,6 +65,12 @@ WORKLOADS = {
         circuit="sycamore_53_14_0.txt", ordering="sycamore_53_m14.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1]] * 3 + [[0]] * 6 + [[0, 1]] * 6},
         reference_sample=None, memory=160 << 30, total_slices=2.0 ** 58),
+    # Sycamore-53 m=16: shipped ordering + 22 bond cuts (largest tensor 2^24, 2^200
+    # slices, 4.6 GB), cut-aware flatten; 64 slices x 64 bitstrings, strong scaling
+    "sycamore_53_16": dict(
+        circuit="sycamore_53_16_0.txt", ordering="sycamore_53_m16.txt", grid="sycamore_53.txt",
+        scaling="strong", cuts={"all": [[0, 1, 2, 3]] * 3 + [[0]] * 22 + [[0, 1]] * 6},
+        reference_sample=None, memory=64 << 30, total_slices=2.0 ** 200),
     # BASELINE configs[4] as named: Sycamore-53 m=20, heavily sliced.  Its grid tensors
     # (four bonds of 2^10) are not representable; config/ordering/sycamore_53_m20.txt =
     # the shipped ordering + 36 bond cuts (tools/augment_ordering.py --max-log2 30

@@ -217,3 +217,23 @@ def test_sycamore_m20_heavily_sliced_with_cut_aware_flatten(gpu_lib):
     assert len(tc) == 2 and 0 < np.linalg.norm(b) < 1e-50
     assert support.rel_err(a, b) < TOL
     _trim_parked_buffers()
+
+
+def test_sycamore_m16_cut_aware_flatten_paths_agree(gpu_lib, monkeypatch):
+    """m=16 (22 extra cuts, cut-aware flatten chosen by the planner because the plain
+    grid tensors do not exist): 4 slices x 2 bitstrings, tensor-core vs FFMA, and the
+    rank shares of a 2-way split add up to the whole."""
+    texts = support.case_texts(dict(
+        circuit="sycamore_53_16_0.txt", ordering="sycamore_53_m16.txt", grid="sycamore_53.txt",
+        cut_values=[[0, 1], [0, 1]] + [[0]] * 23 + [[0]] * 5 + [[0, 1]]))
+    tc, st = gpu_lib.evaluate(*texts, memory_limit=64 << 30)
+    ff, _ = gpu_lib.evaluate(*texts, memory_limit=64 << 30, precision="ffma")
+    a, b = np.array([v for _, v in tc]), np.array([v for _, v in ff])
+    assert st["leaves"] == 8 and 0 < np.linalg.norm(b) < 1e-20
+    assert support.rel_err(a, b) < TOL
+    parts = sum(np.array([v for _, v in gpu_lib.evaluate(*texts, memory_limit=64 << 30,
+                                                         rank=r, world=2)[0]]) for r in range(2))
+    assert support.rel_err(parts, a) < 1e-6
+    monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", "0")
+    with pytest.raises(Exception, match="2\\^32"):
+        gpu_lib.evaluate(*texts, memory_limit=64 << 30)
