@@ -134,7 +134,15 @@ int choose_lanes(const Plan& plan) {
   // lanes only for networks whose arena is small next to the GPU (<= 2 GB each, 4 GB
   // in all): their kernels run for microseconds and do not fill the SMs
   int lanes = (int)std::min<double>(8.0, (4096.0 * 1048576.0) / std::max(arena_bytes, 1.0));
-  if (arena_bytes > 2048.0 * 1048576.0) lanes = 1;
+  if (arena_bytes > 2048.0 * 1048576.0) {
+    lanes = 1;
+    // larger arenas whose schedule is still a stream of small launches (cut-aware
+    // flatten of Sycamore m=16: ~2600 world-line steps per slice, 2e8 flop each):
+    // lanes as long as they fit in 64 GB together
+    const double per_launch = plan.flops_per_pass / std::max<double>(1.0, (double)plan.steps.size());
+    if (per_launch < 1e9)
+      lanes = (int)std::min<double>(8.0, (65536.0 * 1048576.0) / arena_bytes);
+  }
   lanes = (int)std::min<uint64_t>((uint64_t)std::max(lanes, 1), std::max<uint64_t>(1, slices / 2));
   return std::max(lanes, 1);
 }
