@@ -353,7 +353,7 @@ def main():
     c, o, g = load_texts(w, cuts)
     lib = qflex_b200.default_library()
     prep = lib.prepare(c, o, g, memory_limit=w["memory"], device=local_rank,
-                       precision=args.precision)
+                       precision=args.precision, world=world)
 
     # ---- resident: W warm-up + K timed steps
     for _ in range(args.warmup):

@@ -32,7 +32,11 @@
 extern "C" {
 #endif
 
+/* Capacity of the per-bit position tables.  An operand may have at most
+ * QFX_MAX_OPERAND_BITS index bits (2^32 elements = 32 GB of complex64): every kernel
+ * computes element offsets in 32 bits plus a 64-bit base. */
 #define QFX_MAX_BITS 40
+#define QFX_MAX_OPERAND_BITS 32
 #define QFX_OK 0
 #define QFX_ERR_CUDA 1
 #define QFX_ERR_ARG 2
@@ -46,6 +50,11 @@ const char* qfx_last_error(void);
 /* Number of visible CUDA devices (fails loudly when there is no GPU/driver:
  * there is no CPU fallback anywhere in this library). */
 int qfx_device_count(int* n_out);
+
+/* Free and total memory of `device` in bytes (device < 0: the calling thread's current
+ * device).  Replaces what --track-memory reports in the reference, the process'
+ * resident memory (src/memory.h:27-83): here the scratch lives in HBM. */
+int qfx_device_memory(int device, uint64_t* free_bytes_out, uint64_t* total_bytes_out);
 
 /* One context = one GPU + one stream + one arena + one amplitude table.
  * Replaces the process-global state of the reference (global::*, _REORDER_MAPS,

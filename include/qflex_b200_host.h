@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define QFLEX_B200_N_STATS 16
+#define QFLEX_B200_N_STATS 20
 /* stats_out layout (doubles):
  *  [0] seconds_upload   [1] seconds_flatten   [2] seconds_contract (host wall)
  *  [3] device_ms_contract (CUDA events)       [4] leaves executed on this rank
@@ -28,6 +28,9 @@ extern "C" {
  *  [9] flops of one pass over the schedule    [10] bytes of one pass
  *  [11] gemm (FFMA) launches [12] gemm (tensor core) launches
  *  [13] reduce launches      [14] permute launches   [15] number of amplitudes
+ *  [16] fused cut bits (one pass covers 2^f slices of the ordering as written)
+ *  [17] terminal cuts kept open          [18] lanes (contexts on this GPU)
+ *  [19] reserved
  */
 
 /* One-shot EvaluateCircuit.  states_out receives the output bitstrings joined
@@ -45,6 +48,14 @@ void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
                          const char* grid_text, const char* initial_state,
                          const char* final_state, uint64_t memory_limit_bytes,
                          int device, int precision, char* err, uint64_t err_cap);
+/* Same, planned for a run on `world` ranks: the planner undoes bond-cut slicing
+ * (larger kernels, fewer passes) only as far as every rank keeps a share of the
+ * remaining slices.  qflex_b200_prepare plans for world = 1. */
+void* qflex_b200_prepare_sharded(const char* circuit_text, const char* ordering_text,
+                                 const char* grid_text, const char* initial_state,
+                                 const char* final_state, uint64_t memory_limit_bytes,
+                                 int device, int precision, int world, char* err,
+                                 uint64_t err_cap);
 /* ... then run the contraction schedule any number of times.  Only the slices
  * dealt to `rank` of `world` are executed; sum the partial amplitudes across
  * ranks (NCCL all-reduce).  Returns the number of amplitudes or -1. */
@@ -54,6 +65,14 @@ long qflex_b200_contract(void* prepared, int rank, int world, double* amps_out,
 /* Re-run the host->device upload of the gate tensors and the device-side
  * flatten (used to time the full host-buffer path). */
 long qflex_b200_reload(void* prepared, char* err, uint64_t err_cap);
+/* Another final state on the same resident circuit: only the delta tensors closing
+ * the world lines are rewritten and the (ms-scale) flatten re-run; parse, plan, arena
+ * and schedule are reused.  Positions of terminal-cut qubits are ignored.  This is the
+ * batched form of the reference's `final_states` list, which src/pybind_main.cpp:49-73
+ * parses and :111-113 rejects ("Not yet supported"), so that qflexcirq calls
+ * simulate() once per bitstring (qflexcirq/interface/qflex_simulator.py:44-66). */
+long qflex_b200_set_final_state(void* prepared, const char* final_state, char* err,
+                                uint64_t err_cap);
 long qflex_b200_states(void* prepared, char* states_out, uint64_t states_cap);
 /* Text dump of the plan, one step per line:
  * "<phase> <level> <kind> <m_bits> <n_bits> <k_bits> <label>". Returns bytes

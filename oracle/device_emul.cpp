@@ -45,6 +45,11 @@ int qfx_device_count(int* n) {
   *n = 1;
   return QFX_OK;
 }
+int qfx_device_memory(int, uint64_t* free_b, uint64_t* total_b) {
+  *free_b = 0;
+  *total_b = 0;
+  return QFX_OK;
+}
 int qfx_create(int, qfx_ctx** out) {
   *out = new qfx_ctx();
   return QFX_OK;

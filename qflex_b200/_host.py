@@ -11,12 +11,12 @@ import sys
 
 import numpy as np
 
-N_STATS = 16
+N_STATS = 20
 STAT_NAMES = (
     "seconds_upload", "seconds_flatten", "seconds_contract", "device_ms_contract",
     "leaves", "launches", "flops", "bytes", "arena_bytes", "flops_per_pass",
     "bytes_per_pass", "launches_gemm_ffma", "launches_gemm_tc", "launches_reduce",
-    "launches_permute", "n_amplitudes",
+    "launches_permute", "n_amplitudes", "fused_bits", "open_outputs", "lanes", "reserved",
 )
 PRECISIONS = {"auto": 0, "ffma": 1, "bf16x3": 2}
 
@@ -62,11 +62,14 @@ class Prepared:
     def __init__(self, lib, handle):
         self._lib = lib
         self._h = handle
-        n = lib._c.qflex_b200_states(handle, None, 0)
-        buf = ctypes.create_string_buffer(n)
-        lib._c.qflex_b200_states(handle, buf, n)
-        self.states = buf.value.decode().split("\n")
+        self._read_states()
         self.stats = {}
+
+    def _read_states(self):
+        n = self._lib._c.qflex_b200_states(self._h, None, 0)
+        buf = ctypes.create_string_buffer(n)
+        self._lib._c.qflex_b200_states(self._h, buf, n)
+        self.states = buf.value.decode().split("\n")
 
     def contract(self, rank=0, world=1):
         n = len(self.states)
@@ -80,6 +83,13 @@ class Prepared:
             raise QflexError(err.value.decode())
         self.stats = dict(zip(STAT_NAMES, stats.tolist()))
         return amps.view(np.complex128)
+
+    def set_final_state(self, final_state):
+        """Same circuit, another output bitstring: parse/plan/arena are reused."""
+        err = ctypes.create_string_buffer(1 << 16)
+        if self._lib._c.qflex_b200_set_final_state(self._h, _text(final_state), err, len(err)) < 0:
+            raise QflexError(err.value.decode())
+        self._read_states()
 
     def reload(self):
         err = ctypes.create_string_buffer(1 << 16)
@@ -137,12 +147,20 @@ class HostLibrary:
             ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
             ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int,
             ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_prepare_sharded.restype = ctypes.c_void_p
+        c.qflex_b200_prepare_sharded.argtypes = [
+            ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
+            ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+            ctypes.c_char_p, ctypes.c_uint64]
         c.qflex_b200_contract.restype = ctypes.c_long
         c.qflex_b200_contract.argtypes = [
             ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
             ctypes.c_uint64, ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
         c.qflex_b200_reload.restype = ctypes.c_long
         c.qflex_b200_reload.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_set_final_state.restype = ctypes.c_long
+        c.qflex_b200_set_final_state.argtypes = [ctypes.c_void_p, ctypes.c_char_p,
+                                                 ctypes.c_char_p, ctypes.c_uint64]
         c.qflex_b200_states.restype = ctypes.c_long
         c.qflex_b200_states.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
         c.qflex_b200_describe.restype = ctypes.c_long
@@ -161,12 +179,14 @@ class HostLibrary:
         self._c.qflex_b200_set_verbose(int(level))
 
     def prepare(self, circuit, ordering, grid, initial_state="", final_state="",
-                memory_limit=None, device=0, precision="auto"):
+                memory_limit=None, device=0, precision="auto", world=1):
+        """`world` = number of ranks the slices will be dealt over by contract(rank,
+        world): the planner keeps at least that many slices apart."""
         err = ctypes.create_string_buffer(1 << 16)
-        h = self._c.qflex_b200_prepare(
+        h = self._c.qflex_b200_prepare_sharded(
             _text(circuit), _text(ordering), _text(grid), _text(initial_state),
             _text(final_state), _memory_bytes(memory_limit), device,
-            PRECISIONS[precision], err, len(err))
+            PRECISIONS[precision], int(world), err, len(err))
         if not h:
             raise QflexError(err.value.decode())
         return Prepared(self, h)
@@ -245,22 +265,33 @@ def simulate(options, lib=None):
         final = _load_state(options, "final")
         if len(initial) != 1:
             raise QflexError("Not yet supported")
-        # Several final states in one call (the reference answers "Not yet supported",
-        # src/pybind_main.cpp:111-113, and qflexcirq calls simulate once per bitstring):
-        # the inputs are read once and the device buffers of one evaluation are reused
-        # by the next (parked arena), so a batch costs parse + plan + contract per state.
+        # Several final states in one call: the reference answers "Not yet supported"
+        # (src/pybind_main.cpp:111-113) and qflexcirq calls simulate once per bitstring.
         circuit = _load_option(options, "circuit")
         ordering = _load_option(options, "ordering")
         grid = _load_option(options, "grid")
-        result = []
-        for state in final:
-            part, _ = lib.evaluate(
-                circuit, ordering, grid, initial[0], state,
+        rank, world = options.get("rank", 0), options.get("world", 1)
+        if len(final) == 1:
+            return lib.evaluate(
+                circuit, ordering, grid, initial[0], final[0],
                 memory_limit=options.get("memory_limit"), device=options.get("device", 0),
-                rank=options.get("rank", 0), world=options.get("world", 1),
-                precision=options.get("precision", "auto"))
-            result.extend(part)
-        return result
+                rank=rank, world=world, precision=options.get("precision", "auto"))[0]
+        # batch: the circuit is parsed, planned, uploaded once and stays resident; each
+        # further final state rewrites the closing delta tensors and re-runs the flatten
+        prepared = lib.prepare(
+            circuit, ordering, grid, initial[0], final[0],
+            memory_limit=options.get("memory_limit"), device=options.get("device", 0),
+            precision=options.get("precision", "auto"), world=world)
+        try:
+            result = []
+            for n, state in enumerate(final):
+                if n:
+                    prepared.set_final_state(state)
+                amps = prepared.contract(rank, world)
+                result.extend(zip(prepared.states, [complex(a) for a in amps]))
+            return result
+        finally:
+            prepared.close()
     except QflexError as e:
         print(e, file=sys.stderr)
         return []

@@ -107,7 +107,14 @@ int qfx_ensure_ws(qfx_ctx* ctx, size_t bytes) {
   }
   cudaError_t e = cudaMalloc(&ctx->ws, want);
   if (e != cudaSuccess) {
+    // a parked buffer of an earlier context may be what is in the way
     cudaGetLastError();
+    qfx_trim_cache(ctx->device);
+    e = cudaMalloc(&ctx->ws, want);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    ctx->ws = nullptr;
     qfx_set_error("out of device memory allocating the split-K workspace");
     return QFX_ERR_OOM;
   }
@@ -197,6 +204,23 @@ int qfx_device_count(int* n_out) {
   return QFX_OK;
 }
 
+int qfx_device_memory(int device, uint64_t* free_bytes_out, uint64_t* total_bytes_out) {
+  if (free_bytes_out == nullptr || total_bytes_out == nullptr) {
+    qfx_set_error("qfx_device_memory: null argument");
+    return QFX_ERR_ARG;
+  }
+  int prev = 0;
+  QFX_CUDA(cudaGetDevice(&prev));
+  if (device >= 0 && device != prev) QFX_CUDA(cudaSetDevice(device));
+  size_t f = 0, t = 0;
+  cudaError_t e = cudaMemGetInfo(&f, &t);
+  if (device >= 0 && device != prev) cudaSetDevice(prev);
+  if (e != cudaSuccess) return qfx_fail_cuda(e, "cudaMemGetInfo");
+  *free_bytes_out = f;
+  *total_bytes_out = t;
+  return QFX_OK;
+}
+
 int qfx_create(int device, qfx_ctx** ctx_out) {
   if (ctx_out == nullptr) {
     qfx_set_error("qfx_create: null argument");
@@ -244,9 +268,15 @@ int qfx_create(int device, qfx_ctx** ctx_out) {
   ctx->device = device;
   ctx->sm_count = sms;
   if (const char* e = getenv("QFLEX_TC_CHUNK")) ctx->tc_chunk = atoi(e);
-  QFX_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-  QFX_CUDA(cudaEventCreate(&ctx->ev0));
-  QFX_CUDA(cudaEventCreate(&ctx->ev1));
+  cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);
+  if (e != cudaSuccess) {
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return qfx_fail_cuda(e, "qfx_create (stream / events)");
+  }
   *ctx_out = ctx;
   return QFX_OK;
 }
@@ -398,7 +428,18 @@ int qfx_amps_reserve(qfx_ctx* ctx, uint64_t n_amps) {
     if (ctx->amps) QFX_CUDA(cudaFree(ctx->amps));
     ctx->amps = nullptr;
     ctx->n_amps = 0;
-    QFX_CUDA(cudaMalloc(&ctx->amps, n_amps * sizeof(double2)));
+    cudaError_t e = cudaMalloc(&ctx->amps, n_amps * sizeof(double2));
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      qfx_trim_cache(ctx->device);
+      e = cudaMalloc(&ctx->amps, n_amps * sizeof(double2));
+    }
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      ctx->amps = nullptr;
+      qfx_set_error("out of device memory allocating the amplitude table");
+      return QFX_ERR_OOM;
+    }
     ctx->n_amps = n_amps;
   }
   QFX_CUDA(cudaMemsetAsync(ctx->amps, 0, ctx->n_amps * sizeof(double2), ctx->stream));

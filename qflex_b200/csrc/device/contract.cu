@@ -725,21 +725,21 @@ int launch_gemm_cfg(qfx_ctx* ctx, GemmArgs& g, unsigned blocks) {
   constexpr int BM = 1 << TMB, BN = 1 << TNB, BKMAX = 1 << TKB;
   constexpr int NT = (BM / TM) * (BN / TN);
   constexpr size_t smem = 2ull * BKMAX * (BM + BN) * sizeof(float2);
-  static bool attr_full = false, attr_part = false;
+  static qfx_per_device_once attr_full, attr_part;
   if (g.tk == TKB) {
     auto kern = gemm_gather<TMB, TNB, TKB, TM, TN, true>;
-    if (!attr_full) {
+    if (attr_full.need(ctx->device)) {
       QFX_CUDA(cudaFuncSetAttribute(
           kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_full = true;
+      attr_full.mark(ctx->device);
     }
     kern<<<blocks, NT, smem, ctx->stream>>>(g);
   } else {
     auto kern = gemm_gather<TMB, TNB, TKB, TM, TN, false>;
-    if (!attr_part) {
+    if (attr_part.need(ctx->device)) {
       QFX_CUDA(cudaFuncSetAttribute(
           kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr_part = true;
+      attr_part.mark(ctx->device);
     }
     kern<<<blocks, NT, smem, ctx->stream>>>(g);
   }

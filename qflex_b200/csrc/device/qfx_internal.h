@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -41,6 +42,18 @@ struct qfx_prof_scope {
   qfx_ctx* ctx;
   qfx_prof_scope(qfx_ctx* c, int kind, int m, int n, int k, double flops, double bytes);
   ~qfx_prof_scope();
+};
+
+// cudaFuncSetAttribute is per DEVICE: a once-flag per device (bit d = device d done).
+// Two threads may both set the attribute once; that is harmless.
+struct qfx_per_device_once {
+  std::atomic<uint64_t> done{0};
+  bool need(int device) const {
+    return device < 0 || device >= 64 || !((done.load(std::memory_order_acquire) >> device) & 1u);
+  }
+  void mark(int device) {
+    if (device >= 0 && device < 64) done.fetch_or(uint64_t(1) << device, std::memory_order_release);
+  }
 };
 
 void qfx_set_error(const std::string& msg);

@@ -621,15 +621,15 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
     qfx_set_error("cuTensorMapEncodeTiled failed");
     return QFX_ERR_CUDA;
   }
-  static bool attr = false;
-  if (!attr) {
+  static qfx_per_device_once attr;
+  if (attr.need(ctx->device)) {
     QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
     QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
     QFX_CUDA(cudaFuncSetAttribute(tc_fused_bf16x3<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
-    attr = true;
+    attr.mark(ctx->device);
   }
   const int grid = std::min(g.tiles * g.ksplit, ctx->sm_count);
   switch (pick_store_mode(g, C)) {

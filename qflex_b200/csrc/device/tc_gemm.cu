@@ -426,11 +426,11 @@ int qfx_launch_contract_tc(qfx_ctx* ctx, const qfx_contract_desc& d, const float
     qfx_set_error("cuTensorMapEncodeTiled failed");
     return QFX_ERR_CUDA;
   }
-  static bool attr = false;
-  if (!attr) {
+  static qfx_per_device_once attr;
+  if (attr.need(ctx->device)) {
     QFX_CUDA(cudaFuncSetAttribute(tc_gemm_bf16x3, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_BYTES));
-    attr = true;
+    attr.mark(ctx->device);
   }
   const int grid = std::min(g.tiles, ctx->sm_count);
   tc_gemm_bf16x3<<<grid, TC_THREADS, SMEM_BYTES, ctx->stream>>>(mAh, mAm, mBh, mBm, g);

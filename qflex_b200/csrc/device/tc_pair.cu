@@ -710,15 +710,15 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
     qfx_set_error("cuTensorMapEncodeTiled failed");
     return QFX_ERR_CUDA;
   }
-  static bool attr = false;
-  if (!attr) {
+  static qfx_per_device_once attr;
+  if (attr.need(ctx->device)) {
     QFX_CUDA(cudaFuncSetAttribute(tc_pair_bf16x3<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
     QFX_CUDA(cudaFuncSetAttribute(tc_pair_bf16x3<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
     QFX_CUDA(cudaFuncSetAttribute(tc_pair_bf16x3<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   SMEM_LIMIT));
-    attr = true;
+    attr.mark(ctx->device);
   }
   const int grid = 2 * std::min(g.tiles, n_pairs);
   switch (pick_store_mode(g, C)) {

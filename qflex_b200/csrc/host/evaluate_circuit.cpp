@@ -138,6 +138,61 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
       }
     }
     if (!planned) *result = BuildPlan(*input, ordering, final_qubits, 0, cut_aware);
+    if (!fits(*result)) return;
+
+    // Then undo as much of the bond-cut slicing as the memory limit allows (BuildPlan's
+    // fuse_bits: 2^f slices per pass of larger kernels), keeping at least one outer
+    // slice per rank of a multi-GPU run.  QFLEX_FUSE_BITS=<n> caps f, 0 = the ordering
+    // as written.  The arena grows monotonically with f, so bisect.
+    const int n_open = result->open_outputs;
+    int max_fuse = 62;
+    if (const char* e = getenv("QFLEX_FUSE_BITS")) max_fuse = std::max(0, atoi(e));
+    double slices = 1;
+    for (const auto& c : result->cuts)
+      if (!c.terminal) slices *= (double)std::max<std::size_t>(1, c.values.size());
+    const int ranks = std::max(1, where.world);
+    if (slices >= ranks) {
+      int cap = 0;
+      while (slices / (double)(uint64_t(2) << cap) >= ranks) ++cap;
+      max_fuse = std::min(max_fuse, cap);
+    }
+    if (max_fuse <= 0) return;
+    auto try_fuse = [&](int f, Plan* out) {
+      try {
+        Plan p = BuildPlan(*input, ordering, final_qubits, n_open, cut_aware, f);
+        if (p.open_outputs != n_open || !fits(p)) return false;
+        *out = std::move(p);
+        return true;
+      } catch (const std::string&) {
+        return false;
+      }
+    };
+    Plan best;
+    int have = 0;
+    {
+      // how many bits the ordering offers at all
+      Plan probe;
+      int offered = 0;
+      try {
+        probe = BuildPlan(*input, ordering, final_qubits, n_open, cut_aware, max_fuse);
+        offered = probe.fused_bits;
+        if (offered > 0 && probe.open_outputs == n_open && fits(probe)) {
+          best = std::move(probe);
+          have = offered;
+        }
+      } catch (const std::string&) {
+        offered = max_fuse;
+      }
+      if (have == 0 && offered > 0) {
+        int lo = 0, hi = std::min(offered, max_fuse);  // lo fits, hi does not
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) / 2;
+          if (try_fuse(mid, &best)) lo = mid, have = mid;
+          else hi = mid;
+        }
+      }
+    }
+    if (have > 0) *result = std::move(best);
   };
   const char* ca_env = getenv("QFLEX_CUT_AWARE_FLATTEN");
   const bool ca_forced = ca_env && ca_env[0] == '1', ca_forbidden = ca_env && ca_env[0] == '0';
@@ -183,9 +238,21 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
     throw ERROR_MSG("Planner produced ", plan.n_amplitudes, " amplitudes for ",
                     prepared->output_states.size(), " output states.");
 
+  for (const auto& q : final_qubits)
+    prepared->output_positions.push_back(find_output_pos(input, q));
   prepared->session = std::make_unique<Session>(std::move(plan), where.device);
   lap("Time spent creating 2D grid of tensors on the device: ");
   return prepared;
+}
+
+void PreparedCircuit::SetFinalState(const std::string& final_state) {
+  if (!session) throw ERROR_MSG("Circuit is not resident.");
+  session->SetFinalState(final_state);
+  for (std::string& s : output_states) {
+    std::string next = final_state;
+    for (const std::size_t p : output_positions) next[p] = s[p];
+    s = std::move(next);
+  }
 }
 
 std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(

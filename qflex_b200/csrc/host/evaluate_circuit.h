@@ -45,6 +45,13 @@ std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
 struct PreparedCircuit {
   std::vector<std::string> output_states;
   std::unique_ptr<Session> session;
+  // positions (in the state strings) of the qubits with a terminal cut
+  std::vector<std::size_t> output_positions;
+
+  // Moves the resident circuit to another final state (Session::SetFinalState) and
+  // rewrites output_states: the terminal-cut positions keep enumerating their values,
+  // every other position takes the new string's character.
+  void SetFinalState(const std::string& final_state);
 };
 std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
                                                 const DevicePlacement& where);

@@ -47,6 +47,10 @@ class Runner {
   uint64_t leaves() const { return leaves_; }
 
   void run(const std::vector<PlanStep>& steps) {
+    // Nothing to deal (no projected cut at all, e.g. a cut-free ordering or one whose
+    // only cuts are open outputs): the whole schedule, accumulate steps included, is
+    // one share and belongs to rank 0 -- the other ranks contribute zeros to the sum.
+    if (share_levels_ == 0 && world_ > 1 && rank_ != 0) return;
     walk(steps, 0, 0, 0, 0);
   }
 
@@ -144,6 +148,10 @@ int choose_lanes(const Plan& plan) {
       lanes = (int)std::min<double>(8.0, (65536.0 * 1048576.0) / arena_bytes);
   }
   lanes = (int)std::min<uint64_t>((uint64_t)std::max(lanes, 1), std::max<uint64_t>(1, slices / 2));
+  // the memory limit bounds ALL scratch of the run (reference --memory,
+  // src/contraction_utils.cpp:205-214), not one lane's arena
+  lanes = (int)std::min<double>(lanes, std::floor((double)global::memory_limit /
+                                                  std::max(arena_bytes, 1.0)));
   return std::max(lanes, 1);
 }
 }  // namespace
@@ -154,14 +162,18 @@ Session::Session(Plan plan, int device) : plan_(std::move(plan)), device_(device
   try {
     const double t0 = now_s();
     const int n_lanes = choose_lanes(plan_);
+    check(qfx_arena_reserve(ctx_, plan_.arena_elems), "qfx_arena_reserve");
+    check(qfx_amps_reserve(ctx_, plan_.n_amplitudes), "qfx_amps_reserve");
     for (int l = 1; l < n_lanes; ++l) {
+      // an extra lane that cannot get its arena is dropped, not fatal
       qfx_ctx* c = nullptr;
-      check(qfx_create(device, &c), "qfx_create");
+      if (qfx_create(device, &c) != QFX_OK) break;
+      if (qfx_arena_reserve(c, plan_.arena_elems) != QFX_OK ||
+          qfx_amps_reserve(c, plan_.n_amplitudes) != QFX_OK) {
+        qfx_destroy(c);
+        break;
+      }
       lanes_.push_back(c);
-    }
-    for (qfx_ctx* c : lanes_) {
-      check(qfx_arena_reserve(c, plan_.arena_elems), "qfx_arena_reserve");
-      check(qfx_amps_reserve(c, plan_.n_amplitudes), "qfx_amps_reserve");
     }
     Upload();
     const double t1 = now_s();
@@ -204,6 +216,27 @@ void Session::Upload() {
   for (qfx_ctx* c : lanes_)
     check(qfx_upload(c, lo, reinterpret_cast<const float*>(staged.data()), staged.size()),
           "qfx_upload");
+}
+
+void Session::SetFinalState(const std::string& final_state) {
+  if (final_state.size() != plan_.final_delta_upload.size())
+    throw ERROR_MSG("Size of final_conf: ", final_state.size(),
+                    ", must be equal to size of initial_conf: ",
+                    plan_.final_delta_upload.size(), ".");
+  for (std::size_t a = 0; a < final_state.size(); ++a) {
+    const int u = plan_.final_delta_upload[a];
+    if (u < 0) continue;  // terminal cut: an output, whatever the string says there
+    const char c = final_state[a];
+    if (c != '0' && c != '1')
+      throw ERROR_MSG("Final state has non-binary character ", c, " at index ", a,
+                      "despite having no terminal cut there.");
+    auto& data = plan_.uploads[u].data;
+    if (data.size() != 2) throw ERROR_MSG("Final delta tensor of qubit ", a, " is malformed.");
+    data[0] = s_type(c == '0' ? 1.f : 0.f, 0.f);
+    data[1] = s_type(c == '1' ? 1.f : 0.f, 0.f);
+  }
+  Upload();
+  Flatten();
 }
 
 void Session::Flatten() {
@@ -258,7 +291,8 @@ void Session::ContractLane(int lane, int rank, int world, std::vector<double>* a
     rows->resize(std::min<int32_t>(n, 256));
   }
   stats->device_ms_contract = ms;
-  stats->leaves = runner.leaves();
+  // a leaf of a plan with fused cut bits covers 2^fused_bits slices of the ordering
+  stats->leaves = runner.leaves() << plan_.fused_bits;
   check(qfx_stats_get(ctx, &stats->device), "qfx_stats_get");
   amps->assign(2 * plan_.n_amplitudes, 0.0);
   check(qfx_amps_download(ctx, amps->data(), plan_.n_amplitudes), "qfx_amps_download");
@@ -282,7 +316,7 @@ void Session::Contract(int rank, int world,
     for (int l = 0; l < L; ++l)
       threads.emplace_back([&, l]() {
         try {
-          ContractLane(l, rank * L + l, world * L, &amps[l], &st[l], &rows[l]);
+          ContractLane(l, l * world + rank, world * L, &amps[l], &st[l], &rows[l]);
         } catch (const std::string& msg) {
           errors[l] = msg.empty() ? std::string("unknown error") : msg;
         } catch (const std::exception& ex) {

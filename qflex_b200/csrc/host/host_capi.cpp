@@ -47,6 +47,10 @@ void fill_stats(const qflex::Session& s, double* out) {
   out[13] = (double)e.device.launches_reduce;
   out[14] = (double)e.device.launches_permute;
   out[15] = (double)p.n_amplitudes;
+  out[16] = (double)p.fused_bits;
+  out[17] = (double)p.open_outputs;
+  out[18] = (double)s.lanes();
+  out[19] = 0.0;
 }
 
 std::string join_states(const std::vector<std::string>& states) {
@@ -85,10 +89,11 @@ extern "C" {
 
 void qflex_b200_set_verbose(int level) { qflex::global::verbose = level; }
 
-void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
-                         const char* grid_text, const char* initial_state,
-                         const char* final_state, uint64_t memory_limit_bytes,
-                         int device, int precision, char* err, uint64_t err_cap) {
+void* qflex_b200_prepare_sharded(const char* circuit_text, const char* ordering_text,
+                                 const char* grid_text, const char* initial_state,
+                                 const char* final_state, uint64_t memory_limit_bytes,
+                                 int device, int precision, int world, char* err,
+                                 uint64_t err_cap) {
   try {
     if (memory_limit_bytes) qflex::global::memory_limit = memory_limit_bytes;
     qflex::QflexInput input;
@@ -96,9 +101,19 @@ void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
     qflex::DevicePlacement where;
     where.device = device;
     where.precision = precision;
+    where.world = world < 1 ? 1 : world;
     return qflex::PrepareCircuit(&input, where).release();
   }
   QFLEX_CAPI_CATCH(nullptr)
+}
+
+void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
+                         const char* grid_text, const char* initial_state,
+                         const char* final_state, uint64_t memory_limit_bytes,
+                         int device, int precision, char* err, uint64_t err_cap) {
+  return qflex_b200_prepare_sharded(circuit_text, ordering_text, grid_text, initial_state,
+                                    final_state, memory_limit_bytes, device, precision, 1, err,
+                                    err_cap);
 }
 
 long qflex_b200_contract(void* prepared, int rank, int world, double* amps_out,
@@ -126,6 +141,16 @@ long qflex_b200_reload(void* prepared, char* err, uint64_t err_cap) {
     auto* p = static_cast<qflex::PreparedCircuit*>(prepared);
     p->session->Upload();
     p->session->Flatten();
+    return 0;
+  }
+  QFLEX_CAPI_CATCH(-1)
+}
+
+long qflex_b200_set_final_state(void* prepared, const char* final_state, char* err,
+                                uint64_t err_cap) {
+  try {
+    if (prepared == nullptr) throw std::string("null handle");
+    static_cast<qflex::PreparedCircuit*>(prepared)->SetFinalState(final_state ? final_state : "");
     return 0;
   }
   QFLEX_CAPI_CATCH(-1)

@@ -345,6 +345,28 @@ struct NeighbourOrder {
 }  // namespace
 
 namespace {
+// Largest j such that the value list of a bond cut is a sequence of aligned blocks
+// {u * 2^j, ..., u * 2^j + 2^j - 1}: the low j bits of the bond then run over their
+// full range inside every block and need not be sliced.
+int fusable_bits(std::vector<std::size_t> values) {
+  // (the order of a cut's values only orders the fp64 sum over its slices)
+  std::sort(values.begin(), values.end());
+  int j = 0;
+  while ((std::size_t(2) << j) <= values.size()) ++j;
+  for (; j > 0; --j) {
+    const std::size_t block = std::size_t(1) << j;
+    if (values.size() % block) continue;
+    bool ok = true;
+    for (std::size_t t = 0; ok && t < values.size(); t += block) {
+      if (values[t] % block) ok = false;
+      for (std::size_t i = 1; ok && i < block; ++i)
+        if (values[t + i] != values[t] + i) ok = false;
+    }
+    if (ok) return j;
+  }
+  return 0;
+}
+
 // a terminal cut whose values are the whole range in natural order can stay open
 bool cut_can_open(const ContractionOperation& op) {
   if (op.op_type != ContractionOperation::CUT || op.cut.tensors.size() != 1) return false;
@@ -358,7 +380,7 @@ bool cut_can_open(const ContractionOperation& op) {
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               int open_outputs, bool cut_aware_flatten) {
+               int open_outputs, bool cut_aware_flatten, int fuse_bits) {
   Plan plan;
   // the LAST `open_outputs` openable terminal cuts of the ordering stay open (a later
   // cut enlarges fewer of the remaining patches)
@@ -453,7 +475,7 @@ Plan BuildPlan(const QflexInput& input,
   // ---------------------------------------------------------- arena: gates
   uint64_t cursor = 0;
   for (std::size_t i = 0; i < I; ++i)
-    for (std::size_t j = 0; j < J; ++j)
+    for (std::size_t j = 0; j < J; ++j) {
       for (auto& g : net[i][j].chain) {
         g.sym.off = cursor;
         PlanUpload up;
@@ -462,6 +484,11 @@ Plan BuildPlan(const QflexInput& input,
         plan.uploads.push_back(std::move(up));
         cursor = align_up(cursor + g.sym.size());
       }
+      if (is_off(i, j)) continue;
+      // build_network closes every world line without a terminal cut with a delta
+      const bool open_leg = find_grid_coord_in_list(final_qubits, i, j);
+      plan.final_delta_upload.push_back(open_leg ? -1 : (int)plan.uploads.size() - 1);
+    }
 
   // ------------------------------------------------- flatten: sizes first
   plan.site.assign(I, std::vector<SymTensor>(J));
@@ -598,6 +625,47 @@ Plan BuildPlan(const QflexInput& input,
       }
     }
 
+  // ------------------------------------------------- fused cut bits
+  // A bond cut slices the contraction over the values of one bond so that the patches
+  // fit the host memory the reference was written for; every slice re-runs the whole
+  // schedule after the cut on tensors 2^bits smaller.  With 180 GB of HBM most of that
+  // slicing is unnecessary: the LOW `j` bits of a cut bond may simply stay an ordinary
+  // index of its two grid tensors (it is contracted when their patches meet, like any
+  // other bond), and only the high bits are projected.  2^j slices then cost one pass of
+  // 2^j-times larger kernels -- steps that do not carry the bond run once instead of
+  // 2^j times -- and the sum over those slices happens inside the merge's K loop.  Same
+  // pairs, same order; `fuse_bits` is the total handed out, innermost cut first.
+  std::map<const ContractionOperation*, int> fuse_of;
+  {
+    int remaining = std::max(fuse_bits, 0);
+    for (auto it = ordering.rbegin(); it != ordering.rend() && remaining > 0; ++it) {
+      const ContractionOperation& op = *it;
+      if (op.op_type != ContractionOperation::CUT || op.cut.tensors.size() != 2) continue;
+      const std::string index = index_name(op.cut.tensors);
+      if (pre_bond.count(index)) continue;  // projected in the gate tensors
+      const auto& pos = op.cut.tensors[0];
+      if (pos.size() != 2 || pos[0] >= I || pos[1] >= J) continue;
+      const SymTensor& t = plan.site[pos[0]][pos[1]];
+      const int p = t.find(index);
+      if (p < 0) continue;
+      std::vector<std::size_t> values = op.cut.values;
+      if (values.empty())
+        for (std::size_t v = 0; v < (std::size_t(1) << t.idx[p].bits); ++v) values.push_back(v);
+      bool in_range = true;
+      for (const auto v : values) in_range = in_range && v < (std::size_t(1) << t.idx[p].bits);
+      if (!in_range) continue;  // reported by the cut itself below
+      const int j = std::min(fusable_bits(values), remaining);
+      if (j > 0) {
+        fuse_of[&op] = j;
+        remaining -= j;
+      }
+    }
+  }
+  auto fused_bits_of = [&](const ContractionOperation& op) {
+    auto it = fuse_of.find(&op);
+    return it == fuse_of.end() ? 0 : it->second;
+  };
+
   // ------------------------------------------------- schedule: patch sizes
   // Symbolic replay (as ContractionData::Initialize does) to size patch slots.
   struct Patch {
@@ -640,10 +708,13 @@ Plan BuildPlan(const QflexInput& input,
         }
       } else if (!cut_stays_open(op, open_outputs)) {
         const std::string index = index_name(op.cut.tensors);
+        const int keep = fused_bits_of(op);
         for (const auto& pos : op.cut.tensors) {
           SymTensor& t = site[pos[0]][pos[1]];
           const int p = t.find(index);
-          if (p >= 0) t.idx.erase(t.idx.begin() + p);
+          if (p < 0) continue;
+          if (keep > 0) t.idx[p].bits = keep;
+          else t.idx.erase(t.idx.begin() + p);
         }
       }
     }
@@ -765,6 +836,7 @@ Plan BuildPlan(const QflexInput& input,
         cut.values = op.cut.values;
         const int cut_id = (int)plan.cuts.size();
         const bool stays_open = cut_stays_open(op, open_outputs);
+        const int keep = fused_bits_of(op);
         int width = -1;
         const bool pre = pre_bond.count(index) != 0;  // already projected in the gates
         if (pre) width = pre_width.count(index) ? pre_width.at(index) : 0;
@@ -781,8 +853,10 @@ Plan BuildPlan(const QflexInput& input,
           }
           width = t.idx[p].bits;
           if (stays_open) continue;
-          t.var.push_back(VarTerm{cut_id, t.idx[p].pos});
-          t.idx.erase(t.idx.begin() + p);
+          if (keep >= width) continue;  // the whole bond stays an index
+          t.var.push_back(VarTerm{cut_id, t.idx[p].pos + keep});
+          if (keep > 0) t.idx[p].bits = keep;  // low bits stay (same position)
+          else t.idx.erase(t.idx.begin() + p);
         }
         if (stays_open) {
           terminals.push_back(Terminal{-1, index, uint64_t(1) << width});
@@ -799,6 +873,16 @@ Plan BuildPlan(const QflexInput& input,
         if (cut.terminal) {
           plan.n_amplitudes *= cut.values.size();
           terminals.push_back(Terminal{cut_id, index, (uint64_t)cut.values.size()});
+        }
+        if (keep > 0) {
+          // one outer value per aligned block of 2^keep values
+          std::vector<std::size_t> outer;
+          std::sort(cut.values.begin(), cut.values.end());
+          for (std::size_t v = 0; v < cut.values.size(); v += std::size_t(1) << keep)
+            outer.push_back(cut.values[v] >> keep);
+          cut.values = std::move(outer);
+          cut.fused_bits = keep;
+          plan.fused_bits += keep;
         }
         plan.cuts.push_back(std::move(cut));
         ++level;

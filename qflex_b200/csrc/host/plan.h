@@ -110,6 +110,9 @@ struct PlanCut {
   // (mixed radix over the terminal cuts in ordering order, first = most significant:
   // output_index * |values| + i of src/contraction_utils.cpp:300-314)
   uint64_t amp_stride = 0;
+  // bond cut: the low `fused_bits` bits of the bond are not sliced (BuildPlan's
+  // fuse_bits); `values` then holds value >> fused_bits of every aligned block
+  int fused_bits = 0;
 };
 
 struct PlanUpload {
@@ -137,6 +140,14 @@ struct Plan {
   int open_outputs = 0;
   // cut-aware flatten: the device computes amplitudes * 2^amp_scale_log2
   int amp_scale_log2 = 0;
+  // Per active qubit (in the order of the state strings): index into `uploads` of the
+  // delta tensor that closes its world line, or -1 when the qubit has a terminal cut
+  // (open output).  Lets a resident circuit move to another final state by rewriting
+  // two floats per qubit (Session::SetFinalState).
+  std::vector<int> final_delta_upload;
+  // sum of PlanCut::fused_bits: one leaf of this plan covers 2^fused_bits slices of
+  // the ordering as written
+  int fused_bits = 0;
 };
 
 // Builds the full plan.  `final_qubits` = qubits with a terminal cut
@@ -158,10 +169,18 @@ struct Plan {
 // Such sites are flattened inside the slice loop (their world-line products become
 // ordinary steps after the leading cuts) instead of once; grid tensors that would
 // not fit (Sycamore m >= 16: four bonds of 2^8..2^10) become representable.
+//
+// `fuse_bits`: how many bits of bond-cut slicing are undone (innermost cut first): the
+// low j bits of a cut bond whose value list consists of aligned blocks of 2^j values
+// stay an ordinary bond of its two grid tensors and are contracted when their patches
+// meet, so 2^j slices of the ordering run as ONE pass of larger kernels (the batched
+// form of the slice loop, src/contraction_utils.cpp:264-316) and steps that do not
+// carry the bond run once instead of 2^j times.  Patches that carry it grow 2^j-fold;
+// the caller hands out as many bits as fit the memory limit.
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               int open_outputs = 0, bool cut_aware_flatten = false);
+               int open_outputs = 0, bool cut_aware_flatten = false, int fuse_bits = 0);
 
 struct ExecStats {
   double seconds_upload = 0, seconds_flatten = 0, seconds_contract = 0;
@@ -184,9 +203,16 @@ class Session {
 
   void Upload();   // host -> device copy of the gate tensors
   void Flatten();  // network -> grid tensors, on the device
+  // Another output bitstring on the same resident circuit: rewrites the delta tensors
+  // that close the world lines (positions of qubits with a terminal cut are ignored),
+  // re-uploads the gate tensors and flattens again -- parse, plan, arena and the
+  // contraction schedule are reused.  What a batch of final states needs
+  // (src/pybind_main.cpp:49-73,111-113 parses such a list and rejects it).
+  void SetFinalState(const std::string& final_state);
   void Contract(int rank, int world, std::vector<std::complex<double>>* amplitudes);
 
   const Plan& plan() const { return plan_; }
+  int lanes() const { return (int)lanes_.size(); }
   const ExecStats& stats() const { return stats_; }
 
   // Per-launch device timing of the next Contract() calls, by shape class
@@ -205,7 +231,8 @@ class Session {
   // Lanes: extra contexts (own arena + stream) on the SAME device.  Small networks
   // (arena of MBs, contractions of microseconds) leave most SMs idle and are bound
   // by launch latency; their cut slices are independent, so the slices of this rank
-  // are dealt once more over the lanes (lane l acts as rank rank*L+l of world*L),
+  // are dealt once more over the lanes (lane l acts as rank l*world+rank of world*L:
+  // lane-major, so that few slices still reach every rank),
   // each driven by its own host thread, and kernels of different slices overlap on
   // the GPU.  One lane when the arena is large (the kernels fill the GPU).
   std::vector<qfx_ctx*> lanes_;

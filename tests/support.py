@@ -77,6 +77,10 @@ CASES = {
                          grid="rectangular_2x2.txt", final="0000"),
     "rect2x2_0110": dict(circuit="rectangular_2x2_1-2-1_0.txt", ordering="rectangular_2x2.txt",
                          grid="rectangular_2x2.txt", final="0110"),
+    # no cut at all: nothing to deal over ranks (executor.cpp rank shares)
+    "rect2x2_cutfree_0110": dict(
+        circuit="rectangular_2x2_1-2-1_0.txt", grid="rectangular_2x2.txt", final="0110",
+        ordering_text="expand A 0\nexpand A 1\nexpand B 2\nexpand B 3\nmerge A B\n"),
     "sycamore_53_4": dict(circuit="sycamore_53_4_0.txt", ordering="sycamore_53.txt",
                           grid="sycamore_53.txt"),
     "bristlecone_70_1-12-1": dict(circuit="bristlecone_70_1-12-1_0.txt",
@@ -108,6 +112,15 @@ CASES = {
     "sycamore_53_10_1slice": dict(
         circuit="sycamore_53_10_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         cut_values=[[3], [7], [11]]),
+    # BASELINE configs[1] itself (the bench headline): bristlecone_70 1-32-1, one and two
+    # of its 65536 slices (2^20 x 256 x 256 expands, 2^28-element patches; 6.3 GB and
+    # ~14-60 s per slice on the reference)
+    "bristlecone_70_1-32-1_1slice": dict(
+        circuit="bristlecone_70_1-32-1_0.txt", ordering="bristlecone_70.txt",
+        grid="bristlecone_70.txt", cut_values=[[0], [0], [0], [0]]),
+    "bristlecone_70_1-32-1_2slices": dict(
+        circuit="bristlecone_70_1-32-1_0.txt", ordering="bristlecone_70.txt",
+        grid="bristlecone_70.txt", cut_values=[[2], [9], [4], [0, 15]]),
     # 16 of the 4096 slices of config[1]'s little brother
     "bristlecone_70_1-24-1_16slices": dict(
         circuit="bristlecone_70_1-24-1_0.txt", ordering="bristlecone_70.txt",

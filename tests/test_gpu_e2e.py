@@ -58,13 +58,108 @@ def test_projected_and_partly_open_outputs_match_golden(gpu_lib, golden, monkeyp
     assert support.rel_err([a for _, a in res2], [a for _, a in res]) < TOL
 
 
-@pytest.mark.parametrize("precision", ["ffma"])
-def test_precision_modes_agree(gpu_lib, golden, precision):
-    case = support.CASES["bristlecone_48_1-24-1"]
+@pytest.mark.parametrize("precision", ["ffma", "bf16x3", "auto"])
+@pytest.mark.parametrize("name", ["bristlecone_48_1-24-1", "sycamore_53_8_64amps"])
+def test_precision_modes_agree(gpu_lib, golden, precision, name):
+    case = support.CASES[name]
     c, o, g = support.case_texts(case)
-    res, _ = gpu_lib.evaluate(c, o, g, memory_limit=8 << 30, precision=precision)
-    _, want = _amps(golden, "bristlecone_48_1-24-1")
+    res, st = gpu_lib.evaluate(c, o, g, memory_limit=8 << 30, precision=precision)
+    _, want = _amps(golden, name)
     assert support.rel_err([a for _, a in res], want) < TOL
+    if precision == "ffma":
+        assert st["launches_gemm_tc"] == 0
+    if precision == "bf16x3" and name == "sycamore_53_8_64amps":
+        assert st["launches_gemm_tc"] > 0
+
+
+@pytest.mark.parametrize("precision", ["auto", "ffma"])
+def test_headline_workload_one_slice_matches_reference(gpu_lib, golden, precision):
+    """BASELINE configs[1] itself, the circuit bench.py times: bristlecone_70 1-32-1, one
+    of its 65536 slices, against the unmodified reference's amplitude (71 s and 6.3 GB
+    there), through the tensor-core path (2^20 x 256 x 256 on tc_pair) and through FFMA."""
+    name = "bristlecone_70_1-32-1_1slice"
+    c, o, g = support.case_texts(support.CASES[name])
+    res, st = gpu_lib.evaluate(c, o, g, memory_limit=64 << 30, precision=precision)
+    states, want = _amps(golden, name)
+    assert [s for s, _ in res] == states
+    assert support.rel_err([a for _, a in res], want) < TOL
+    assert (st["launches_gemm_tc"] > 0) == (precision == "auto")
+
+
+FUSED_GOLDENS = ["bristlecone_70_1-24-1_16slices", "bristlecone_70_1-16-1", "bristlecone_48_1-24-1",
+                 "sycamore_53_4", "sycamore_53_8_64amps", "rect7x7_1-32-1_4amps"]
+
+
+@pytest.mark.parametrize("name", FUSED_GOLDENS)
+def test_sliced_and_fused_plans_match_golden(gpu_lib, golden, monkeypatch, name):
+    """The default plan undoes bond-cut slicing as far as memory allows (2^f slices per
+    pass); QFLEX_FUSE_BITS=0 executes the ordering slice by slice as the reference
+    does.  Both against the reference's amplitudes."""
+    case = support.CASES[name]
+    texts = support.case_texts(case)
+    args = (case.get("initial", ""), case.get("final", ""))
+    states, want = _amps(golden, name)
+    fused, st1 = gpu_lib.evaluate(*texts, *args, memory_limit=64 << 30)
+    monkeypatch.setenv("QFLEX_FUSE_BITS", "0")
+    sliced, st0 = gpu_lib.evaluate(*texts, *args, memory_limit=64 << 30)
+    assert [s for s, _ in fused] == states == [s for s, _ in sliced]
+    assert support.rel_err([a for _, a in fused], want) < TOL
+    assert support.rel_err([a for _, a in sliced], want) < TOL
+    assert st0["fused_bits"] == 0 and st0["leaves"] == st1["leaves"]
+    if st1["fused_bits"] > 0:
+        assert st1["launches"] < st0["launches"]
+
+
+CUT_AWARE_GOLDENS = ["bristlecone_70_1-24-1_16slices", "sycamore_53_8_64amps",
+                     "sycamore_53_10_1slice", "bristlecone_48_1-24-1", "rect7x7_1-32-1_4amps"]
+
+
+@pytest.mark.parametrize("name", CUT_AWARE_GOLDENS)
+def test_cut_aware_flatten_matches_reference_golden(gpu_lib, golden, monkeypatch, name):
+    """The cut-aware flatten (leading bond cuts projected in the gate tensors, the sites
+    next to them flattened inside the slice loop; what replaces src/read_circuit.cpp:
+    548-689 for Sycamore m >= 14) forced on circuits the reference can run: the CUDA path
+    against the reference's amplitudes, not against another kernel of this engine."""
+    _trim_parked_buffers()
+    monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", "1")
+    case = support.CASES[name]
+    res, st = gpu_lib.evaluate(*support.case_texts(case), case.get("initial", ""),
+                               case.get("final", ""), memory_limit=64 << 30)
+    states, want = _amps(golden, name)
+    assert [s for s, _ in res] == states
+    assert support.rel_err([a for _, a in res], want) < TOL
+
+
+@pytest.mark.parametrize("name,max_log2", [("sycamore_53_8_64amps", 19), ("sycamore_53_10_1slice", 28),
+                                           ("bristlecone_70_1-24-1_16slices", 18)])
+def test_augmented_ordering_sums_to_the_golden(gpu_lib, golden, monkeypatch, name, max_log2):
+    """tools/augment_ordering.py picks the bond cuts that make every intermediate fit
+    2^max_log2 elements.  With its FIRST pick added on top of the shipped ordering and
+    summed over ALL values of that extra cut, the amplitudes are still the golden's:
+    slice by slice, with the slicing fused back, and with the cut-aware flatten (the
+    configuration Sycamore m >= 14 runs in, where nothing else pins the amplitudes)."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location(
+        "augment_ordering", os.path.join(support.ROOT, "tools", "augment_ordering.py"))
+    tool = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(tool)
+    case = support.CASES[name]
+    c, o, g = support.case_texts(case)
+    _, info = tool.augment(c, g, o, max_log2)
+    assert info["added"], "the limit must force extra cuts"
+    o2 = "cut () %d %d\n" % tuple(info["added"][0]) + o
+    states, want = _amps(golden, name)
+    base_leaves = None
+    for cut_aware, fuse in (("0", "0"), ("0", "62"), ("1", "0")):
+        _trim_parked_buffers()
+        monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", cut_aware)
+        monkeypatch.setenv("QFLEX_FUSE_BITS", fuse)
+        res, st = gpu_lib.evaluate(c, o2, g, memory_limit=64 << 30)
+        assert [s for s, _ in res] == states
+        assert support.rel_err([a for _, a in res], want) < TOL, (cut_aware, fuse, info["added"])
+        base_leaves = base_leaves or st["leaves"]
+        assert st["leaves"] == base_leaves and st["leaves"] >= 2 * len(states)
 
 
 @pytest.mark.parametrize("world", [2, 8])

@@ -309,3 +309,64 @@ def test_contract_chains_runs_independent_world_lines_in_one_launch():
         got = ctx.download(off, want.size)
         assert support.rel_err(got, want) < 1e-5
     ctx.close()
+
+
+def test_copy_and_scalar_accumulate(ctx):
+    """qfx_copy (Tensor::operator= / _copy, src/tensor.cpp:107-139) and
+    qfx_scalar_accumulate (`amplitudes[i] += *output->data()`,
+    src/contraction_utils.cpp:348-352) called directly."""
+    rng = np.random.default_rng(5)
+    n = 70001  # odd length, not a multiple of the vector width
+    a = _rand(n, rng)
+    ctx.reserve(3 * n + 64)
+    ctx.upload(0, a)
+    ctx.upload(n + 7, np.zeros(n, dtype=np.complex64))
+    ctx.copy(0, n + 7, n)
+    assert np.array_equal(ctx.download(n + 7, n), a)
+    assert np.array_equal(ctx.download(0, n), a)
+    ctx.copy(3, 2 * n + 20, 1)
+    assert ctx.download(2 * n + 20, 1)[0] == a[3]
+    ctx.amps_reserve(4)
+    for slot, offs in ((0, [1, 5, 9]), (3, [2, 2]), (2, [])):
+        for off in offs:
+            ctx.scalar_accumulate(off, slot)
+    got = ctx.amps(4)
+    want = np.array([a[1].astype(np.complex128) + a[5] + a[9], 0, 0, 2 * a[2].astype(np.complex128)])
+    assert np.array_equal(got, want)  # complex64 -> complex128 sums of <= 3 terms are exact
+    with pytest.raises(Exception):
+        ctx.scalar_accumulate(1, 4)      # slot outside the table
+    with pytest.raises(Exception):
+        ctx.copy(0, 3 * n + 64, 8)       # destination outside the arena
+
+
+def test_headline_shape_full_size_rows_against_oracle(ctx):
+    """The class that carries 70 % of bristlecone_70 1-32-1: 2^20 x 256 x 256 on the
+    CTA-pair tensor-core kernel, at FULL size; 2048 rows sampled over the whole range
+    are recomputed by the oracle in complex128."""
+    from qflex_b200 import _device
+    m, n, k = 20, 8, 8
+    rng = np.random.default_rng(2032)
+    t = dict(a_k=list(range(k)), a_m=list(range(k, k + m)), b_n=list(range(n)),
+             b_k=list(range(n, n + k)), c_n=list(range(n)), c_m=list(range(n, n + m)))
+    sa, sb, sc = 1 << (m + k), 1 << (n + k), 1 << (m + n)
+    a = (rng.standard_normal(2 * sa, dtype=np.float32)).view(np.complex64)
+    b = (rng.standard_normal(2 * sb, dtype=np.float32)).view(np.complex64)
+    oa, ob, oc = 0, sa + 32, sa + sb + 64
+    ctx.reserve(oc + sc + 64)
+    ctx.upload(oa, a)
+    ctx.upload(ob, b)
+    before = ctx.stats()
+    ctx.contract(_device.make_desc(oa, ob, oc, t["a_m"], t["c_m"], t["b_n"], t["c_n"],
+                                   t["a_k"], t["b_k"]))
+    after = ctx.stats()
+    assert after["launches_gemm_tc"] - before["launches_gemm_tc"] == 1
+    rows = np.unique(np.concatenate([rng.integers(0, 1 << m, 2040), [0, 127, 128, 255, 256,
+                                                                      (1 << m) - 1, (1 << m) - 256, 1 << 19]]))
+    A = a.reshape(1 << m, 1 << k)
+    B = b.reshape(1 << k, 1 << n).astype(np.complex128)
+    worst = 0.0
+    for r in rows:
+        got = ctx.download(oc + (int(r) << n), 1 << n)
+        want = A[r].astype(np.complex128) @ B
+        worst = max(worst, support.rel_err(got, want))
+    assert worst < 2e-5, worst

@@ -201,7 +201,7 @@ def test_kernels_are_sm100a_sass():
     assert "sm_100a" in out.stdout
 
 
-def test_augmented_ordering_keeps_the_amplitudes(emul, golden):
+def test_augmented_ordering_keeps_the_amplitudes(emul, golden, monkeypatch):
     """tools/augment_ordering.py: bond cuts added until every intermediate fits; the
     planner's sizes agree with the tool's graph replay and the amplitudes (sums over
     the extra slices) do not move."""
@@ -223,7 +223,8 @@ def test_augmented_ordering_keeps_the_amplitudes(emul, golden):
     assert support.rel_err(np.array([v for _, v in res]), want) < TOL
     res0, st0 = emul.evaluate(c, o, g, memory_limit=8 << 30)
     assert st["leaves"] == 4 * st0["leaves"]  # the cut bond has dimension 4
-    # the tool's flop count per slice is the planner's
+    # the tool's flop count per slice is the planner's (ordering as written)
+    monkeypatch.setenv("QFLEX_FUSE_BITS", "0")
     p = emul.prepare(c, o, g, memory_limit=8 << 30)
     p.contract()
     assert abs(p.stats["flops_per_pass"] - info0["flops_per_slice"]) < 0.05 * info0["flops_per_slice"]  # the tool ignores output indices
@@ -240,6 +241,7 @@ def test_cut_aware_flatten_is_bit_identical(emul, monkeypatch, name):
     case = support.CASES[name]
     texts = support.case_texts(case)
     args = (case.get("initial", ""), case.get("final", ""))
+    monkeypatch.setenv("QFLEX_FUSE_BITS", "0")  # slice by slice, as the ordering is written
     r0, s0 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
     monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", "1")
     r1, s1 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
@@ -248,3 +250,89 @@ def test_cut_aware_flatten_is_bit_identical(emul, monkeypatch, name):
                        for l in texts[1].splitlines() if l.split("#")[0].strip())
     if has_bond_cut:
         assert s1["launches"] > s0["launches"] and s1["arena_bytes"] < s0["arena_bytes"]
+
+
+FUSE_CASES = ["test", "simple_1100x", "sycamore_53_4", "bristlecone_70_1-12-1",
+              "bristlecone_48_1-16-1", "rect2x2_0000"]
+
+
+@pytest.mark.parametrize("name", FUSE_CASES)
+def test_fused_cut_bits_keep_the_amplitudes(emul, golden, monkeypatch, name):
+    """The planner undoes bond-cut slicing as far as the memory limit allows (low bits
+    of a cut bond stay an ordinary bond): fewer, larger launches, the same amplitudes
+    and the same leaf count as the ordering executed slice by slice (QFLEX_FUSE_BITS=0)."""
+    case = support.CASES[name]
+    texts = support.case_texts(case)
+    args = (case.get("initial", ""), case.get("final", ""))
+    states, want = _amps(golden, name)
+    monkeypatch.setenv("QFLEX_FUSE_BITS", "0")
+    r0, s0 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
+    assert s0["fused_bits"] == 0
+    monkeypatch.delenv("QFLEX_FUSE_BITS")
+    r1, s1 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
+    assert [s for s, _ in r1] == states == [s for s, _ in r0]
+    assert support.rel_err([a for _, a in r1], want) < TOL
+    assert support.rel_err([a for _, a in r1], [a for _, a in r0]) < 1e-5
+    assert s1["leaves"] == s0["leaves"]
+    has_bond_cut = any(l.split("#")[0].strip().startswith("cut") and len(l.split(")")[1].split()) == 2
+                       for l in texts[1].splitlines() if l.split("#")[0].strip())
+    if has_bond_cut:
+        assert s1["fused_bits"] > 0 and s1["launches"] < s0["launches"]
+        assert s1["flops"] <= s0["flops"]
+    # one bit at a time: every intermediate setting is the same sum
+    monkeypatch.setenv("QFLEX_FUSE_BITS", "1")
+    r2, s2 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
+    assert s2["fused_bits"] <= 1 and support.rel_err([a for _, a in r2], want) < TOL
+
+
+def test_fusion_respects_the_memory_limit_and_the_rank_count(emul, golden):
+    case = support.CASES["bristlecone_70_1-12-1"]
+    c, o, g = support.case_texts(case)
+    full = emul.prepare(c, o, g, memory_limit=8 << 30)
+    full.contract()
+    small = emul.prepare(c, o, g, memory_limit=1500000)
+    small.contract()
+    assert small.stats["arena_bytes"] <= 1500000
+    assert small.stats["fused_bits"] < full.stats["fused_bits"]
+    _, want = _amps(golden, "bristlecone_70_1-12-1")
+    # planned for 8 ranks: at least 8 slices stay apart, every rank gets a share
+    p8 = emul.prepare(c, o, g, memory_limit=8 << 30, world=8)
+    parts, shares = np.zeros(len(want), dtype=complex), []
+    for r in range(8):
+        parts += p8.contract(r, 8)
+        shares.append(p8.stats["leaves"])
+    assert min(shares) > 0 and sum(shares) == full.stats["leaves"]
+    assert p8.stats["fused_bits"] == full.stats["fused_bits"] - 3
+    assert support.rel_err(parts, want) < TOL
+    for p in (full, small, p8):
+        p.close()
+
+
+def test_unaligned_cut_values_are_not_fused(emul, golden):
+    name = "sycamore_53_8_2slices_64amps"   # first cut: values (3, 12)
+    case = support.CASES[name]
+    res, st = emul.evaluate(*support.case_texts(case), memory_limit=8 << 30)
+    assert st["fused_bits"] == 0
+    _, want = _amps(golden, name)
+    assert support.rel_err([a for _, a in res], want) < TOL
+
+
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("ordering", ["cut_free", "terminal_only"])
+def test_rank_shares_without_a_dealt_cut(emul, world, ordering):
+    """with no projected cut the accumulate steps ran on every rank and the
+    all-reduce returned world x the amplitudes."""
+    import json
+    fix = json.load(open(os.path.join(support.ROOT, "tests", "golden", "simulation_fixtures.json")))
+    c, g = fix["circuit_test_fsim"], fix["grid_2x2_test"]
+    o = "\n".join(l for l in fix["ordering_2x2_test"].splitlines() if not l.startswith("cut"))
+    final = "0110"
+    if ordering == "terminal_only":
+        o = "cut () 3\ncut () 2\n" + o
+        final = "01xx"
+    p = emul.prepare(c, o, g, "", final)
+    full = p.contract(0, 1).copy()
+    assert np.linalg.norm(full) > 0
+    total = sum(p.contract(r, world) for r in range(world))
+    assert support.rel_err(total, full) < 1e-12
+    p.close()

@@ -23,11 +23,12 @@ dist.init_process_group("gloo")
 lib = support.emulated_host_library()
 case = support.CASES[%(case)r]
 c, o, g = support.case_texts(case)
-p = lib.prepare(c, o, g, memory_limit=8 << 30)
+ini, fin = case.get("initial", ""), case.get("final", "")
+p = lib.prepare(c, o, g, ini, fin, memory_limit=8 << 30, world=dist.get_world_size())
 full = sharded.contract_sharded(p)
 leaves = p.stats["leaves"]
 p.close()
-res, _ = sharded.evaluate_sharded(lib, c, o, g, memory_limit=8 << 30)
+res, _ = sharded.evaluate_sharded(lib, c, o, g, ini, fin, memory_limit=8 << 30)
 print("RESULT " + json.dumps({"rank": dist.get_rank(), "leaves": leaves,
       "re": full.real.tolist(), "im": full.imag.tolist(),
       "ev_states": [s for s, _ in res],
@@ -76,6 +77,17 @@ def test_two_ranks_allreduce_to_the_reference_amplitudes(golden):
         assert support.rel_err(ev, want) < 1e-4
     # the all-reduce leaves the same table on both ranks
     assert outs[0]["re"] == outs[1]["re"] and outs[0]["im"] == outs[1]["im"]
+
+
+def test_orderings_without_a_dealt_cut_are_not_counted_twice(golden):
+    """No cut at all: the whole schedule is one share; rank 0 runs it, rank 1 adds zeros."""
+    outs = _run_world("rect2x2_cutfree_0110", 2)
+    g = golden["rect2x2_cutfree_0110"]
+    want = np.array(g["re"]) + 1j * np.array(g["im"])
+    for o in outs:
+        assert support.rel_err(np.array(o["re"]) + 1j * np.array(o["im"]), want) < 1e-4
+        assert support.rel_err(np.array(o["ev_re"]) + 1j * np.array(o["ev_im"]), want) < 1e-4
+    assert sorted(o["leaves"] for o in outs) == [0, len(want)]
 
 
 def test_single_process_is_the_identity_collective(emul, golden):
