@@ -1,17 +1,22 @@
 #!/usr/bin/env python
 """Headline benchmark: contraction throughput on BASELINE.json configs[1]
-(bristlecone_70 depth 1-32-1 with the shipped ordering; a FIXED SUBSET of its
-65536 cut-slices, 8 slices per GPU, selected through cut value lists exactly as
-SURVEY 8d prescribes, identically for this engine and for the reference).
+(bristlecone_70 depth 1-32-1 with the shipped ordering).  The job is a FIXED SUBSET of
+its 65536 cut-slices -- 64 slices selected through cut value lists exactly as SURVEY 8d
+prescribes, the same 64 whatever the GPU count (STRONG scaling: the slices are dealt
+over the ranks, one all-reduce of the amplitude table per step).
 
   python bench.py --gpus N --steps K --warmup W            (our arm)
   python bench.py --impl reference --gpus N --steps K --warmup W   (CPU reference arm)
 
-A step = one pass of the schedule over this rank's slices.  `value` is measured
-with the network resident in HBM (gate tensors uploaded, grid tensors
-flattened); `e2e` is the same metric through qflex_b200_evaluate (the
-EvaluateCircuit C-ABI call) with HOST text buffers: parse + plan + host->device
-upload + flatten + contract + device->host amplitudes inside the timed region.
+A step = one pass of the schedule over the job's slices.  `value` is measured with the
+network resident in HBM (gate tensors uploaded, grid tensors flattened) and counts the
+job's algorithmic flops ONCE (work replicated on several ranks is not counted twice);
+`e2e` is the same metric through qflex_b200_evaluate (the EvaluateCircuit C-ABI call)
+with HOST text buffers: parse + plan + host->device upload + flatten + contract +
+device->host amplitudes inside the timed region.
+
+The reference arm and the cpu_baseline leg run the UNMODIFIED reference (oracle/_ref,
+built by oracle/Makefile) on the box's host cores; they load nothing of the product.
 """
 import argparse
 import json
@@ -24,59 +29,64 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+CONFIG = os.path.join(ROOT, "config")
 
-SLICES_PER_GPU = 8
 WORKLOADS = {
-    # name -> (circuit, ordering, grid, cut value lists per world size)
+    # name -> files, cut value lists ("all": the same job at every world size = strong
+    # scaling; per-world lists = weak scaling), the bounded sample the reference is timed on
+    # BASELINE configs[1], the headline: 64 of the 65536 slices
     "bristlecone_70_1-32-1": dict(
+        circuit="bristlecone_70_1-32-1_0.txt", ordering="bristlecone_70.txt",
+        grid="bristlecone_70.txt", scaling="strong",
+        cuts={"all": [[0, 1, 2, 3], [0, 1, 2, 3], [0, 1], [0, 1]]},
+        reference_sample=[[0], [0], [0], [0]], golden="bristlecone_70_1-32-1_1slice",
+        sweep_proxy="bristlecone_70_1-24-1", memory=64 << 30, total_slices=65536),
+    # the round-1 form of the headline: 8 slices per GPU (weak scaling)
+    "bristlecone_70_1-32-1_weak": dict(
         circuit="bristlecone_70_1-32-1_0.txt", ordering="bristlecone_70.txt",
         grid="bristlecone_70.txt",
         cuts={1: [[0, 1], [0, 1], [0, 1], [0]], 2: [[0, 1], [0, 1], [0, 1], [0, 1]],
               4: [[0, 1], [0, 1], [0, 1], [0, 1, 2, 3]],
               8: [[0, 1], [0, 1], [0, 1, 2, 3], [0, 1, 2, 3]]},
-        reference_sample=[[0], [0], [0], [0]], memory=64 << 30, total_slices=65536),
+        reference_sample=[[0], [0], [0], [0]], golden="bristlecone_70_1-32-1_1slice",
+        sweep_proxy="bristlecone_70_1-24-1", memory=64 << 30, total_slices=65536),
+    # BASELINE configs[0]: the whole circuit the reference's CI runs (2 slices x 4 amplitudes)
+    "bristlecone_48_1-24-1": dict(
+        circuit="bristlecone_48_1-24-1_0.txt", ordering="bristlecone_48.txt",
+        grid="bristlecone_48.txt", scaling="strong", cuts={"all": None},
+        reference_sample="all", golden="bristlecone_48_1-24-1", memory=8 << 30, total_slices=2),
     "bristlecone_70_1-24-1": dict(
         circuit="bristlecone_70_1-24-1_0.txt", ordering="bristlecone_70.txt",
-        grid="bristlecone_70.txt",
-        cuts={1: [[0, 1], [0, 1], [0, 1], [0]], 2: [[0, 1], [0, 1], [0, 1], [0, 1]],
-              4: [[0, 1], [0, 1], [0, 1], [0, 1, 2, 3]],
-              8: [[0, 1], [0, 1], [0, 1, 2, 3], [0, 1, 2, 3]]},
+        grid="bristlecone_70.txt", scaling="strong",
+        cuts={"all": [[0, 1, 2, 3], [0, 1, 2, 3], [0, 1], [0, 1]]},
         reference_sample=[[0, 1], [0, 1], [0, 1], [0]], memory=8 << 30, total_slices=4096),
-    # BASELINE configs[4] stand-in (m=20 is not representable): Sycamore-53
-    # m=10, a low-fidelity batch of 64 of its 16384 slices, STRONG scaling (the same
-    # 64 slices whatever the GPU count)
+    # BASELINE configs[4] stand-in: Sycamore-53 m=10, a low-fidelity batch of 64 of its
+    # 16384 slices, strong scaling
     "sycamore_53_10": dict(
         circuit="sycamore_53_10_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1, 2, 3], [0, 1, 2, 3], [0, 1, 2, 3]]},
         reference_sample=[[0], [0], [0]], memory=100 << 30, total_slices=16384),
-    # one step up from the m=10 stand-in: Sycamore-53 m=12 (29.6 GB arena here, 7.1e14
-    # flop per slice; the reference cannot hold its patches in this host's memory), 8
-    # of its slices, strong scaling
+    # Sycamore-53 m=12 (29.6 GB arena here, 7.1e14 flop per slice; the reference cannot
+    # hold its patches in this host's memory), 8 of its slices, strong scaling
     "sycamore_53_12": dict(
         circuit="sycamore_53_12_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1], [0, 1], [0, 1]]},
         reference_sample=None, memory=100 << 30, total_slices=None),
-    # BASELINE configs[2] as named: Sycamore-53 m=14.  The shipped 3-cut ordering needs
-    # a 2^44-element patch; config/ordering/sycamore_53_m14.txt = that ordering plus the
-    # six bond cuts tools/augment_ordering.py adds for a 2^30 limit (largest tensor
-    # 2^28, 2.45e14 flop per slice, 2^58 slices, 81 GB arena: the flattened grid
-    # tensors).  8 slices x 64 output bitstrings, strong scaling.
+    # BASELINE configs[2] as named: Sycamore-53 m=14 with config/ordering/sycamore_53_m14.txt
+    # (shipped ordering + six bond cuts from tools/augment_ordering.py; 2^58 slices, 81 GB
+    # arena).  8 slices x 64 output bitstrings, strong scaling.
     "sycamore_53_14": dict(
         circuit="sycamore_53_14_0.txt", ordering="sycamore_53_m14.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1]] * 3 + [[0]] * 6 + [[0, 1]] * 6},
         reference_sample=None, memory=160 << 30, total_slices=2.0 ** 58),
-    # Sycamore-53 m=16: shipped ordering + 22 bond cuts (largest tensor 2^24, 2^200
-    # slices, 4.6 GB), cut-aware flatten; 64 slices x 64 bitstrings, strong scaling
+    # Sycamore-53 m=16: shipped ordering + 22 bond cuts, cut-aware flatten; 64 slices x
+    # 64 bitstrings, strong scaling
     "sycamore_53_16": dict(
         circuit="sycamore_53_16_0.txt", ordering="sycamore_53_m16.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1, 2, 3]] * 3 + [[0]] * 22 + [[0, 1]] * 6},
         reference_sample=None, memory=64 << 30, total_slices=2.0 ** 200),
-    # BASELINE configs[4] as named: Sycamore-53 m=20, heavily sliced.  Its grid tensors
-    # (four bonds of 2^10) are not representable; config/ordering/sycamore_53_m20.txt =
-    # the shipped ordering + 36 bond cuts (tools/augment_ordering.py --max-log2 30
-    # --extra 14: largest tensor 2^30, 2^390 slices) and the planner's cut-aware
-    # flatten projects them in the gate tensors (120 GB arena).  8 of the slices x 64
-    # output bitstrings, strong scaling.
+    # BASELINE configs[4] as named: Sycamore-53 m=20 (+36 bond cuts, cut-aware flatten,
+    # 120 GB arena).  8 of the slices x 64 output bitstrings, strong scaling.
     "sycamore_53_20": dict(
         circuit="sycamore_53_20_0.txt", ordering="sycamore_53_m20.txt", grid="sycamore_53.txt",
         scaling="strong", cuts={"all": [[0, 1]] * 3 + [[0]] * 36 + [[0, 1]] * 6},
@@ -94,10 +104,8 @@ WORKLOADS = {
         grid="rectangular_7x7.txt", scaling="strong",
         cuts={"all": [list(range(16)), [0, 1, 2, 3]] + [[0, 1]] * 6},
         reference_sample=[[0], [0]] + [[0, 1]] * 6, memory=16 << 30, total_slices=256),
-    # BASELINE configs[3] as named: 7x7 depth 1-40-1 (bond dimension 32; two bond cuts
-    # of 32 values each = 1024 slices).  64.2 GB arena here (the reference's buffer
-    # scheme needs 72 GB and ~7e14 flop per slice: it is not timed on the host).
-    # 64 output bitstrings per slice; slices grow with the GPU count (weak scaling).
+    # BASELINE configs[3] as named: 7x7 depth 1-40-1 (two bond cuts of 32 values = 1024
+    # slices; 64 GB arena).  64 output bitstrings per slice; weak scaling.
     "rectangular_7x7_1-40-1": dict(
         circuit="rectangular_7x7_1-40-1_0.txt", ordering="rectangular_7x7_v2.txt",
         grid="rectangular_7x7.txt",
@@ -105,16 +113,37 @@ WORKLOADS = {
               4: [[0, 1], [0, 1]] + [[0, 1]] * 6, 8: [[0, 1, 2, 3], [0, 1]] + [[0, 1]] * 6},
         reference_sample=None, memory=160 << 30, total_slices=1024),
 }
+FLOPS_CACHE = os.path.join(ROOT, "bench_reference_flops.json")
 
 
 def workload_cuts(w, world):
-    return w["cuts"].get("all") or w["cuts"][world]
+    return w["cuts"]["all"] if "all" in w["cuts"] else w["cuts"][world]
+
+
+def restrict_cuts(ordering_text, values_per_cut):
+    """Value list of the k-th `cut` line := values_per_cut[k] (same rewrite as
+    qflex_b200.restrict_cuts; repeated here so that the reference arm imports nothing of
+    the product)."""
+    import re
+    out, k = [], 0
+    for line in ordering_text.splitlines():
+        if line.strip().startswith("cut"):
+            if k < len(values_per_cut) and values_per_cut[k] is not None:
+                vals = ",".join(str(v) for v in values_per_cut[k])
+                line = re.sub(r"\([0-9,\s]*\)", "(" + vals + ")", line, count=1)
+            k += 1
+        out.append(line)
+    return "\n".join(out) + "\n"
 
 
 def load_texts(w, cut_values):
-    from tests import support
-    return support.case_texts(dict(circuit=w["circuit"], ordering=w["ordering"], grid=w["grid"],
-                                   cut_values=cut_values))
+    def read(kind, name):
+        with open(os.path.join(CONFIG, kind, name)) as f:
+            return f.read()
+    o = read("ordering", w["ordering"])
+    if cut_values not in (None, "all"):
+        o = restrict_cuts(o, cut_values)
+    return read("circuits", w["circuit"]), o, read("grid", w["grid"])
 
 
 def measured_peaks():
@@ -172,62 +201,97 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def cpu_reference_run(w, cut_values, threads):
-    """Times the UNMODIFIED reference (oracle/_ref) on `cut_values` in a child
-    process (thread env must be set before OpenBLAS/libgomp load).  Returns
-    (seconds, n_slices) of its EvaluateCircuit."""
+# ---------------------------------------------------------------- reference (CPU) legs
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_reference_run(wname, cut_values, omp, blas, wait="passive", timeout=3000):
+    """Times the UNMODIFIED reference (oracle/_ref) on `cut_values` of workload `wname`
+    in a child process (thread settings must be in the environment before OpenBLAS and
+    libgomp load; the child imports oracle/ref_run.py only).  Returns
+    (seconds of its EvaluateCircuit, n_slices, [[re, im]...])."""
     code = (
         "import sys, json; sys.path.insert(0, %r)\n"
-        "from tests import support\n"
         "import bench\n"
+        "from oracle import ref_run\n"
         "w = bench.WORKLOADS[%r]\n"
         "c, o, g = bench.load_texts(w, %r)\n"
-        "support.reference_set_threads(%d)\n"
-        "res, secs = support.reference_evaluate(c, o, g, memory=%d)\n"
+        "ref_run.reference_set_threads(%d)\n"
+        "res, secs = ref_run.reference_evaluate(c, o, g, memory=%d)\n"
         "print(json.dumps({'secs': secs, 'amps': [[a.real, a.imag] for _, a in res]}))\n"
-    ) % (ROOT, [k for k, v in WORKLOADS.items() if v is w][0], cut_values, threads[1], w["memory"])
-    env = dict(os.environ, OMP_NUM_THREADS=str(threads[0]), OPENBLAS_NUM_THREADS=str(threads[1]),
-               OMP_WAIT_POLICY="passive")
+    ) % (ROOT, wname, cut_values, blas, WORKLOADS[wname]["memory"])
+    env = dict(os.environ, OMP_NUM_THREADS=str(omp), OPENBLAS_NUM_THREADS=str(blas),
+               OMP_WAIT_POLICY=wait)
     p = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE,
-                       stderr=subprocess.PIPE, text=True, timeout=3000)
+                       stderr=subprocess.PIPE, text=True, timeout=timeout)
     if p.returncode != 0:
         raise RuntimeError("reference run failed: " + p.stderr[-2000:])
     out = json.loads(p.stdout.strip().splitlines()[-1])
     n = 1
-    for v in cut_values:
-        n *= len(v)
+    if cut_values not in (None, "all"):
+        for v in cut_values:
+            n *= len(v)
+    else:
+        n = WORKLOADS[wname].get("total_slices") or 1
     return out["secs"], n, out["amps"]
 
 
-def host_threads():
-    cores = os.cpu_count() or 1
-    try:
-        cores = len(os.sched_getaffinity(0))
-    except AttributeError:
-        pass
-    # OpenMP for the reorder passes, OpenBLAS threads for cgemm; passive waiting
-    # avoids the oversubscription collapse recorded in SURVEY section 0.
-    return cores, (min(cores, 16), min(cores, 32))
+def sweep_reference_threads(wname, budget_s=75.0):
+    """(OMP_NUM_THREADS, OPENBLAS_NUM_THREADS) in {1, n/2, n}^2 x
+    OMP_WAIT_POLICY in {active, passive}; the reference collapses under oversubscription
+    (229 s vs 0.97 s in the survey's probe), so the sweep runs on a cheap proxy of the
+    workload (its small sibling circuit, or itself when cheap), every run under a
+    timeout, the whole sweep under a time budget.  Returns (best setting, table)."""
+    w = WORKLOADS[wname]
+    proxy = w.get("sweep_proxy", wname)
+    sample = WORKLOADS[proxy]["reference_sample"]
+    n = host_cores()
+    counts = sorted({1, max(1, n // 2), n})
+    # most promising first, so that a short budget still sees them
+    order = sorted(((o, b, wt) for o in counts for b in counts for wt in ("passive", "active")),
+                   key=lambda s: (-min(s[0], n // 2 or 1) - s[1], s[2] != "passive"))
+    table, best, t0, limit = [], None, time.time(), 20.0
+    for omp, blas, wait in order:
+        if time.time() - t0 > budget_s:
+            break
+        try:
+            secs, _, _ = cpu_reference_run(proxy, sample, omp, blas, wait, timeout=limit)
+        except subprocess.TimeoutExpired:
+            table.append(dict(omp=omp, blas=blas, wait=wait, seconds=None, note="> %.0f s" % limit))
+            continue
+        except Exception as e:
+            table.append(dict(omp=omp, blas=blas, wait=wait, seconds=None, note=str(e)[:80]))
+            continue
+        table.append(dict(omp=omp, blas=blas, wait=wait, seconds=secs))
+        if best is None or secs < best[3]:
+            best = (omp, blas, wait, secs)
+            limit = max(3.0, min(limit, 4.0 * secs + 2.0))  # python start-up included
+    if best is None:
+        best = (min(n, 16), min(n, 32), "passive", None)
+    return best[:3], dict(proxy=proxy, proxy_sample=sample, runs=table, host_cores=n)
 
 
-def run_reference_arm(args, w, wname):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return 0
-    cores, threads = host_threads()
-    sample = w["reference_sample"]
-    if sample is None:
-        print(json.dumps({"impl": "reference", "unavailable":
-                          "%s: the reference needs more host memory and time than a bounded "
-                          "sample allows (see the workload's comment in bench.py)" % wname}), flush=True)
-        return 0
-    times = []
-    for i in range(args.warmup + args.steps):
-        secs, n_slices, _ = cpu_reference_run(w, sample, threads)
-        if i >= args.warmup:
-            times.append(secs)
-    ms = 1e3 * sum(times) / len(times)
-    val = plan_flops(w, sample) / (ms * 1e-3) / 1e12
+def reference_flops(wname, sample):
+    """Algorithmic flops (sum 8*M*N*K) of the REFERENCE's schedule on the
+    slices `sample` selects -- projected leaves, slice by slice.  Read from
+    bench_reference_flops.json (written by tools/make_reference_flops.py with the
+    planner on the CPU-emulated ABI) so that this arm loads nothing of the product."""
+    with open(FLOPS_CACHE) as f:
+        table = json.load(f)
+    return table[wname + "|" + json.dumps(sample)]
+
+
+def reference_line(args, wname, w, seconds, n_slices, threads, cores, extra=None):
+    ms = 1e3 * sum(seconds) / len(seconds)
+    val = reference_flops(wname, w["reference_sample"]) / (ms * 1e-3) / 1e12
+    omp, blas, wait = threads
+    sample = ("%s slice(s) of %s per step (cut values %s), reference EvaluateCircuit, "
+              "OMP=%d OPENBLAS=%d %s wait, %d host cores"
+              % (n_slices, wname, w["reference_sample"], omp, blas, wait, cores))
     line = {
         "impl": "reference", "metric": "contraction_tflops", "value": val, "unit": "TFLOP/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
@@ -235,64 +299,46 @@ def run_reference_arm(args, w, wname):
         "dtype": "complex64",
         "data": "shipped circuit (config/circuits/%s), deterministic" % w["circuit"],
         "config": {"workload": wname, "slices_per_step": n_slices,
-                   "note": "reference qflex EvaluateCircuit on host cores, OpenBLAS + OpenMP"},
+                   "note": "unmodified reference qflex (oracle/_ref) on host cores, OpenBLAS + OpenMP"},
         "slices_per_s": n_slices / (ms * 1e-3),
-        "cpu_baseline": {"value": val, "unit": "TFLOP/s", "cores": max(threads), "kind": "reference",
-                         "sample": "%d slice(s) of %s per step, OMP=%d OPENBLAS=%d passive wait, %d host cores"
-                                   % (n_slices, wname, threads[0], threads[1], cores)},
+        "cpu_baseline": {"value": val, "unit": "TFLOP/s", "cores": max(omp, blas),
+                         "kind": "reference", "sample": sample},
         "e2e": {"value": val, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    if extra:
+        line["cpu_baseline"].update(extra)
+    return line
+
+
+def run_reference_arm(args, wname, w):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    if w["reference_sample"] is None:
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "%s: the reference needs more host memory and time than a bounded "
+                          "sample allows (see the workload's comment in bench.py)" % wname}), flush=True)
+        return 0
+    threads, sweep = sweep_reference_threads(wname)
+    times = []
+    for i in range(args.warmup + args.steps):
+        secs, n_slices, _ = cpu_reference_run(wname, w["reference_sample"], *threads)
+        if i >= args.warmup:
+            times.append(secs)
+    print(json.dumps(reference_line(args, wname, w, times, n_slices, threads, sweep["host_cores"],
+                                    {"thread_sweep": sweep})), flush=True)
     return 0
 
 
-_FLOPS_CACHE = {}
-
-
-def plan_flops(w, cut_values):
-    """Algorithmic flops of one pass of the REFERENCE's schedule over the slices
-    `cut_values` selects = sum over the schedule of 8*M*N*K x (how often the step runs: the product of the value
-    counts of the cuts that precede it).  Planner's symbolic replay; the plan is only
-    described, not contracted."""
+# ---------------------------------------------------------------- our arm
+def gate_upload_bytes(c):
+    """Bytes of gate tensors copied host->device per EvaluateCircuit call."""
     import re
-    key = (w["circuit"], json.dumps(cut_values))
-    if key not in _FLOPS_CACHE:
-        import qflex_b200
-        c, o, g = load_texts(w, cut_values)
-        fan = []
-        for line in o.splitlines():
-            m = re.match(r"\s*cut\s*\(([0-9,\s]*)\)", line)
-            if m:
-                vals = [v for v in m.group(1).split(",") if v.strip()]
-                if not vals:
-                    raise ValueError("bench workloads must give every cut an explicit value list")
-                fan.append(len(vals))
-        # the reference contracts projected leaves (one per output bitstring): count
-        # the flops of THAT plan, not of the open-output plan the engine itself runs
-        saved = os.environ.get("QFLEX_OPEN_OUTPUTS")
-        os.environ["QFLEX_OPEN_OUTPUTS"] = "0"
-        try:
-            try:
-                p = qflex_b200.default_library().prepare(c, o, g, memory_limit=w["memory"])
-            except qflex_b200.QflexError:
-                from tests import support
-                p = support.emulated_host_library().prepare(c, o, g, memory_limit=w["memory"])
-        finally:
-            if saved is None:
-                del os.environ["QFLEX_OPEN_OUTPUTS"]
-            else:
-                os.environ["QFLEX_OPEN_OUTPUTS"] = saved
-        total = 0.0
-        for r in p.describe():
-            if r["phase"] == "grid" and r["kind"] in ("contract", "dot"):
-                times = 1
-                for f in fan[: r["level"]]:
-                    times *= f
-                total += times * 8.0 * 2.0 ** (r["m_bits"] + r["n_bits"] + r["k_bits"])
-        p.close()
-        _FLOPS_CACHE[key] = total
-    return _FLOPS_CACHE[key]
+    n1 = len(re.findall(r"^\s*\d+\s+(h|t|x_1_2|y_1_2|hz_1_2|rz\S*)\s", c, flags=re.M))
+    n2 = len(re.findall(r"^\s*\d+\s+(cz|cx)\s", c, flags=re.M))
+    nf = len(re.findall(r"^\s*\d+\s+fsim", c, flags=re.M))
+    nq = int(c.split()[0])
+    return 8 * (4 * n1 + 2 * 8 * n2 + 2 * 16 * nf + 2 * 2 * nq)
 
 
 def main():
@@ -305,11 +351,11 @@ def main():
     ap.add_argument("--precision", default="auto", choices=["auto", "ffma", "bf16x3"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    if args.warmup < 3 and args.impl == "ours":
-        args.warmup = 3  # timing rule: at least 3 warm-up steps
     w = WORKLOADS[args.workload]
     if args.impl == "reference":
-        return run_reference_arm(args, w, args.workload)
+        return run_reference_arm(args, args.workload, w)
+    if args.warmup < 3:
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
 
     import numpy as np
     import torch
@@ -327,15 +373,12 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
+    reducer = sharded.AmplitudeReducer(dev if world > 1 else None)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-
-    def allreduce_amps(a):
-        # one NCCL sum of 2*n_amps doubles (qflex_b200/sharded.py)
-        return sharded.allreduce_amplitudes(a, device=dev)
 
     def max_over_ranks(x):
         t = torch.tensor([x], dtype=torch.float64, device=dev)
@@ -355,63 +398,83 @@ def main():
     prep = lib.prepare(c, o, g, memory_limit=w["memory"], device=local_rank,
                        precision=args.precision, world=world)
 
-    # ---- resident: W warm-up + K timed steps
+    # ---- resident: W warm-up + K timed steps (no per-launch profiling in here)
     for _ in range(args.warmup):
-        amps = allreduce_amps(prep.contract(rank, world))
+        amps = reducer.allreduce(prep.contract(rank, world))
     sampler = ClockSampler(local_rank)
-    prep.profile(True)
     barrier()
     if rank == 0:
         sampler.start()
     t0 = time.perf_counter()
-    dev_ms, flops_done, launches, leaves, prof, tc_launches = 0.0, 0.0, 0, 0, {}, 0
+    dev_ms, flops_done, launches, leaves, tc_launches = 0.0, 0.0, 0, 0, 0
     for _ in range(args.steps):
         part = prep.contract(rank, world)
-        amps = allreduce_amps(part)
+        amps = reducer.allreduce(part)
         st = prep.stats
         dev_ms += st["device_ms_contract"]
         flops_done += st["flops"]
         launches += int(st["launches"])
         leaves += int(st["leaves"])
         tc_launches += int(st["launches_gemm_tc"])
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    wall = max_over_ranks(wall)
+    dev_ms_max = max_over_ranks(dev_ms)
+    executed_flops = sum_over_ranks(flops_done)   # replicated work counted per rank
+    total_leaves = sum_over_ranks(leaves)
+    total_launches = int(sum_over_ranks(launches))
+    job_flops = prep.stats["flops_job"]            # the job once, whatever the rank count
+    ms_per_step = 1e3 * wall / args.steps
+    value = job_flops * args.steps / wall / 1e12
+    arena_bytes = prep.stats["arena_bytes"]
+    plan_info = {k: int(prep.stats[k]) for k in ("fused_bits", "open_outputs", "lanes")}
+    n_amps = len(prep.states)
+
+    # ---- one more pass with per-launch CUDA events: shape classes for the roofline
+    prof = {}
+    prep.profile(True)
+    for _ in range(max(1, min(args.steps, 2))):
+        prep.contract(rank, world)
         for r in prep.profile_rows():
             key = (int(r["kind"]), int(r["m_bits"]), int(r["n_bits"]), int(r["k_bits"]))
             acc = prof.setdefault(key, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0))
             for f in ("launches", "ms", "flops", "bytes"):
                 acc[f] += r[f]
-    barrier()
-    wall = time.perf_counter() - t0
-    clocks = sampler.stop() if rank == 0 else None
     prep.profile(False)
-    wall = max_over_ranks(wall)
-    total_flops = sum_over_ranks(flops_done)
-    total_leaves = sum_over_ranks(leaves)
-    total_launches = int(sum_over_ranks(launches))
-    ms_per_step = 1e3 * wall / args.steps
-    value = total_flops / wall / 1e12
-    arena_bytes = prep.stats["arena_bytes"]
-    n_amps = len(prep.states)
     prep.close()
 
     # ---- e2e: EvaluateCircuit through the C ABI from host text buffers
-    h2d = 0
-    e2e_steps = max(1, min(args.steps, 2))
+    e2e_steps = max(5, args.steps)
     lib.evaluate(c, o, g, memory_limit=w["memory"], device=local_rank, rank=rank, world=world,
                  precision=args.precision)  # warm-up (allocator, module load)
     barrier()
     t0 = time.perf_counter()
-    e2e_flops = 0.0
     for _ in range(e2e_steps):
         res, st = lib.evaluate(c, o, g, memory_limit=w["memory"], device=local_rank, rank=rank,
                                world=world, precision=args.precision)
-        part = np.array([a for _, a in res])
-        full = allreduce_amps(part)
-        e2e_flops += st["flops"]
+        full = reducer.allreduce(np.array([a for _, a in res]))
     barrier()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
-    e2e_value = sum_over_ranks(e2e_flops) / e2e_wall / 1e12
-    h2d = gate_upload_bytes(lib, c, o, g, w)
+    e2e_value = st["flops_job"] * e2e_steps / e2e_wall / 1e12
+    h2d = gate_upload_bytes(c) + len(c) + len(o) + len(g)
     parity = float(np.linalg.norm(full - amps) / max(np.linalg.norm(amps), 1e-300))
+
+    # ---- parity of THIS workload against the reference: the bounded sample the CPU arm
+    # runs (one slice), through the same C-ABI call
+    parity_ref, sample_amps = {}, None
+    if rank == 0 and w.get("reference_sample") is not None:
+        sc, so, sg = load_texts(w, w["reference_sample"])
+        sres, _ = lib.evaluate(sc, so, sg, memory_limit=w["memory"], device=local_rank,
+                               precision=args.precision)
+        sample_amps = np.array([a for _, a in sres])
+        gpath = os.path.join(ROOT, "tests", "golden", "amplitudes.json")
+        if w.get("golden") and os.path.exists(gpath):
+            with open(gpath) as f:
+                gold = json.load(f)[w["golden"]]
+            want = np.array(gold["re"]) + 1j * np.array(gold["im"])
+            parity_ref["parity_vs_reference_golden"] = float(
+                np.linalg.norm(sample_amps - want) / np.linalg.norm(want))
 
     if rank != 0:
         if world > 1:
@@ -447,84 +510,92 @@ def main():
     roof["traffic"] = None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(tpath):
-        # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel class
-        # from one `ncu --set full` capture (profiles/ncu_traffic.json names the file)
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel class,
+        # NOT measured in this run: read from the committed `ncu --set full` capture that
+        # profiles/ncu_traffic.json names
         with open(tpath) as f:
             t = json.load(f).get("%d,%d,%d" % dom_key[1:])
         if t:
             roof["traffic"] = t["dram_bytes_per_launch"]
-            roof["traffic_source"] = t["source"]
+            roof["traffic_source"] = "from committed ncu capture: " + t["source"]
             roof["algorithmic_bytes_per_launch"] = dom["bytes"] / dom["launches"]
     roof["kernel"] = "contract m=%d n=%d k=%d bits" % dom_key[1:]
     roof["launches"] = int(dom["launches"])
     roof["ms_per_launch"] = per_launch_ms
     roof["share_of_device_time"] = dom["ms"] / sum(v["ms"] for v in prof.values())
     roof["arithmetic_intensity"] = ai
-    roof["peak_source"] = ("%s: hbm_gbs %.1f (MEASURED_PEAKS.json); FFMA peak derived = "
-                           "148 SM x 128 lanes x 2 x %.0f MHz" % (peak_src, peaks["hbm_gbs"], sm_max))
+    roof["timing"] = "CUDA events per launch on the context stream, in a separate profiled pass"
+    roof["peak_source"] = ("%s: hbm_gbs %.1f, bf16 sustained %.1f (MEASURED_PEAKS.json); FFMA peak "
+                           "derived = 148 SM x 128 lanes x 2 x %.0f MHz"
+                           % (peak_src, peaks["hbm_gbs"], peaks["bf16_tflops_sustained"], sm_max))
 
+    # whole-step roofline: sum of per-class t_min over the measured class times
+    def t_min_ms(key, v):
+        tc = (args.precision != "ffma" and min(key[1], key[2]) >= 4 and key[3] >= 4 and
+              max(key[1], key[2]) >= 7)
+        pipe = peaks["bf16_tflops_sustained"] / 3.0 if tc else ffma_peak
+        return max(v["flops"] / (pipe * 1e9), v["bytes"] / (peaks["hbm_gbs"] * 1e6))
+    step_frac = (sum(t_min_ms(k, v) for k, v in prof.items()) /
+                 max(1e-9, sum(v["ms"] for v in prof.values())))
+
+    slices_per_step = total_leaves / args.steps / max(1, n_amps)
     line = {
         "metric": "contraction_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": w.get("scaling", "weak"), "vs_baseline": None,
         "dtype": "complex64",
         "data": "shipped circuit (config/circuits/%s), deterministic; synthetic = none needed" % w["circuit"],
-        "config": {"workload": args.workload,
-                   "slices_per_gpu": total_leaves / args.steps / world / max(1, n_amps),
-                   "slices_per_step": int(total_leaves / args.steps), "cut_values": cuts,
-                   "arena_gb": arena_bytes / 2 ** 30, "precision": args.precision,
+        "config": {"workload": args.workload, "slices_per_step": int(round(slices_per_step)),
+                   "slices_per_gpu": slices_per_step / world, "amplitudes_per_slice": n_amps,
+                   "cut_values": cuts, "arena_gb": arena_bytes / 2 ** 30,
+                   "precision": args.precision, "plan": plan_info,
                    "l2": "working set per contraction (>= 2 GB patches) exceeds the 126 MB L2",
                    "collective": "one NCCL all-reduce(sum) of %d complex128 per step" % n_amps},
-        # leaves = (bond-cut slices) x (output bitstrings): one leaf = one scalar result
-        "slices_per_s": total_leaves / wall,
+        # `value` counts the job's flops once; executed = what the ranks ran in all
+        # (steps above the dealt cut level are replicated on every rank)
+        "executed_tflops": executed_flops / wall / 1e12,
+        "replicated_share": max(0.0, executed_flops / (job_flops * args.steps) - 1.0),
+        "slices_per_s": total_leaves / max(1, n_amps) / wall,
+        "leaves_per_s": total_leaves / wall,
         # amplitudes/s of the FULL circuit at this rate: every output bitstring needs all
         # of the circuit's bond-cut slices
         "amplitudes_per_s_full_circuit": (total_leaves / wall / float(w["total_slices"])
                                           if w.get("total_slices") else None),
-        "device_ms_per_step_rank0": dev_ms / args.steps,
-        "e2e": {"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 16 * n_amps, "steps": e2e_steps,
-                "ms_per_step": 1e3 * e2e_wall / e2e_steps,
-                "parity_vs_resident_run": parity},
+        "device_ms_per_step": dev_ms_max / args.steps,
+        "e2e": dict({"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d,
+                     "d2h_bytes_per_step": 16 * n_amps, "steps": e2e_steps,
+                     "ms_per_step": 1e3 * e2e_wall / e2e_steps,
+                     "parity_vs_resident_run": parity}, **parity_ref),
         "gpu_launches": total_launches,
-        "clocks": clocks, "roofline": roof,
+        "clocks": clocks, "roofline": roof, "step_roofline_frac": step_frac,
         "kernel_classes": [dict(kind=k[0], m_bits=k[1], n_bits=k[2], k_bits=k[3],
                                 launches=int(v["launches"]), ms=v["ms"],
                                 tflops=v["flops"] / v["ms"] / 1e9 if v["ms"] else None,
-                                gbs=v["bytes"] / v["ms"] / 1e6 if v["ms"] else None)
-                           for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])[:8]],
+                                gbs=v["bytes"] / v["ms"] / 1e6 if v["ms"] else None,
+                                frac_of_roof=t_min_ms(k, v) / v["ms"] if v["ms"] else None)
+                           for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])[:10]],
     }
-    if world == 1 and not args.no_cpu_baseline and w["reference_sample"] is None:
-        line["cpu_baseline"] = {"value": None, "unit": "TFLOP/s", "cores": 0, "kind": "reference",
-                                "sample": "not run: no bounded sample of this workload fits the host"}
-    elif world == 1 and not args.no_cpu_baseline:
-        try:
-            cores, threads = host_threads()
-            secs, n_slices, ref_amps = cpu_reference_run(w, w["reference_sample"], threads)
-            fl = plan_flops(w, w["reference_sample"])
-            line["cpu_baseline"] = {
-                "value": fl / secs / 1e12, "unit": "TFLOP/s", "cores": max(threads),
-                "kind": "reference", "seconds": secs,
-                "sample": "%d slice(s) of %s (cut values %s), reference EvaluateCircuit, "
-                          "OMP=%d OPENBLAS=%d passive wait, %d host cores"
-                          % (n_slices, args.workload, w["reference_sample"], threads[0], threads[1], cores)}
-        except Exception as e:  # the baseline is reported, never a gate
+    if world == 1 and not args.no_cpu_baseline:
+        if w["reference_sample"] is None:
             line["cpu_baseline"] = {"value": None, "unit": "TFLOP/s", "cores": 0, "kind": "reference",
-                                    "sample": "failed: %s" % str(e)[:200]}
+                                    "sample": "not run: no bounded sample of this workload fits the host"}
+        else:
+            try:
+                threads, sweep = sweep_reference_threads(args.workload, budget_s=60.0)
+                secs, n_slices, ref_amps = cpu_reference_run(args.workload, w["reference_sample"], *threads)
+                ref_line = reference_line(args, args.workload, w, [secs], n_slices, threads,
+                                          sweep["host_cores"], {"seconds": secs, "thread_sweep": sweep})
+                line["cpu_baseline"] = ref_line["cpu_baseline"]
+                want = np.array([complex(a, b) for a, b in ref_amps])
+                line["e2e"]["parity_vs_reference"] = float(
+                    np.linalg.norm(sample_amps - want) / np.linalg.norm(want))
+            except Exception as e:  # the baseline is reported, never a gate
+                line["cpu_baseline"] = {"value": None, "unit": "TFLOP/s", "cores": 0, "kind": "reference",
+                                        "sample": "failed: %s" % str(e)[:200]}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
-
-
-def gate_upload_bytes(lib, c, o, g, w):
-    """Bytes of gate tensors copied host->device per EvaluateCircuit call."""
-    import re
-    n1 = len(re.findall(r"^\s*\d+\s+(h|t|x_1_2|y_1_2|hz_1_2|rz\S*)\s", c, flags=re.M))
-    n2 = len(re.findall(r"^\s*\d+\s+(cz|cx)\s", c, flags=re.M))
-    nf = len(re.findall(r"^\s*\d+\s+fsim", c, flags=re.M))
-    nq = int(c.split()[0])
-    return 8 * (4 * n1 + 2 * 8 * n2 + 2 * 16 * nf + 2 * 2 * nq)
 
 
 if __name__ == "__main__":

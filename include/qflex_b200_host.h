@@ -30,7 +30,8 @@ extern "C" {
  *  [13] reduce launches      [14] permute launches   [15] number of amplitudes
  *  [16] fused cut bits (one pass covers 2^f slices of the ordering as written)
  *  [17] terminal cuts kept open          [18] lanes (contexts on this GPU)
- *  [19] reserved
+ *  [19] algorithmic flops of the whole job executed once (all slices; what one rank
+ *       alone would execute -- the useful work of a sharded run)
  */
 
 /* One-shot EvaluateCircuit.  states_out receives the output bitstrings joined
@@ -65,6 +66,10 @@ long qflex_b200_contract(void* prepared, int rank, int world, double* amps_out,
 /* Re-run the host->device upload of the gate tensors and the device-side
  * flatten (used to time the full host-buffer path). */
 long qflex_b200_reload(void* prepared, char* err, uint64_t err_cap);
+/* The stats_out layout above for a resident circuit without running it (plan
+ * figures: arena bytes, flops per pass, flops of the whole job, fused bits ...; the
+ * execution figures are those of the last contract()). */
+long qflex_b200_plan_stats(void* prepared, double* stats_out);
 /* Another final state on the same resident circuit: only the delta tensors closing
  * the world lines are rewritten and the (ms-scale) flatten re-run; parse, plan, arena
  * and schedule are reused.  Positions of terminal-cut qubits are ignored.  This is the

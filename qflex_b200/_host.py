@@ -16,7 +16,7 @@ STAT_NAMES = (
     "seconds_upload", "seconds_flatten", "seconds_contract", "device_ms_contract",
     "leaves", "launches", "flops", "bytes", "arena_bytes", "flops_per_pass",
     "bytes_per_pass", "launches_gemm_ffma", "launches_gemm_tc", "launches_reduce",
-    "launches_permute", "n_amplitudes", "fused_bits", "open_outputs", "lanes", "reserved",
+    "launches_permute", "n_amplitudes", "fused_bits", "open_outputs", "lanes", "flops_job",
 )
 PRECISIONS = {"auto": 0, "ffma": 1, "bf16x3": 2}
 
@@ -56,6 +56,23 @@ def _memory_bytes(m):
     return int(num) * scale[s]
 
 
+def restrict_cuts(ordering_text, values_per_cut):
+    """Rewrites the value list of the k-th `cut` line (k = 0, 1, ...) of an ordering
+    with values_per_cut[k] (None keeps the line): a fixed subset of the slices /
+    output bitstrings, selected the same way for this engine and for the reference
+    (the grammar's `cut (v1,v2,...) a b`, reference docs/input_formats.md)."""
+    import re
+    out, k = [], 0
+    for line in ordering_text.splitlines():
+        if line.strip().startswith("cut"):
+            if k < len(values_per_cut) and values_per_cut[k] is not None:
+                vals = ",".join(str(v) for v in values_per_cut[k])
+                line = re.sub(r"\([0-9,\s]*\)", "(" + vals + ")", line, count=1)
+            k += 1
+        out.append(line)
+    return "\n".join(out) + "\n"
+
+
 class Prepared:
     """A circuit resident on one GPU: contract() can be called repeatedly."""
 
@@ -83,6 +100,13 @@ class Prepared:
             raise QflexError(err.value.decode())
         self.stats = dict(zip(STAT_NAMES, stats.tolist()))
         return amps.view(np.complex128)
+
+    def plan_stats(self):
+        """Plan figures (arena_bytes, flops_per_pass, flops_job, fused_bits, ...) without
+        contracting."""
+        stats = np.zeros(N_STATS, dtype=np.float64)
+        self._lib._c.qflex_b200_plan_stats(self._h, stats.ctypes.data_as(ctypes.c_void_p))
+        return dict(zip(STAT_NAMES, stats.tolist()))
 
     def set_final_state(self, final_state):
         """Same circuit, another output bitstring: parse/plan/arena are reused."""
@@ -158,6 +182,8 @@ class HostLibrary:
             ctypes.c_uint64, ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
         c.qflex_b200_reload.restype = ctypes.c_long
         c.qflex_b200_reload.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_plan_stats.restype = ctypes.c_long
+        c.qflex_b200_plan_stats.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         c.qflex_b200_set_final_state.restype = ctypes.c_long
         c.qflex_b200_set_final_state.argtypes = [ctypes.c_void_p, ctypes.c_char_p,
                                                  ctypes.c_char_p, ctypes.c_uint64]

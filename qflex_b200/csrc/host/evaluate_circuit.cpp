@@ -5,6 +5,7 @@
 #include "evaluate_circuit.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 
 #include <chrono>
@@ -15,12 +16,14 @@
 namespace qflex {
 namespace {
 
-// Position of grid site `pos` in the string of active qubits.
+// Position of grid site `pos` in the state strings: its rank among the active qubits
+// in row-major order.
 std::size_t find_output_pos(const QflexInput* input, const std::vector<std::size_t>& pos) {
-  std::size_t p = pos[0] * input->grid.J + pos[1];
-  for (const auto& off : input->grid.qubits_off)
-    if (off[0] < pos[0] || (off[0] == pos[0] && off[1] < pos[1])) --p;
-  return p;
+  const std::size_t J = input->grid.J, target = pos[0] * J + pos[1];
+  std::size_t skipped = 0;
+  for (const auto& q : input->grid.qubits_off)
+    if (q.size() == 2 && q[0] * J + q[1] < target) ++skipped;
+  return target - skipped;
 }
 
 double seconds_since(const std::chrono::steady_clock::time_point& t0) {
@@ -37,39 +40,50 @@ std::string get_output_states(
   if (final_qubits == nullptr) throw ERROR_MSG("Final qubits must be non-null.");
   if (output_states == nullptr) throw ERROR_MSG("Output states must be non-null");
 
-  std::string base_state = input->final_state;
-  const bool unspecified = input->final_state.empty();
-  if (unspecified) base_state = std::string(input->initial_state.length(), '0');
-
-  std::vector<std::size_t> where;
-  std::vector<std::vector<std::size_t>> what;
+  // One digit per terminal cut, in ordering order: where it sits in the state string
+  // and which values it takes.
+  struct Digit {
+    std::size_t where;
+    std::vector<std::size_t> values;
+  };
+  std::vector<Digit> digits;
   for (const auto& op : ordering) {
     if (op.op_type != ContractionOperation::CUT || op.cut.tensors.size() != 1) continue;
-    const std::size_t p = find_output_pos(input, op.cut.tensors[0]);
-    if (unspecified) base_state[p] = 'x';
-    where.push_back(p);
-    what.push_back(op.cut.values.empty() ? std::vector<std::size_t>{0, 1} : op.cut.values);
+    Digit d{find_output_pos(input, op.cut.tensors[0]), op.cut.values};
+    if (d.values.empty()) d.values = {0, 1};
+    digits.push_back(std::move(d));
     final_qubits->push_back(op.cut.tensors[0]);
   }
-  // each terminal cut multiplies the list; earlier cuts vary slowest
-  output_states->push_back(base_state);
-  for (std::size_t c = 0; c < where.size(); ++c) {
-    std::vector<std::string> grown;
-    for (const std::string& state : *output_states)
-      for (const std::size_t val : what[c]) {
-        std::string s = state;
-        s[where[c]] = std::to_string(val).at(0);
-        grown.push_back(std::move(s));
-      }
-    *output_states = std::move(grown);
+
+  // The template: the requested final state, or all zeros with 'x' at the outputs.
+  std::string base = input->final_state;
+  if (base.empty()) {
+    base.assign(input->initial_state.length(), '0');
+    for (const auto& d : digits) base[d.where] = 'x';
   }
-  for (std::size_t i = 0; i < output_states->at(0).length(); ++i) {
-    const char c = output_states->at(0)[i];
-    if (c != '0' && c != '1')
-      throw ERROR_MSG("Final state has non-binary character ", c, " at index ", i,
+
+  // Mixed-radix count over the digits, first terminal cut most significant: amplitude
+  // number n belongs to the state whose digits are n's expansion (the slot formula
+  // output_index * |values| + i of src/contraction_utils.cpp:300-314).
+  std::size_t total = 1;
+  for (const auto& d : digits) total *= d.values.size();
+  output_states->reserve(output_states->size() + total);
+  for (std::size_t n = 0; n < total; ++n) {
+    std::string state = base;
+    std::size_t rest = n;
+    for (std::size_t k = digits.size(); k--;) {
+      const Digit& d = digits[k];
+      state[d.where] = (char)('0' + d.values[rest % d.values.size()] % 10);
+      rest /= d.values.size();
+    }
+    output_states->push_back(std::move(state));
+  }
+  const std::string& first = output_states->at(0);
+  for (std::size_t i = 0; i < first.length(); ++i)
+    if (first[i] != '0' && first[i] != '1')
+      throw ERROR_MSG("Final state has non-binary character ", first[i], " at index ", i,
                       "despite having no terminal cut there.");
-  }
-  return base_state;
+  return base;
 }
 
 std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
@@ -167,30 +181,30 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
         return false;
       }
     };
+    // Fusing pays while the schedule is a stream of small launches; once the average
+    // contraction is large (>= ~1e11 flop, hundreds of microseconds on the tensor
+    // cores) it only grows the arena and the merges' K.  Every fused bit about doubles
+    // the work per launch: aim for the smallest f that reaches the target
+    // (QFLEX_FUSE_TARGET_FLOPS), back off by bisection when it does not fit.
+    double target = 1e11;
+    if (const char* e = getenv("QFLEX_FUSE_TARGET_FLOPS")) target = std::max(1.0, atof(e));
+    const double mean0 =
+        result->flops_per_pass / std::max<double>(1.0, (double)result->steps.size());
+    int want = 0;
+    while (want < max_fuse && std::ldexp(mean0, want) < target) ++want;
+    if (want <= 0) return;
     Plan best;
     int have = 0;
-    {
-      // how many bits the ordering offers at all
-      Plan probe;
-      int offered = 0;
-      try {
-        probe = BuildPlan(*input, ordering, final_qubits, n_open, cut_aware, max_fuse);
-        offered = probe.fused_bits;
-        if (offered > 0 && probe.open_outputs == n_open && fits(probe)) {
-          best = std::move(probe);
-          have = offered;
-        }
-      } catch (const std::string&) {
-        offered = max_fuse;
+    if (try_fuse(want, &best)) {
+      have = want;
+    } else {
+      int lo = 0, hi = want;  // lo fits, hi does not
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) / 2;
+        if (try_fuse(mid, &best)) lo = mid, have = mid;
+        else hi = mid;
       }
-      if (have == 0 && offered > 0) {
-        int lo = 0, hi = std::min(offered, max_fuse);  // lo fits, hi does not
-        while (hi - lo > 1) {
-          const int mid = (lo + hi) / 2;
-          if (try_fuse(mid, &best)) lo = mid, have = mid;
-          else hi = mid;
-        }
-      }
+      // `best` holds the last successful try, which is lo (bisection only raises lo)
     }
     if (have > 0) *result = std::move(best);
   };

@@ -1,8 +1,10 @@
 // extern "C" surface of libqflex_host.so (include/qflex_b200_host.h).
+#include <algorithm>
 #include <cstring>
 #include <exception>
 #include <sstream>
 #include <string>
+#include <vector>
 
 #include "errors.h"
 #include "evaluate_circuit.h"
@@ -50,7 +52,16 @@ void fill_stats(const qflex::Session& s, double* out) {
   out[16] = (double)p.fused_bits;
   out[17] = (double)p.open_outputs;
   out[18] = (double)s.lanes();
-  out[19] = 0.0;
+  // flops of ONE execution of the whole job (every slice, each step counted once per
+  // combination of the cuts before it) -- what a single rank alone would execute
+  double all = 0.0;
+  {
+    std::vector<double> fan(p.cuts.size() + 1, 1.0);
+    for (std::size_t c = 0; c < p.cuts.size(); ++c)
+      fan[c + 1] = fan[c] * (double)std::max<std::size_t>(1, p.cuts[c].values.size());
+    for (const auto& st : p.steps) all += st.flops * fan[std::min<std::size_t>(st.level, p.cuts.size())];
+  }
+  out[19] = all;
 }
 
 std::string join_states(const std::vector<std::string>& states) {
@@ -144,6 +155,12 @@ long qflex_b200_reload(void* prepared, char* err, uint64_t err_cap) {
     return 0;
   }
   QFLEX_CAPI_CATCH(-1)
+}
+
+long qflex_b200_plan_stats(void* prepared, double* stats_out) {
+  if (prepared == nullptr || stats_out == nullptr) return -1;
+  fill_stats(*static_cast<qflex::PreparedCircuit*>(prepared)->session, stats_out);
+  return QFLEX_B200_N_STATS;
 }
 
 long qflex_b200_set_final_state(void* prepared, const char* final_state, char* err,

@@ -78,67 +78,72 @@ bool parse_cut_values(const std::string& token, std::vector<std::size_t>* out) {
 
 }  // namespace
 
+namespace {
+
+// One line of the ordering grammar:
+//   expand <patch> <qubit> | cut (<v,..>) <qubit> [<qubit>] | merge <patch> <patch>
+// tokenised once; qubit ids are resolved against the grid by the caller.
+struct OrderingLine {
+  std::string verb;
+  std::vector<std::string> words;  // everything after the verb
+};
+
+OrderingLine tokenize(const std::string& line) {
+  OrderingLine out;
+  std::stringstream ss(line);
+  ss >> out.verb;
+  for (std::string w; ss >> w;) out.words.push_back(w);
+  return out;
+}
+
+}  // namespace
+
 void ordering_data_to_contraction_ordering(
     const QflexInput& input, std::list<ContractionOperation>* ordering) {
   if (ordering == nullptr) throw ERROR_MSG("Ordering must be non-null.");
 
-  const std::size_t grid_size = input.grid.I * input.grid.J;
-  std::string current;
-  auto fail = [&current](const std::string& why) {
-    return ERROR_MSG("Parsing failed on line: '", current, "' with error: ", why);
-  };
-  auto check_index = [&](long int index) {
-    if (static_cast<std::size_t>(static_cast<long int>(grid_size)) != grid_size)
-      throw fail("Grid is too big.");
-    if (index < 0 || index >= static_cast<long int>(grid_size))
-      throw fail(utils::concat("Index ", index, " must be within grid boundaries."));
-  };
-  auto is_off = [&](const std::vector<std::size_t>& pos) {
-    return find_grid_coord_in_list(input.grid.qubits_off, pos[0], pos[1]);
-  };
+  const std::size_t J = input.grid.J;
+  const std::size_t sites = input.grid.I * J;
+  std::vector<char> off(sites, 0);
+  for (const auto& q : input.grid.qubits_off)
+    if (q.size() == 2 && q[0] < input.grid.I && q[1] < J) off[q[0] * J + q[1]] = 1;
 
-  for (const auto& line : input.ordering.instructions) {
+  for (const std::string& line : input.ordering.instructions) {
     if (line.empty() || line[0] == '#') continue;
-    current = line;
-    std::stringstream ss(line);
-    std::string operation;
-    ss >> operation;
-    if (operation == "expand") {
-      std::string patch;
-      long int index = 0;
-      ss >> patch >> index;
-      check_index(index);
-      const auto position = get_qubit_coords(index, input.grid.J);
-      if (is_off(position)) throw fail("Index must specify an active qubit.");
-      ordering->emplace_back(ExpandPatch(patch, position));
-    } else if (operation == "cut") {
-      std::string values_str;
+    auto fail = [&line](const std::string& why) {
+      return ERROR_MSG("Parsing failed on line: '", line, "' with error: ", why);
+    };
+    // qubit id (a word of the line) -> grid position; `which` names it in messages
+    auto site_of = [&](const std::string& word, const char* which) {
+      char* end = nullptr;
+      const long id = std::strtol(word.c_str(), &end, 10);
+      if (static_cast<std::size_t>(static_cast<long>(sites)) != sites) throw fail("Grid is too big.");
+      if (id < 0 || id >= static_cast<long>(sites))  // (a non-number reads as 0, as >> does)
+        throw fail(utils::concat("Index ", id, " must be within grid boundaries."));
+      if (off[id]) throw fail(utils::concat(which, " must specify an active qubit."));
+      return get_qubit_coords((std::size_t)id, J);
+    };
+    const OrderingLine t = tokenize(line);
+    const auto word = [&](std::size_t i) { return i < t.words.size() ? t.words[i] : std::string("0"); };
+    if (t.verb == "expand") {
+      ordering->emplace_back(ExpandPatch(word(0), site_of(word(1), "Index")));
+    } else if (t.verb == "merge") {
+      ordering->emplace_back(MergePatches(t.words.size() > 0 ? t.words[0] : "",
+                                          t.words.size() > 1 ? t.words[1] : ""));
+    } else if (t.verb == "cut") {
       std::vector<std::size_t> values;
-      ss >> values_str;
-      if (!parse_cut_values(values_str, &values))
+      if (!parse_cut_values(t.words.empty() ? "" : t.words[0], &values))
         throw fail("Cut values must be comma-separated ints, e.g. (0,1,3).");
-      long int index_1 = 0, index_2 = 0;
-      ss >> index_1;
-      check_index(index_1);
-      const auto position_1 = get_qubit_coords(index_1, input.grid.J);
-      if (is_off(position_1)) throw fail("Index 1 must specify an active qubit.");
-      if (ss.eof()) {
-        ordering->emplace_back(CutIndex({position_1}, values));
+      const auto first = site_of(word(1), "Index 1");
+      if (t.words.size() < 3) {
+        ordering->emplace_back(CutIndex({first}, values));  // terminal cut
       } else {
-        ss >> index_2;
-        check_index(index_2);
-        const auto position_2 = get_qubit_coords(index_2, input.grid.J);
-        if (is_off(position_2)) throw fail("Index 2 must specify an active qubit.");
-        // the lower qubit id always comes first in a bond name
-        if (index_1 < index_2)
-          ordering->emplace_back(CutIndex({position_1, position_2}, values));
-        else
-          ordering->emplace_back(CutIndex({position_2, position_1}, values));
+        const auto second = site_of(word(2), "Index 2");
+        // a bond is named lower qubit id first
+        const bool in_order = first[0] * J + first[1] < second[0] * J + second[1];
+        ordering->emplace_back(in_order ? CutIndex({first, second}, values)
+                                        : CutIndex({second, first}, values));
       }
-    } else if (operation == "merge") {
-      std::string patch_1, patch_2;
-      ss >> patch_1 >> patch_2;
-      ordering->emplace_back(MergePatches(patch_1, patch_2));
     } else {
       throw fail("Received an invalid operation in config.");
     }
@@ -146,65 +151,64 @@ void ordering_data_to_contraction_ordering(
   ValidateOrdering(*ordering);
 }
 
+// The rules of src/contraction_utils.h:189-204, stated on two clocks: `epoch` counts
+// the cuts seen so far; a patch remembers the epoch in which it first held a tensor.
+// A patch that held something before the latest cut is frozen -- it was contracted
+// inside an outer slice loop and may not grow inside an inner one -- and so is a patch
+// that has been merged away.  Tensors are expanded once, indices cut once, patches
+// merged away once.  All violations are collected into one message.
 void ValidateOrdering(const std::list<ContractionOperation>& ordering) {
-  struct PatchState {
-    bool is_active = false;  // expanded, no cut since
-    bool is_used = false;    // expanded and a cut happened afterwards
-    bool is_merged = false;  // merged into another patch
+  constexpr long kEmpty = -1;
+  struct PatchLife {
+    long born = kEmpty;   // epoch of the first expand / merge into this patch
+    bool gone = false;    // merged into another patch
   };
-  std::unordered_map<std::string, PatchState> patches;
-  std::unordered_set<std::string> cut_indices, used_tensors;
-  std::string problems;
+  std::unordered_map<std::string, PatchLife> life;
+  std::unordered_set<std::string> seen_tensor, seen_cut;
+  std::vector<std::string> complaints;
+  long epoch = 0;
+  auto frozen = [&](const PatchLife& p) { return p.born != kEmpty && p.born < epoch; };
+
   for (const auto& op : ordering) {
-    switch (op.op_type) {
-      case ContractionOperation::EXPAND: {
-        PatchState& p = patches[op.expand.id];
-        if (p.is_used)
-          problems = utils::concat(problems, "\nTensor at (", op.expand.tensor[0],
-                                   ",", op.expand.tensor[1],
-                                   ") is added to non-empty patch ",
-                                   op.expand.id.c_str(), " after a cut.");
-        if (p.is_merged)
-          problems = utils::concat(problems, "\nTensor at (", op.expand.tensor[0],
-                                   ",", op.expand.tensor[1],
-                                   ") is added to non-empty patch ",
-                                   op.expand.id.c_str(), " after a cut.");
-        const std::string name =
-            utils::concat("(", op.expand.tensor[0], ",", op.expand.tensor[1], ")");
-        if (!used_tensors.insert(name).second)
-          problems = utils::concat(problems, "\nTensor ", name,
-                                   " is contracted multiple times.");
-        p.is_active = true;
-        break;
+    if (op.op_type == ContractionOperation::CUT) {
+      std::string index;
+      try {
+        index = index_name(op.cut.tensors);
+      } catch (const std::string& err_msg) {
+        throw ERROR_MSG("Failed to during CUT. Error:\n\t[", err_msg, "]");
       }
-      case ContractionOperation::CUT: {
-        try {
-          for (auto& kv : patches)
-            if (kv.second.is_active) kv.second.is_used = true;
-          const std::string index = index_name(op.cut.tensors);
-          if (!cut_indices.insert(index).second)
-            problems = utils::concat(problems, "\nIndex ", index.c_str(),
-                                     " is cut multiple times.");
-        } catch (const std::string& err_msg) {
-          throw ERROR_MSG("Failed to during CUT. Error:\n\t[", err_msg, "]");
-        }
-        break;
-      }
-      case ContractionOperation::MERGE: {
-        if (patches[op.merge.source_id].is_merged)
-          problems = utils::concat(problems, "\nPatch ", op.merge.source_id.c_str(),
-                                   " is merged multiple times.");
-        if (patches[op.merge.target_id].is_used)
-          problems = utils::concat(problems, "\nPatch ", op.merge.source_id.c_str(),
-                                   " is merged into non-empty patch ",
-                                   op.merge.target_id.c_str(), " after a cut.");
-        patches[op.merge.source_id].is_merged = true;
-        patches[op.merge.target_id].is_active = true;
-        break;
-      }
+      if (!seen_cut.insert(index).second)
+        complaints.push_back(utils::concat("Index ", index, " is cut multiple times."));
+      ++epoch;
+    } else if (op.op_type == ContractionOperation::EXPAND) {
+      PatchLife& p = life[op.expand.id];
+      const auto& at = op.expand.tensor;
+      if (frozen(p) || p.gone)
+        complaints.push_back(utils::concat("Tensor at (", at[0], ",", at[1],
+                                           ") is added to non-empty patch ", op.expand.id,
+                                           " after a cut."));
+      const std::string name = utils::concat("(", at[0], ",", at[1], ")");
+      if (!seen_tensor.insert(name).second)
+        complaints.push_back(utils::concat("Tensor ", name, " is contracted multiple times."));
+      if (p.born == kEmpty) p.born = epoch;
+    } else {
+      PatchLife& from = life[op.merge.source_id];
+      if (from.gone)
+        complaints.push_back(
+            utils::concat("Patch ", op.merge.source_id, " is merged multiple times."));
+      from.gone = true;
+      PatchLife& into = life[op.merge.target_id];  // (may rehash: `from` is not used below)
+      if (frozen(into))
+        complaints.push_back(utils::concat("Patch ", op.merge.source_id,
+                                           " is merged into non-empty patch ",
+                                           op.merge.target_id, " after a cut."));
+      if (into.born == kEmpty) into.born = epoch;
     }
   }
-  if (!problems.empty()) throw problems;
+  if (complaints.empty()) return;
+  std::string all;
+  for (const auto& c : complaints) all += "\n" + c;
+  throw all;
 }
 
 }  // namespace qflex

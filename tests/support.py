@@ -6,12 +6,16 @@ reference (oracle/_ref, test infrastructure) and the CPU-emulated host library.
 import ctypes
 import os
 import re
+import sys
 
 import numpy as np
 
+ROOT_ = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT_ not in sys.path:
+    sys.path.insert(0, ROOT_)
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CONFIG = os.path.join(ROOT, "config")
-REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libqflex_ref.so")
 
 SIMPLE_CIRCUIT = """5
 0 h 0
@@ -52,20 +56,7 @@ merge a b
 SIMPLE_GRID = "1 1\n1 1\n0 1\n"
 
 
-def restrict_cuts(ordering_text, values_per_cut):
-    """Rewrites the value list of the k-th `cut` line (k = 0, 1, ...) with
-    values_per_cut[k] (None keeps the line).  This is how a fixed subset of
-    slices is selected identically for the reference and for this engine."""
-    out, k = [], 0
-    for line in ordering_text.splitlines():
-        s = line.strip()
-        if s.startswith("cut"):
-            if k < len(values_per_cut) and values_per_cut[k] is not None:
-                vals = ",".join(str(v) for v in values_per_cut[k])
-                line = re.sub(r"\([0-9,\s]*\)", "(" + vals + ")", line, count=1)
-            k += 1
-        out.append(line)
-    return "\n".join(out) + "\n"
+from qflex_b200._host import restrict_cuts  # noqa: E402,F401  (slice subsets)
 
 
 # name -> files under config/ (or inline texts), optional final state
@@ -142,79 +133,9 @@ def case_texts(case):
     return c, o, g
 
 
-_ref = None
-
-
-def reference_available():
-    return os.path.exists(REF_LIB)
-
-
-def reference_library():
-    global _ref
-    if _ref is None:
-        lib = ctypes.CDLL(REF_LIB)
-        lib.ref_evaluate.restype = ctypes.c_long
-        lib.ref_multiply.restype = ctypes.c_long
-        lib.ref_reorder.restype = ctypes.c_long
-        _ref = lib
-    return _ref
-
-
-def reference_set_threads(n):
-    reference_library().ref_set_blas_threads(int(n))
-
-
-def reference_evaluate(circuit, ordering, grid, initial="", final="", memory=64 << 30,
-                       cap=1 << 16):
-    """The reference's own EvaluateCircuit (oracle/ref_capi.cpp)."""
-    lib = reference_library()
-    amps = np.zeros(2 * cap)
-    states = ctypes.create_string_buffer(cap * 96)
-    err = ctypes.create_string_buffer(1 << 16)
-    secs = ctypes.c_double()
-    n = lib.ref_evaluate(circuit.encode(), ordering.encode(), grid.encode(), initial.encode(),
-                         final.encode(), ctypes.c_ulong(memory), states,
-                         ctypes.c_ulong(len(states)), amps.ctypes.data_as(ctypes.c_void_p),
-                         ctypes.c_ulong(cap), ctypes.byref(secs), err, ctypes.c_ulong(len(err)))
-    if n < 0:
-        raise RuntimeError(err.value.decode())
-    vals = amps[: 2 * n].view(np.complex128)
-    return list(zip(states.value.decode().split("\n"), [complex(v) for v in vals])), secs.value
-
-
-def reference_multiply(a, a_idx, a_dims, b, b_idx, b_dims):
-    """The reference's own qflex::multiply on caller data."""
-    lib = reference_library()
-    a = np.ascontiguousarray(a, dtype=np.complex64).copy()
-    b = np.ascontiguousarray(b, dtype=np.complex64).copy()
-    ad = (ctypes.c_ulong * len(a_dims))(*a_dims)
-    bd = (ctypes.c_ulong * len(b_dims))(*b_dims)
-    cap = int(np.prod(a_dims, dtype=np.int64) * np.prod(b_dims, dtype=np.int64))
-    c = np.zeros(max(cap, 1), dtype=np.complex64)
-    names = ctypes.create_string_buffer(4096)
-    cd = (ctypes.c_ulong * 64)()
-    err = ctypes.create_string_buffer(1 << 14)
-    n = lib.ref_multiply(";".join(a_idx).encode(), ad, a.ctypes.data_as(ctypes.c_void_p),
-                         ";".join(b_idx).encode(), bd, b.ctypes.data_as(ctypes.c_void_p),
-                         c.ctypes.data_as(ctypes.c_void_p), ctypes.c_ulong(c.size), names,
-                         ctypes.c_ulong(len(names)), cd, err, ctypes.c_ulong(len(err)))
-    if n < 0:
-        raise RuntimeError(err.value.decode())
-    dims = [int(cd[i]) for i in range(n)]
-    idx = names.value.decode().split(";") if n else []
-    return c[: int(np.prod(dims, dtype=np.int64)) if dims else 1], idx, dims
-
-
-def reference_reorder(data, idx, dims, new_idx):
-    lib = reference_library()
-    d = np.ascontiguousarray(data, dtype=np.complex64).copy()
-    dd = (ctypes.c_ulong * len(dims))(*dims)
-    err = ctypes.create_string_buffer(1 << 14)
-    rc = lib.ref_reorder(";".join(idx).encode(), dd, d.ctypes.data_as(ctypes.c_void_p),
-                         ";".join(new_idx).encode(), err, ctypes.c_ulong(len(err)))
-    if rc < 0:
-        raise RuntimeError(err.value.decode())
-    return d
+from oracle.ref_run import (REF_LIB, reference_available, reference_library,  # noqa: E402,F401
+                            reference_set_threads, reference_evaluate, reference_multiply,
+                            reference_reorder)
 
 
 def emulated_host_library():

@@ -125,6 +125,20 @@ def test_plan_describe_and_flop_model(emul):
 
 @pytest.mark.parametrize("bad,needle", [
     (dict(ordering="expand a 1\nexpand a 1\n"), "is contracted multiple times"),
+    # the scenarios of the reference's ValidateOrdering tests
+    # (tests/src/contraction_utils_test.cpp:104-224), through the text front-end
+    (dict(ordering="cut () 1 3\ncut (2,3) 1 3\n"), "Index (0,1),(1,1) is cut multiple times."),
+    (dict(ordering="merge a b\nmerge a c\n"), "Patch a is merged multiple times."),
+    (dict(ordering="merge a b\nexpand a 1\n"),
+     "Tensor at (0,1) is added to non-empty patch a after a cut."),
+    (dict(ordering="expand a 1\ncut () 1 3\nexpand a 2\n"),
+     "Tensor at (1,0) is added to non-empty patch a after a cut."),
+    (dict(ordering="expand b 1\ncut () 1 3\nmerge a b\n"),
+     "Patch a is merged into non-empty patch b after a cut."),
+    (dict(ordering="merge a b\ncut () 1 3\nexpand b 1\n"),
+     "Tensor at (0,1) is added to non-empty patch b after a cut."),
+    (dict(ordering="merge a c\ncut () 1 3\nmerge b c\n"),
+     "Patch b is merged into non-empty patch c after a cut."),
     (dict(ordering="frobnicate a 1\n"), "Received an invalid operation in config."),
     (dict(ordering="expand a 9\n"), "Index 9 must be within grid boundaries."),
     (dict(ordering="expand a 4\n"), "Index must specify an active qubit."),
