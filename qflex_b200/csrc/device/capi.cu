@@ -268,6 +268,7 @@ int qfx_create(int device, qfx_ctx** ctx_out) {
   ctx->device = device;
   ctx->sm_count = sms;
   if (const char* e = getenv("QFLEX_TC_CHUNK")) ctx->tc_chunk = atoi(e);
+  if (const char* e = getenv("QFLEX_TC_DEBIAS")) ctx->tc_debias = atoi(e) != 0;
   cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&ctx->ev1);

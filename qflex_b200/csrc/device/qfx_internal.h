@@ -27,6 +27,7 @@ struct qfx_ctx {
   qfx_stats stats{};
   // per-launch profiling (qfx_profile_begin/end)
   int tc_chunk = 0;  // k blocks per TMEM accumulation chunk (0 = default)
+  bool tc_debias = true;  // compensate the tensor core's accumulation bias (tc_common.cuh)
   bool profiling = false;
   struct ProfRec {
     int kind, m, n, k;

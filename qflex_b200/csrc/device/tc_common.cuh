@@ -72,7 +72,31 @@ struct FusedArgs {
   float2* part;       // split-K partial results [ksplit][M][N] (natural layout)
   int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads (timing experiments)
   int8_t c_m[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
+  // Compensation of the tensor core's accumulation bias (tc_debias_scale below): what
+  // is read from a TMEM accumulator is multiplied by scale_full (an accumulator that
+  // integrated `chunk` k blocks) or scale_last (the shorter last chunk of a tile).
+  float scale_full, scale_last;
 };
+
+// The tcgen05 accumulator adds with round-toward-zero.  For data of random sign that
+// shrinks every result by the same expected factor, about 1.2e-8 per MMA instruction
+// accumulated into the same TMEM tile (measured: tools/tc_bias.py, profiles/
+// tc_bias_r2.log -- 24 instructions 2.7e-7, 48: 5.5e-7, 96: 1.27e-6).  One contraction
+// hides that inside its 4e-6 random error, but a bias adds up LINEARLY over the ~45
+// tensor-core contractions behind an amplitude of bristlecone_70 1-32-1 (measured
+// -5.6e-5 against the reference, the FFMA path: 1e-6) while the random parts add in
+// quadrature.  The epilogue therefore multiplies what it reads from TMEM by
+// 1 + beta(instructions); QFLEX_TC_DEBIAS=0 switches it off.
+inline float tc_debias_scale(int mma_instructions, bool enabled) {
+  if (!enabled || mma_instructions <= 0) return 1.0f;
+  static const double steps[] = {0, 6, 12, 24, 48, 96, 192};
+  static const double beta[] = {0, 0.6e-7, 1.3e-7, 2.7e-7, 5.5e-7, 1.27e-6, 2.9e-6};
+  const double t = (double)mma_instructions;
+  int i = 0;
+  while (i < 5 && t > steps[i + 1]) ++i;
+  const double f = (t - steps[i]) / (steps[i + 1] - steps[i]);
+  return (float)(1.0 + beta[i] + f * (beta[i + 1] - beta[i]));
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

@@ -355,12 +355,14 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
           if (p < npieces && !(g.dbg & 8)) {
             uint32_t r[16];
             tmem_ld16(t_row + (uint32_t)(p * 16), r);
+            // (scale: accumulation-bias compensation of this chunk, tc_common.cuh)
+            const float scale = (ch + 1 == g.nchunks) ? g.scale_last : g.scale_full;
             if (ch == 0) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) sum[p][j] = __uint_as_float(r[j]);
+              for (int j = 0; j < 16; ++j) sum[p][j] = __uint_as_float(r[j]) * scale;
             } else {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) sum[p][j] += __uint_as_float(r[j]);
+              for (int j = 0; j < 16; ++j) sum[p][j] = fmaf(__uint_as_float(r[j]), scale, sum[p][j]);
             }
           }
         }
@@ -557,6 +559,12 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   g.nkk = (int)std::min<uint64_t>(4, (2 * K) / 16);
   g.chunk = ctx->tc_chunk > 0 ? ctx->tc_chunk : 4;
   g.nchunks = (g.kblocks + g.chunk - 1) / g.chunk;
+  {
+    // MMA instructions per accumulator: 3 products x nkk k16-steps x k blocks
+    const int last = g.kblocks - (g.nchunks - 1) * g.chunk;
+    g.scale_full = tc_debias_scale(3 * g.nkk * std::min(g.chunk, g.kblocks), ctx->tc_debias);
+    g.scale_last = tc_debias_scale(3 * g.nkk * last, ctx->tc_debias);
+  }
   g.bn = (int)std::min<uint64_t>(2 * N, MAX_BN);
   g.tiles_n = (int)((2 * N) / g.bn);
   g.tiles = (int)((M / BM) * g.tiles_n);

@@ -474,6 +474,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
         for (int p = 0; p < 8; ++p)
           if (p < npieces && !(g.dbg & 8)) tmem_reg_fence(sum[p]);
+        {
+          const float scale = g.scale_full;  // accumulation-bias compensation
+#pragma unroll
+          for (int p = 0; p < 8; ++p)
+            if (p < npieces) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) sum[p][j] *= scale;
+            }
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
@@ -623,6 +632,7 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   g.nkk = (int)std::min<uint64_t>(4, (2 * K) / 16);
   g.chunk = g.kblocks;
   g.nchunks = 1;
+  g.scale_full = g.scale_last = tc_debias_scale(3 * g.nkk * g.kblocks, ctx->tc_debias);
   // UMMA N per instruction: 256, except N' = 256 where two n tiles of 128 (two
   // accumulators draining alternately) beat one of 256 (2^20 x 128 x 256: 0.61 ->
   // 0.51 ms).  For N' = 512, 128-wide tiles (8-KB B' slots, twice as many) measured

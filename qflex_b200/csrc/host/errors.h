@@ -8,6 +8,7 @@
 #include <ctime>
 #include <sstream>
 #include <string>
+#include <type_traits>
 
 namespace qflex::global {
 // Same process-wide knobs as the reference (src/global.h:9-15).
@@ -18,11 +19,31 @@ inline std::size_t track_memory_seconds = 0;
 
 namespace qflex::utils {
 
+// Appends one part of a message.  Strings, characters and integers take the direct
+// route (index names are built tens of thousands of times per plan; a stringstream per
+// name was a third of the planning time); everything else is formatted by operator<<
+// exactly as the reference's concat does (src/utils.h:14-27).
+namespace detail {
+inline void append(std::string& out, const std::string& v) { out += v; }
+inline void append(std::string& out, const char* v) { out += v; }
+inline void append(std::string& out, char v) { out += v; }
+template <typename T>
+void append(std::string& out, const T& v) {
+  if constexpr (std::is_integral_v<T> && !std::is_same_v<T, bool>) {
+    out += std::to_string(v);
+  } else {
+    std::stringstream ss;
+    ss << v;
+    out += ss.str();
+  }
+}
+}  // namespace detail
+
 template <typename... Ts>
 std::string concat(const Ts&... parts) {
-  std::stringstream ss;
-  (ss << ... << parts);
-  return ss.str();
+  std::string out;
+  (detail::append(out, parts), ...);
+  return out;
 }
 
 inline std::string get_date_time() {

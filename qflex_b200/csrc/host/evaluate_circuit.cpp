@@ -128,11 +128,12 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
   const auto fits = [&](const Plan& p) {
     return (double)p.arena_elems * sizeof(s_type) <= (double)global::memory_limit;
   };
+  PlanCache cache;  // phase 1 of BuildPlan, shared by the searches below
   auto plan_with = [&](bool cut_aware, Plan* result) {
     bool planned = false;
     auto try_open = [&](int n) {
       try {
-        Plan p = BuildPlan(*input, ordering, final_qubits, n, cut_aware);
+        Plan p = BuildPlan(*input, ordering, final_qubits, n, cut_aware, 0, &cache);
         if (p.open_outputs == 0 || !fits(p)) return false;
         *result = std::move(p);
         return true;
@@ -151,7 +152,7 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
         }
       }
     }
-    if (!planned) *result = BuildPlan(*input, ordering, final_qubits, 0, cut_aware);
+    if (!planned) *result = BuildPlan(*input, ordering, final_qubits, 0, cut_aware, 0, &cache);
     if (!fits(*result)) return;
 
     // Then undo as much of the bond-cut slicing as the memory limit allows (BuildPlan's
@@ -173,7 +174,7 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
     if (max_fuse <= 0) return;
     auto try_fuse = [&](int f, Plan* out) {
       try {
-        Plan p = BuildPlan(*input, ordering, final_qubits, n_open, cut_aware, f);
+        Plan p = BuildPlan(*input, ordering, final_qubits, n_open, cut_aware, f, &cache);
         if (p.open_outputs != n_open || !fits(p)) return false;
         *out = std::move(p);
         return true;

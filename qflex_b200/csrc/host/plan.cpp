@@ -380,7 +380,7 @@ bool cut_can_open(const ContractionOperation& op) {
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               int open_outputs, bool cut_aware_flatten, int fuse_bits) {
+               int open_outputs, bool cut_aware_flatten, int fuse_bits, PlanCache* cache) {
   Plan plan;
   // the LAST `open_outputs` openable terminal cuts of the ordering stay open (a later
   // cut enlarges fewer of the remaining patches)
@@ -395,8 +395,6 @@ Plan BuildPlan(const QflexInput& input,
   auto cut_stays_open = [&](const ContractionOperation& op, int) {
     return std::find(open_ops.begin(), open_ops.end(), &op) != open_ops.end();
   };
-  plan.flatten_steps.reserve(4096);  // PlanStep is ~300 bytes: avoid regrowth copies
-  plan.steps.reserve(512);
   const std::size_t I = input.grid.I, J = input.grid.J;
   const auto& off = input.grid.qubits_off;
   // (passing `off` to find_grid_coord_in_list would copy it into a std::optional on
@@ -407,223 +405,266 @@ Plan BuildPlan(const QflexInput& input,
   auto is_off = [&](std::size_t i, std::size_t j) {
     return i < I && j < J && off_mask[i * J + j] != 0;
   };
-
-  std::vector<std::vector<SiteNet>> net;
-  build_network(input, final_qubits, &net);
-
-  // ------------------------------------------ cut-aware flatten: project the gates
-  // bond cuts that open the ordering -> id of the cut (position among the kept cuts)
+  // Phase 1 (network, gate uploads, flatten steps, grid-tensor layouts: ~95 % of the
+  // planning time) does not depend on open_outputs / fuse_bits -- except, with the
+  // cut-aware flatten, on which leading terminal cuts stay open -- so the searches of
+  // PrepareCircuit over those two knobs reuse it through `cache`.
+  std::vector<const ContractionOperation*> phase1_key;
+  if (cut_aware_flatten) phase1_key = open_ops;
   std::map<std::string, int> pre_bond, pre_width;
-  std::vector<std::vector<char>> dynamic(I, std::vector<char>(J, 0));
-  if (cut_aware_flatten) {
-    int id = 0;
-    for (const auto& op : ordering) {
-      if (op.op_type != ContractionOperation::CUT) break;
-      if (cut_stays_open(op, 0)) continue;
-      if (op.cut.tensors.size() == 2) pre_bond[index_name(op.cut.tensors)] = id;
-      ++id;
+  std::vector<PlanStep> dyn_steps;
+  uint64_t work_base = 0, work_flatten = 0;
+  if (cache != nullptr && cache->valid && cache->cut_aware == cut_aware_flatten &&
+      cache->key == phase1_key) {
+    plan = cache->plan;
+    pre_bond = cache->pre_bond;
+    pre_width = cache->pre_width;
+    dyn_steps = cache->dyn_steps;
+    work_base = cache->work_base;
+    work_flatten = cache->work_flatten;
+  } else {
+    plan.flatten_steps.reserve(4096);  // PlanStep is ~300 bytes: avoid regrowth copies
+    plan.steps.reserve(512);
+
+    std::vector<std::vector<SiteNet>> net;
+    build_network(input, final_qubits, &net);
+
+    // ------------------------------------------ cut-aware flatten: project the gates
+    // bond cuts that open the ordering -> id of the cut (position among the kept cuts)
+    std::vector<std::vector<char>> dynamic(I, std::vector<char>(J, 0));
+    if (cut_aware_flatten) {
+      int id = 0;
+      for (const auto& op : ordering) {
+        if (op.op_type != ContractionOperation::CUT) break;
+        if (cut_stays_open(op, 0)) continue;
+        if (op.cut.tensors.size() == 2) pre_bond[index_name(op.cut.tensors)] = id;
+        ++id;
+      }
+      for (std::size_t i = 0; i < I; ++i)
+        for (std::size_t j = 0; j < J; ++j) {
+          // virtual legs of every pre-cut bond, in chain (= chronological) order
+          std::map<std::string, std::vector<std::pair<std::size_t, std::string>>> legs;
+          auto& chain = net[i][j].chain;
+          for (std::size_t k = 0; k < chain.size(); ++k)
+            for (const auto& ix : chain[k].sym.idx) {
+              auto it = net[i][j].virt_to_bond.find(ix.name);
+              if (it != net[i][j].virt_to_bond.end() && pre_bond.count(it->second))
+                legs[it->second].push_back({k, ix.name});
+            }
+          for (const auto& kv : legs) {
+            int total = 0;
+            for (const auto& leg : kv.second) {
+              const SymTensor& t = chain[leg.first].sym;
+              total += t.idx[t.find(leg.second)].bits;
+            }
+            pre_width[kv.first] = total;
+            // A slice of a bond of w bits carries ~2^(-w/2) of the amplitude: with
+            // hundreds of cut bits the partial amplitudes leave fp32's range (Sycamore
+            // m=20: 2^-220).  One side of the bond (its first site) takes a factor 2 per
+            // two projected bits -- exact in floating point -- undone in fp64 at the end.
+            const bool scale_here = kv.first.rfind(utils::concat("(", i, ",", j, "),"), 0) == 0;
+            int carry = 0;
+            int seen = 0;  // the first leg is the most significant field of the bond value
+            for (const auto& leg : kv.second) {
+              SymTensor& t = chain[leg.first].sym;
+              const int p = t.find(leg.second);
+              seen += t.idx[p].bits;
+              if (scale_here) {
+                carry += t.idx[p].bits;
+                for (; carry >= 2; carry -= 2) {
+                  for (auto& x : chain[leg.first].data) x *= 2.0f;
+                  ++plan.amp_scale_log2;
+                }
+              }
+              VarTerm term;
+              term.cut = pre_bond.at(kv.first);
+              term.shift = t.idx[p].pos;
+              term.from = total - seen;
+              term.width = t.idx[p].bits;
+              t.var.push_back(term);
+              t.idx.erase(t.idx.begin() + p);
+            }
+            dynamic[i][j] = 1;
+          }
+        }
     }
+
+    // ---------------------------------------------------------- arena: gates
+    uint64_t cursor = 0;
     for (std::size_t i = 0; i < I; ++i)
       for (std::size_t j = 0; j < J; ++j) {
-        // virtual legs of every pre-cut bond, in chain (= chronological) order
-        std::map<std::string, std::vector<std::pair<std::size_t, std::string>>> legs;
-        auto& chain = net[i][j].chain;
-        for (std::size_t k = 0; k < chain.size(); ++k)
-          for (const auto& ix : chain[k].sym.idx) {
+        for (auto& g : net[i][j].chain) {
+          g.sym.off = cursor;
+          PlanUpload up;
+          up.off = cursor;
+          up.data = g.data;
+          plan.uploads.push_back(std::move(up));
+          cursor = align_up(cursor + g.sym.size());
+        }
+        if (is_off(i, j)) continue;
+        // build_network closes every world line without a terminal cut with a delta
+        const bool open_leg = find_grid_coord_in_list(final_qubits, i, j);
+        plan.final_delta_upload.push_back(open_leg ? -1 : (int)plan.uploads.size() - 1);
+      }
+
+    // ------------------------------------------------- flatten: sizes first
+    plan.site.assign(I, std::vector<SymTensor>(J));
+    uint64_t max_chain = 1, max_dyn_chain = 0;
+    // The world-line products are derived ONCE here (bit tables, sizes); their arena
+    // offsets are filled in below, when the ping-pong buffers are placed.
+    std::vector<std::vector<std::vector<PlanStep>>> line_steps(
+        I, std::vector<std::vector<PlanStep>>(J));
+    std::vector<std::vector<SymTensor>> line_result(I, std::vector<SymTensor>(J));
+    for (std::size_t i = 0; i < I; ++i)
+      for (std::size_t j = 0; j < J; ++j) {
+        if (is_off(i, j)) continue;
+        if (net[i][j].chain.empty()) throw ERROR_MSG("Time-direction cannot be empty");
+        SymTensor a = net[i][j].chain[0].sym;
+        line_steps[i][j].reserve(net[i][j].chain.size());
+        for (std::size_t k = 1; k < net[i][j].chain.size(); ++k) {
+          line_steps[i][j].emplace_back();
+          a = make_contract(a, net[i][j].chain[k].sym, 0, &line_steps[i][j].back());
+          if (dynamic[i][j]) max_dyn_chain = std::max(max_dyn_chain, a.size());
+          else max_chain = std::max(max_chain, a.size());
+        }
+        line_result[i][j] = a;
+        // final layout: [(o)] ++ bonds ordered by consumption
+        SymTensor& site = plan.site[i][j];
+        if (find_grid_coord_in_list(final_qubits, i, j)) {
+          SymIndex o;
+          o.name = index_name({i, j}, {});
+          o.bits = 1;
+          site.idx.push_back(o);
+        }
+        std::vector<GridPos> pairs;
+        if (i > 0 && !is_off(i - 1, j)) pairs.push_back({i - 1, j});
+        if (j > 0 && !is_off(i, j - 1)) pairs.push_back({i, j - 1});
+        if (i + 1 < I && !is_off(i + 1, j)) pairs.push_back({i + 1, j});
+        if (j + 1 < J && !is_off(i, j + 1)) pairs.push_back({i, j + 1});
+        NeighbourOrder cmp{ordering, {i, j}};
+        std::sort(pairs.begin(), pairs.end(), cmp);
+        for (const auto& p : pairs) {
+          SymIndex b;
+          b.name = (p[0] < i || p[1] < j) ? index_name(p, {i, j}) : index_name({i, j}, p);
+          b.bits = 0;
+          for (const auto& ix : a.idx) {
             auto it = net[i][j].virt_to_bond.find(ix.name);
-            if (it != net[i][j].virt_to_bond.end() && pre_bond.count(it->second))
-              legs[it->second].push_back({k, ix.name});
+            if (it != net[i][j].virt_to_bond.end() && it->second == b.name) b.bits += ix.bits;
           }
-        for (const auto& kv : legs) {
-          int total = 0;
-          for (const auto& leg : kv.second) {
-            const SymTensor& t = chain[leg.first].sym;
-            total += t.idx[t.find(leg.second)].bits;
-          }
-          pre_width[kv.first] = total;
-          // A slice of a bond of w bits carries ~2^(-w/2) of the amplitude: with
-          // hundreds of cut bits the partial amplitudes leave fp32's range (Sycamore
-          // m=20: 2^-220).  One side of the bond (its first site) takes a factor 2 per
-          // two projected bits -- exact in floating point -- undone in fp64 at the end.
-          const bool scale_here = kv.first.rfind(utils::concat("(", i, ",", j, "),"), 0) == 0;
-          int carry = 0;
-          int seen = 0;  // the first leg is the most significant field of the bond value
-          for (const auto& leg : kv.second) {
-            SymTensor& t = chain[leg.first].sym;
-            const int p = t.find(leg.second);
-            seen += t.idx[p].bits;
-            if (scale_here) {
-              carry += t.idx[p].bits;
-              for (; carry >= 2; carry -= 2) {
-                for (auto& x : chain[leg.first].data) x *= 2.0f;
-                ++plan.amp_scale_log2;
-              }
-            }
-            VarTerm term;
-            term.cut = pre_bond.at(kv.first);
-            term.shift = t.idx[p].pos;
-            term.from = total - seen;
-            term.width = t.idx[p].bits;
-            t.var.push_back(term);
-            t.idx.erase(t.idx.begin() + p);
-          }
-          dynamic[i][j] = 1;
+          if (b.bits == 0 && pre_bond.count(b.name)) continue;  // projected in the gates
+          site.idx.push_back(b);
         }
+        site.make_dense();
+        if (site.rank_bits() != a.rank_bits())
+          throw ERROR_MSG("Flattened tensor at (", i, ",", j,
+                          ") has indices that are neither bonds nor outputs: ",
+                          tensor_to_string(a));
+        site.off = cursor;
+        cursor = align_up(cursor + site.size());
       }
-  }
+    // sites flattened inside the slice loop share one ping-pong pair of their own (the
+    // work region below belongs to the patches by then)
+    const uint64_t dyn_ping = cursor, dyn_pong = cursor + align_up(max_dyn_chain);
+    if (max_dyn_chain > 0) cursor = dyn_pong + align_up(max_dyn_chain);
+    work_base = cursor;
+    // Ping-pong buffers of the world-line products.  One pair PER SITE when that is
+    // affordable (<= 2^26 elements = 512 MB in all): the chains are then independent
+    // and run concurrently (qfx_contract_chains); otherwise one shared pair and the
+    // sites are flattened one after the other.
+    uint64_t n_sites = 0;
+    for (std::size_t i = 0; i < I; ++i)
+      for (std::size_t j = 0; j < J; ++j)
+        if (!is_off(i, j) && !dynamic[i][j]) ++n_sites;
+    const uint64_t pair_elems = 2 * align_up(max_chain);
+    plan.flatten_parallel = n_sites * pair_elems <= (uint64_t(1) << 26);
+    work_flatten = plan.flatten_parallel ? n_sites * pair_elems : pair_elems;
 
-  // ---------------------------------------------------------- arena: gates
-  uint64_t cursor = 0;
-  for (std::size_t i = 0; i < I; ++i)
-    for (std::size_t j = 0; j < J; ++j) {
-      for (auto& g : net[i][j].chain) {
-        g.sym.off = cursor;
-        PlanUpload up;
-        up.off = cursor;
-        up.data = g.data;
-        plan.uploads.push_back(std::move(up));
-        cursor = align_up(cursor + g.sym.size());
-      }
-      if (is_off(i, j)) continue;
-      // build_network closes every world line without a terminal cut with a delta
-      const bool open_leg = find_grid_coord_in_list(final_qubits, i, j);
-      plan.final_delta_upload.push_back(open_leg ? -1 : (int)plan.uploads.size() - 1);
-    }
-
-  // ------------------------------------------------- flatten: sizes first
-  plan.site.assign(I, std::vector<SymTensor>(J));
-  uint64_t max_chain = 1, max_dyn_chain = 0;
-  for (std::size_t i = 0; i < I; ++i)
-    for (std::size_t j = 0; j < J; ++j) {
-      if (is_off(i, j)) continue;
-      if (net[i][j].chain.empty()) throw ERROR_MSG("Time-direction cannot be empty");
-      SymTensor a = net[i][j].chain[0].sym;
-      for (std::size_t k = 1; k < net[i][j].chain.size(); ++k) {
-        PlanStep dummy;
-        a = make_contract(a, net[i][j].chain[k].sym, 0, &dummy);
-        if (dynamic[i][j]) max_dyn_chain = std::max(max_dyn_chain, a.size());
-        else max_chain = std::max(max_chain, a.size());
-      }
-      // final layout: [(o)] ++ bonds ordered by consumption
-      SymTensor& site = plan.site[i][j];
-      if (find_grid_coord_in_list(final_qubits, i, j)) {
-        SymIndex o;
-        o.name = index_name({i, j}, {});
-        o.bits = 1;
-        site.idx.push_back(o);
-      }
-      std::vector<GridPos> pairs;
-      if (i > 0 && !is_off(i - 1, j)) pairs.push_back({i - 1, j});
-      if (j > 0 && !is_off(i, j - 1)) pairs.push_back({i, j - 1});
-      if (i + 1 < I && !is_off(i + 1, j)) pairs.push_back({i + 1, j});
-      if (j + 1 < J && !is_off(i, j + 1)) pairs.push_back({i, j + 1});
-      NeighbourOrder cmp{ordering, {i, j}};
-      std::sort(pairs.begin(), pairs.end(), cmp);
-      for (const auto& p : pairs) {
-        SymIndex b;
-        b.name = (p[0] < i || p[1] < j) ? index_name(p, {i, j}) : index_name({i, j}, p);
-        b.bits = 0;
+    // ------------------------------------------------- flatten: real steps
+    for (std::size_t i = 0; i < I; ++i)
+      for (std::size_t j = 0; j < J; ++j) {
+        if (is_off(i, j)) continue;
+        const auto& chain = net[i][j].chain;
+        const bool dyn = dynamic[i][j] != 0;
+        std::vector<PlanStep>& out_steps = dyn ? dyn_steps : plan.flatten_steps;
+        const std::size_t first_step = out_steps.size();
+        const int chain_id = dyn ? -1 : plan.n_chains++;
+        const uint64_t ping =
+            dyn ? dyn_ping
+                : work_base + (plan.flatten_parallel ? (uint64_t)chain_id * pair_elems : 0);
+        const uint64_t pong = dyn ? dyn_pong : ping + align_up(max_chain);
+        SymTensor a = std::move(line_result[i][j]);
+        if (chain.size() == 1) a = chain[0].sym;
+        bool in_ping = false;
+        uint64_t prev = chain[0].sym.off;
+        for (std::size_t k = 1; k < chain.size(); ++k) {
+          PlanStep& st = line_steps[i][j][k - 1];
+          st.level = 0;
+          st.chain = chain_id;
+          st.label = utils::concat("flatten (", i, ",", j, ") gate ", k);
+          const uint64_t dst = in_ping ? pong : ping;
+          st.desc.off_a = prev;  // the running product (first: the initial delta)
+          st.desc.off_c = dst;
+          st.desc.precision = QFX_PREC_FFMA;
+          prev = dst;
+          in_ping = !in_ping;
+          out_steps.push_back(std::move(st));
+        }
+        if (chain.size() > 1) a.off = prev;
+        // one permute into the final layout
+        const SymTensor& site = plan.site[i][j];
+        PlanStep pm;
+        pm.kind = PlanStep::PERMUTE;
+        pm.level = 0;
+        pm.chain = chain_id;
+        pm.label = utils::concat("flatten (", i, ",", j, ") layout");
+        pm.src = a.off;
+        pm.dst = site.off;
+        pm.n_bits = a.rank_bits();
+        // destination position of every source index: (o) keeps its name, virtual
+        // legs land inside their bond in chronological order (first = slowest)
+        std::map<std::string, int> bond_fill;  // bits already placed, from the top
+        bool identity = true;
         for (const auto& ix : a.idx) {
+          int dpos;
           auto it = net[i][j].virt_to_bond.find(ix.name);
-          if (it != net[i][j].virt_to_bond.end() && it->second == b.name) b.bits += ix.bits;
+          if (it == net[i][j].virt_to_bond.end()) {
+            const int s = site.find(ix.name);
+            if (s < 0)
+              throw ERROR_MSG("Index ", ix.name, " of flattened tensor (", i, ",", j,
+                              ") has no place in the grid tensor.");
+            dpos = site.idx[s].pos;
+          } else {
+            const int s = site.find(it->second);
+            int& used = bond_fill[it->second];
+            used += ix.bits;
+            dpos = site.idx[s].pos + site.idx[s].bits - used;
+          }
+          for (int b = 0; b < ix.bits; ++b) {
+            pm.dst_pos[ix.pos + b] = (int8_t)(dpos + b);
+            if (ix.pos + b != dpos + b) identity = false;
+          }
         }
-        if (b.bits == 0 && pre_bond.count(b.name)) continue;  // projected in the gates
-        site.idx.push_back(b);
-      }
-      site.make_dense();
-      if (site.rank_bits() != a.rank_bits())
-        throw ERROR_MSG("Flattened tensor at (", i, ",", j,
-                        ") has indices that are neither bonds nor outputs: ",
-                        tensor_to_string(a));
-      site.off = cursor;
-      cursor = align_up(cursor + site.size());
-    }
-  // sites flattened inside the slice loop share one ping-pong pair of their own (the
-  // work region below belongs to the patches by then)
-  const uint64_t dyn_ping = cursor, dyn_pong = cursor + align_up(max_dyn_chain);
-  if (max_dyn_chain > 0) cursor = dyn_pong + align_up(max_dyn_chain);
-  std::vector<PlanStep> dyn_steps;
-  const uint64_t work_base = cursor;
-  // Ping-pong buffers of the world-line products.  One pair PER SITE when that is
-  // affordable (<= 2^26 elements = 512 MB in all): the chains are then independent
-  // and run concurrently (qfx_contract_chains); otherwise one shared pair and the
-  // sites are flattened one after the other.
-  uint64_t n_sites = 0;
-  for (std::size_t i = 0; i < I; ++i)
-    for (std::size_t j = 0; j < J; ++j)
-      if (!is_off(i, j) && !dynamic[i][j]) ++n_sites;
-  const uint64_t pair_elems = 2 * align_up(max_chain);
-  plan.flatten_parallel = n_sites * pair_elems <= (uint64_t(1) << 26);
-  uint64_t work_flatten = plan.flatten_parallel ? n_sites * pair_elems : pair_elems;
-
-  // ------------------------------------------------- flatten: real steps
-  for (std::size_t i = 0; i < I; ++i)
-    for (std::size_t j = 0; j < J; ++j) {
-      if (is_off(i, j)) continue;
-      const auto& chain = net[i][j].chain;
-      const bool dyn = dynamic[i][j] != 0;
-      std::vector<PlanStep>& out_steps = dyn ? dyn_steps : plan.flatten_steps;
-      const std::size_t first_step = out_steps.size();
-      const int chain_id = dyn ? -1 : plan.n_chains++;
-      const uint64_t ping =
-          dyn ? dyn_ping
-              : work_base + (plan.flatten_parallel ? (uint64_t)chain_id * pair_elems : 0);
-      const uint64_t pong = dyn ? dyn_pong : ping + align_up(max_chain);
-      SymTensor a = chain[0].sym;
-      bool in_ping = false;
-      for (std::size_t k = 1; k < chain.size(); ++k) {
-        PlanStep st;
-        st.level = 0;
-        st.chain = chain_id;
-        st.label = utils::concat("flatten (", i, ",", j, ") gate ", k);
-        const uint64_t dst = in_ping ? pong : ping;
-        a = make_contract(a, chain[k].sym, dst, &st);
-        st.desc.precision = QFX_PREC_FFMA;
-        in_ping = !in_ping;
-        out_steps.push_back(std::move(st));
-      }
-      // one permute into the final layout
-      const SymTensor& site = plan.site[i][j];
-      PlanStep pm;
-      pm.kind = PlanStep::PERMUTE;
-      pm.level = 0;
-      pm.chain = chain_id;
-      pm.label = utils::concat("flatten (", i, ",", j, ") layout");
-      pm.src = a.off;
-      pm.dst = site.off;
-      pm.n_bits = a.rank_bits();
-      // destination position of every source index: (o) keeps its name, virtual
-      // legs land inside their bond in chronological order (first = slowest)
-      std::map<std::string, int> bond_fill;  // bits already placed, from the top
-      bool identity = true;
-      for (const auto& ix : a.idx) {
-        int dpos;
-        auto it = net[i][j].virt_to_bond.find(ix.name);
-        if (it == net[i][j].virt_to_bond.end()) {
-          const int s = site.find(ix.name);
-          if (s < 0)
-            throw ERROR_MSG("Index ", ix.name, " of flattened tensor (", i, ",", j,
-                            ") has no place in the grid tensor.");
-          dpos = site.idx[s].pos;
+        if (identity && out_steps.size() > first_step && chain.size() > 1) {
+          // last world-line product can write the grid tensor directly
+          out_steps.back().desc.off_c = site.off;
         } else {
-          const int s = site.find(it->second);
-          int& used = bond_fill[it->second];
-          used += ix.bits;
-          dpos = site.idx[s].pos + site.idx[s].bits - used;
-        }
-        for (int b = 0; b < ix.bits; ++b) {
-          pm.dst_pos[ix.pos + b] = (int8_t)(dpos + b);
-          if (ix.pos + b != dpos + b) identity = false;
+          pm.bytes = 16.0 * (double)(1ull << pm.n_bits);
+          out_steps.push_back(std::move(pm));
         }
       }
-      if (identity && out_steps.size() > first_step && chain.size() > 1) {
-        // last world-line product can write the grid tensor directly
-        out_steps.back().desc.off_c = site.off;
-      } else {
-        pm.bytes = 16.0 * (double)(1ull << pm.n_bits);
-        out_steps.push_back(std::move(pm));
-      }
+
+    if (cache != nullptr) {
+      cache->valid = true;
+      cache->cut_aware = cut_aware_flatten;
+      cache->key = phase1_key;
+      cache->plan = plan;
+      cache->pre_bond = pre_bond;
+      cache->pre_width = pre_width;
+      cache->dyn_steps = dyn_steps;
+      cache->work_base = work_base;
+      cache->work_flatten = work_flatten;
     }
+  }
 
   // ------------------------------------------------- fused cut bits
   // A bond cut slices the contraction over the values of one bond so that the patches
@@ -719,7 +760,7 @@ Plan BuildPlan(const QflexInput& input,
       }
     }
   }
-  cursor = work_base;
+  uint64_t cursor = work_base;
   std::map<uint64_t, uint64_t> spare;  // result size -> spare slot offset
   for (auto& kv : patches) {
     if (kv.second.need == 0) continue;

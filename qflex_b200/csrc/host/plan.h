@@ -23,6 +23,7 @@
 #include <complex>
 #include <cstdint>
 #include <list>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -150,6 +151,19 @@ struct Plan {
   int fused_bits = 0;
 };
 
+struct ContractionOperation;
+// Phase-1 results of BuildPlan kept between calls on the SAME (input, ordering,
+// final_qubits); see BuildPlan.
+struct PlanCache {
+  bool valid = false;
+  bool cut_aware = false;
+  std::vector<const ContractionOperation*> key;
+  Plan plan;  // uploads, flatten steps, site layouts
+  std::map<std::string, int> pre_bond, pre_width;
+  std::vector<PlanStep> dyn_steps;
+  uint64_t work_base = 0, work_flatten = 0;
+};
+
 // Builds the full plan.  `final_qubits` = qubits with a terminal cut
 // (EvaluateCircuit passes get_output_states' list).  Throws std::string.
 //
@@ -180,7 +194,8 @@ struct Plan {
 Plan BuildPlan(const QflexInput& input,
                const std::list<ContractionOperation>& ordering,
                const std::vector<std::vector<std::size_t>>& final_qubits,
-               int open_outputs = 0, bool cut_aware_flatten = false, int fuse_bits = 0);
+               int open_outputs = 0, bool cut_aware_flatten = false, int fuse_bits = 0,
+               PlanCache* cache = nullptr);
 
 struct ExecStats {
   double seconds_upload = 0, seconds_flatten = 0, seconds_contract = 0;

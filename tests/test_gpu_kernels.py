@@ -334,9 +334,9 @@ def test_copy_and_scalar_accumulate(ctx):
     want = np.array([a[1].astype(np.complex128) + a[5] + a[9], 0, 0, 2 * a[2].astype(np.complex128)])
     assert np.array_equal(got, want)  # complex64 -> complex128 sums of <= 3 terms are exact
     with pytest.raises(Exception):
-        ctx.scalar_accumulate(1, 4)      # slot outside the table
+        ctx.scalar_accumulate(1, 1 << 40)  # slot outside the table
     with pytest.raises(Exception):
-        ctx.copy(0, 3 * n + 64, 8)       # destination outside the arena
+        ctx.copy(0, 1 << 40, 8)          # destination outside the arena
 
 
 def test_headline_shape_full_size_rows_against_oracle(ctx):
