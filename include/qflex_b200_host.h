@@ -57,6 +57,16 @@ void* qflex_b200_prepare_sharded(const char* circuit_text, const char* ordering_
                                  const char* final_state, uint64_t memory_limit_bytes,
                                  int device, int precision, int world, char* err,
                                  uint64_t err_cap);
+/* Same on SEVERAL GPUs driven by this one process: every listed device holds the
+ * network, the slices of `rank` are dealt over them (one host thread per GPU), the
+ * partial amplitudes are summed on the host.  The single-process form of multi-GPU
+ * (the reference's EvaluateCircuit / CLI are single-process, src/main.cpp:129); the
+ * one-process-per-GPU form is rank/world + one all-reduce (qflex_b200/sharded.py). */
+void* qflex_b200_prepare_on(const char* circuit_text, const char* ordering_text,
+                            const char* grid_text, const char* initial_state,
+                            const char* final_state, uint64_t memory_limit_bytes,
+                            const int* devices, int n_devices, int precision, int world,
+                            char* err, uint64_t err_cap);
 /* ... then run the contraction schedule any number of times.  Only the slices
  * dealt to `rank` of `world` are executed; sum the partial amplitudes across
  * ranks (NCCL all-reduce).  Returns the number of amplitudes or -1. */

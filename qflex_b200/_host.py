@@ -176,6 +176,11 @@ class HostLibrary:
             ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
             ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
             ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_prepare_on.restype = ctypes.c_void_p
+        c.qflex_b200_prepare_on.argtypes = [
+            ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
+            ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+            ctypes.c_int, ctypes.c_char_p, ctypes.c_uint64]
         c.qflex_b200_contract.restype = ctypes.c_long
         c.qflex_b200_contract.argtypes = [
             ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
@@ -205,10 +210,20 @@ class HostLibrary:
         self._c.qflex_b200_set_verbose(int(level))
 
     def prepare(self, circuit, ordering, grid, initial_state="", final_state="",
-                memory_limit=None, device=0, precision="auto", world=1):
+                memory_limit=None, device=0, precision="auto", world=1, devices=None):
         """`world` = number of ranks the slices will be dealt over by contract(rank,
-        world): the planner keeps at least that many slices apart."""
+        world): the planner keeps at least that many slices apart.  `devices` = list of
+        GPUs THIS process drives (one host thread each; overrides `device`)."""
         err = ctypes.create_string_buffer(1 << 16)
+        if devices:
+            arr = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
+            h = self._c.qflex_b200_prepare_on(
+                _text(circuit), _text(ordering), _text(grid), _text(initial_state),
+                _text(final_state), _memory_bytes(memory_limit), arr, len(devices),
+                PRECISIONS[precision], int(world), err, len(err))
+            if not h:
+                raise QflexError(err.value.decode())
+            return Prepared(self, h)
         h = self._c.qflex_b200_prepare_sharded(
             _text(circuit), _text(ordering), _text(grid), _text(initial_state),
             _text(final_state), _memory_bytes(memory_limit), device,

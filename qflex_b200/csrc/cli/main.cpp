@@ -14,6 +14,7 @@
 
 #include "../host/errors.h"
 #include "../host/evaluate_circuit.h"
+#include "../host/memory.h"
 
 namespace {
 
@@ -25,7 +26,7 @@ std::string usage() {
 
   Usage:
     qflex_b200.x <circuit_filename> <ordering_filename> <grid_filename> [<initial_conf> <final_conf> <verbosity_level> <memory_limit> <track_memory_seconds>]
-    qflex_b200.x -c <circuit_filename> -o <ordering_filename> -g <grid_filename> [--initial-conf=<initial_conf> --final-conf=<final_conf> --verbosity=<verbosity_level> --memory=<memory_limit> --track-memory=<seconds>] [--device=<id>] [--precision=<auto|ffma|bf16x3>]
+    qflex_b200.x -c <circuit_filename> -o <ordering_filename> -g <grid_filename> [--initial-conf=<initial_conf> --final-conf=<final_conf> --verbosity=<verbosity_level> --memory=<memory_limit> --track-memory=<seconds>] [--device=<id> | --devices=<list>] [--precision=<auto|ffma|bf16x3>]
     qflex_b200.x (-h | --help)
     qflex_b200.x --version
 
@@ -38,11 +39,13 @@ std::string usage() {
       qflex::global::verbose, R"(].
     -m,--memory=<memory_limit>             Memory limit [default: )",
       qflex::utils::readable_memory_string((double)qflex::global::memory_limit), R"(].
-    -t,--track-memory=<seconds>            Accepted for compatibility [default: )",
+    -t,--track-memory=<seconds>            If <verbosity_level> > 0, track memory usage [default: )",
       qflex::global::track_memory_seconds, R"(].
     --initial-conf=<initial_conf>          Initial configuration.
     --final-conf=<final_conf>              Final configuration.
     --device=<id>                          CUDA device [default: 0].
+    --devices=<list>                       Several GPUs, e.g. 0,1,2,3 or all: the cut slices are
+                                           dealt over them (default: $QFLEX_DEVICES).
     --precision=<mode>                     auto | ffma | bf16x3 [default: auto].
     --version                              Show version.
 )");
@@ -60,7 +63,7 @@ Args parse(int argc, char** argv) {
       {"-v", "--verbosity"}, {"-m", "--memory"}, {"-t", "--track-memory"}};
   static const std::vector<std::string> longs = {
       "--circuit", "--ordering", "--grid", "--verbosity", "--memory",
-      "--track-memory", "--initial-conf", "--final-conf", "--device", "--precision"};
+      "--track-memory", "--initial-conf", "--final-conf", "--device", "--devices", "--precision"};
   Args a;
   for (int i = 1; i < argc; ++i) {
     std::string tok = argv[i];
@@ -150,6 +153,13 @@ int main(int argc, char** argv) {
 
     qflex::DevicePlacement where;
     if (args.opt.count("--device")) where.device = std::stoi(args.opt.at("--device"));
+    if (args.opt.count("--devices")) where.devices = qflex::ParseDeviceList(args.opt.at("--devices"));
+    else if (const char* e = getenv("QFLEX_DEVICES")) where.devices = qflex::ParseDeviceList(e);
+    // --track-memory: the reference's SIGALRM report (src/main.cpp:108-112), host + device
+    if (qflex::global::verbose > 0 && qflex::global::track_memory_seconds > 0) {
+      signal(SIGALRM, qflex::memory::print_memory_usage);
+      alarm(qflex::global::track_memory_seconds);
+    }
     if (args.opt.count("--precision")) {
       const std::string p = args.opt.at("--precision");
       if (p == "auto") where.precision = QFX_PREC_AUTO;

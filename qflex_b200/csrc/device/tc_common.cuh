@@ -80,8 +80,9 @@ struct FusedArgs {
 
 // The tcgen05 accumulator adds with round-toward-zero.  For data of random sign that
 // shrinks every result by the same expected factor, about 1.2e-8 per MMA instruction
-// accumulated into the same TMEM tile (measured: tools/tc_bias.py, profiles/
-// tc_bias_r2.log -- 24 instructions 2.7e-7, 48: 5.5e-7, 96: 1.27e-6).  One contraction
+// accumulated into the same TMEM tile (measured: tools/tc_bias.py,
+// profiles/tc_bias_r2_off.log -- 24 instructions 2.7e-7, 48: 5.5e-7, 96: 1.27e-6; with
+// the compensation, profiles/tc_bias_r2_on.log: within +-7e-8).  One contraction
 // hides that inside its 4e-6 random error, but a bias adds up LINEARLY over the ~45
 // tensor-core contractions behind an amplitude of bristlecone_70 1-32-1 (measured
 // -5.6e-5 against the reference, the FFMA path: 1e-6) while the random parts add in

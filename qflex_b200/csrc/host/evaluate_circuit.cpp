@@ -165,7 +165,7 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
     double slices = 1;
     for (const auto& c : result->cuts)
       if (!c.terminal) slices *= (double)std::max<std::size_t>(1, c.values.size());
-    const int ranks = std::max(1, where.world);
+    const int ranks = std::max(1, where.world) * std::max<int>(1, (int)where.devices.size());
     if (slices >= ranks) {
       int cap = 0;
       while (slices / (double)(uint64_t(2) << cap) >= ranks) ++cap;
@@ -255,7 +255,10 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
 
   for (const auto& q : final_qubits)
     prepared->output_positions.push_back(find_output_pos(input, q));
-  prepared->session = std::make_unique<Session>(std::move(plan), where.device);
+  prepared->session =
+      where.devices.empty()
+          ? std::make_unique<Session>(std::move(plan), where.device)
+          : std::make_unique<Session>(std::move(plan), where.devices);
   lap("Time spent creating 2D grid of tensors on the device: ");
   return prepared;
 }
@@ -293,9 +296,33 @@ std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
   return result;
 }
 
+std::vector<int> ParseDeviceList(const std::string& text) {
+  std::vector<int> out;
+  if (text.empty()) return out;
+  if (text == "all") {
+    int n = 0;
+    if (qfx_device_count(&n) != QFX_OK) throw ERROR_MSG("No CUDA device: ", qfx_last_error());
+    for (int d = 0; d < n; ++d) out.push_back(d);
+    return out;
+  }
+  std::size_t pos = 0;
+  while (pos <= text.size()) {
+    const std::size_t comma = std::min(text.find(',', pos), text.size());
+    const std::string item = text.substr(pos, comma - pos);
+    if (item.empty() || item.find_first_not_of("0123456789") != std::string::npos)
+      throw ERROR_MSG("Device list '", text, "' must be comma-separated device numbers or 'all'.");
+    out.push_back(std::atoi(item.c_str()));
+    pos = comma + 1;
+  }
+  return out;
+}
+
 std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
     QflexInput* input) {
-  return EvaluateCircuit(input, DevicePlacement{}, nullptr);
+  // the reference's signature; the GPUs come from the environment
+  DevicePlacement where;
+  if (const char* e = getenv("QFLEX_DEVICES")) where.devices = ParseDeviceList(e);
+  return EvaluateCircuit(input, where, nullptr);
 }
 
 }  // namespace qflex

@@ -30,6 +30,9 @@ std::string get_output_states(
 // single-process; defaults reproduce it: device 0, rank 0 of 1).
 struct DevicePlacement {
   int device = 0;
+  // several GPUs driven by THIS process (empty: `device` alone).  EvaluateCircuit(input)
+  // and the CLI fill it from QFLEX_DEVICES ("0,1,2,3" or "all") / --devices.
+  std::vector<int> devices;
   int rank = 0;
   int world = 1;
   int precision = QFX_PREC_AUTO;
@@ -55,6 +58,9 @@ struct PreparedCircuit {
 };
 std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
                                                 const DevicePlacement& where);
+
+// "0,2,5" -> {0, 2, 5}; "all" -> every visible device; "" -> {}.  Throws on garbage.
+std::vector<int> ParseDeviceList(const std::string& text);
 
 }  // namespace qflex
 

@@ -130,10 +130,12 @@ class Runner {
 }  // namespace
 
 namespace {
-int choose_lanes(const Plan& plan) {
+// lanes per device
+int choose_lanes(const Plan& plan, int n_devices) {
   if (const char* e = getenv("QFLEX_LANES")) return std::max(1, std::min(16, atoi(e)));
   uint64_t slices = 1;
   for (const auto& c : plan.cuts) slices *= std::max<uint64_t>(1, c.values.size());
+  slices = std::max<uint64_t>(1, slices / (uint64_t)std::max(1, n_devices));
   const double arena_bytes = (double)plan.arena_elems * 8.0;
   // lanes only for networks whose arena is small next to the GPU (<= 2 GB each, 4 GB
   // in all): their kernels run for microseconds and do not fill the SMs
@@ -156,24 +158,47 @@ int choose_lanes(const Plan& plan) {
 }
 }  // namespace
 
-Session::Session(Plan plan, int device) : plan_(std::move(plan)), device_(device) {
-  check(qfx_create(device, &ctx_), "qfx_create");
-  lanes_.push_back(ctx_);
+Session::Session(Plan plan, int device) : Session(std::move(plan), std::vector<int>{device}) {}
+
+Session::Session(Plan plan, std::vector<int> devices)
+    : plan_(std::move(plan)), devices_(std::move(devices)) {
+  if (devices_.empty()) devices_.push_back(0);
   try {
     const double t0 = now_s();
-    const int n_lanes = choose_lanes(plan_);
-    check(qfx_arena_reserve(ctx_, plan_.arena_elems), "qfx_arena_reserve");
-    check(qfx_amps_reserve(ctx_, plan_.n_amplitudes), "qfx_amps_reserve");
-    for (int l = 1; l < n_lanes; ++l) {
-      // an extra lane that cannot get its arena is dropped, not fatal
+    // One lane per device first (each must get its arena), then further lanes device
+    // by device while they fit: lanes_[l * n_devices + d] is lane l of device d, so the
+    // dealing in Contract() reaches every device before any second lane.
+    for (const int d : devices_) {
       qfx_ctx* c = nullptr;
-      if (qfx_create(device, &c) != QFX_OK) break;
-      if (qfx_arena_reserve(c, plan_.arena_elems) != QFX_OK ||
-          qfx_amps_reserve(c, plan_.n_amplitudes) != QFX_OK) {
-        qfx_destroy(c);
+      check(qfx_create(d, &c), "qfx_create");
+      lanes_.push_back(c);
+      check(qfx_arena_reserve(c, plan_.arena_elems), "qfx_arena_reserve");
+      check(qfx_amps_reserve(c, plan_.n_amplitudes), "qfx_amps_reserve");
+    }
+    ctx_ = lanes_[0];
+    const int n_lanes = choose_lanes(plan_, (int)devices_.size());
+    for (int l = 1; l < n_lanes; ++l) {
+      // an extra round of lanes that cannot get its arenas is dropped, not fatal
+      std::vector<qfx_ctx*> round;
+      bool ok = true;
+      for (const int d : devices_) {
+        qfx_ctx* c = nullptr;
+        if (qfx_create(d, &c) != QFX_OK) {
+          ok = false;
+          break;
+        }
+        round.push_back(c);
+        if (qfx_arena_reserve(c, plan_.arena_elems) != QFX_OK ||
+            qfx_amps_reserve(c, plan_.n_amplitudes) != QFX_OK) {
+          ok = false;
+          break;
+        }
+      }
+      if (!ok) {
+        for (qfx_ctx* c : round) qfx_destroy(c);
         break;
       }
-      lanes_.push_back(c);
+      lanes_.insert(lanes_.end(), round.begin(), round.end());
     }
     Upload();
     const double t1 = now_s();
@@ -203,19 +228,23 @@ void Session::Upload() {
     hi = std::max<uint64_t>(hi, up.off + up.data.size());
   }
   if (hi - lo > (uint64_t(1) << 24)) {  // scattered uploads: keep them separate
-    for (qfx_ctx* c : lanes_)
+    for (qfx_ctx* c : lanes_) {
+      check(qfx_bind_thread(c), "qfx_bind_thread");
       for (const auto& up : plan_.uploads)
         check(qfx_upload(c, up.off, reinterpret_cast<const float*>(up.data.data()),
                          up.data.size()),
               "qfx_upload");
+    }
     return;
   }
   std::vector<s_type> staged(hi - lo, s_type(0.f, 0.f));
   for (const auto& up : plan_.uploads)
     std::copy(up.data.begin(), up.data.end(), staged.begin() + (up.off - lo));
-  for (qfx_ctx* c : lanes_)
+  for (qfx_ctx* c : lanes_) {
+    check(qfx_bind_thread(c), "qfx_bind_thread");
     check(qfx_upload(c, lo, reinterpret_cast<const float*>(staged.data()), staged.size()),
           "qfx_upload");
+  }
 }
 
 void Session::SetFinalState(const std::string& final_state) {
@@ -242,8 +271,14 @@ void Session::SetFinalState(const std::string& final_state) {
 void Session::Flatten() {
   // replicated on every rank and lane: site tensors are MB-scale.  Launches are
   // asynchronous, so the lanes' flattens overlap on the device.
-  for (qfx_ctx* c : lanes_) PrepareLane(c);
-  for (qfx_ctx* c : lanes_) check(qfx_sync(c), "qfx_sync");
+  for (qfx_ctx* c : lanes_) {
+    check(qfx_bind_thread(c), "qfx_bind_thread");
+    PrepareLane(c);
+  }
+  for (qfx_ctx* c : lanes_) {
+    check(qfx_bind_thread(c), "qfx_bind_thread");
+    check(qfx_sync(c), "qfx_sync");
+  }
 }
 
 void Session::PrepareLane(qfx_ctx* ctx) {

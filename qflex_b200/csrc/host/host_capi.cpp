@@ -118,6 +118,26 @@ void* qflex_b200_prepare_sharded(const char* circuit_text, const char* ordering_
   QFLEX_CAPI_CATCH(nullptr)
 }
 
+void* qflex_b200_prepare_on(const char* circuit_text, const char* ordering_text,
+                            const char* grid_text, const char* initial_state,
+                            const char* final_state, uint64_t memory_limit_bytes,
+                            const int* devices, int n_devices, int precision, int world,
+                            char* err, uint64_t err_cap) {
+  try {
+    if (memory_limit_bytes) qflex::global::memory_limit = memory_limit_bytes;
+    if (devices == nullptr || n_devices < 1) throw std::string("empty device list");
+    qflex::QflexInput input;
+    load_input(&input, circuit_text, ordering_text, grid_text, initial_state, final_state);
+    qflex::DevicePlacement where;
+    where.devices.assign(devices, devices + n_devices);
+    where.device = devices[0];
+    where.precision = precision;
+    where.world = world < 1 ? 1 : world;
+    return qflex::PrepareCircuit(&input, where).release();
+  }
+  QFLEX_CAPI_CATCH(nullptr)
+}
+
 void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
                          const char* grid_text, const char* initial_state,
                          const char* final_state, uint64_t memory_limit_bytes,

@@ -212,6 +212,12 @@ struct ExecStats {
 class Session {
  public:
   Session(Plan plan, int device);
+  // The same plan resident on SEVERAL GPUs of this process (the reference's
+  // EvaluateCircuit and CLI are single-process, src/main.cpp:129): every device gets
+  // its own arena(s) and flattened network, one host thread per lane drives it, the
+  // slices of this rank are dealt over (lane, device) and the partial amplitude tables
+  // are summed on the host in a fixed order -- 16 bytes per amplitude, no collective.
+  Session(Plan plan, std::vector<int> devices);
   ~Session();
   Session(const Session&) = delete;
   Session& operator=(const Session&) = delete;
@@ -228,6 +234,7 @@ class Session {
 
   const Plan& plan() const { return plan_; }
   int lanes() const { return (int)lanes_.size(); }
+  int devices() const { return (int)devices_.size(); }
   const ExecStats& stats() const { return stats_; }
 
   // Per-launch device timing of the next Contract() calls, by shape class
@@ -250,8 +257,8 @@ class Session {
   // lane-major, so that few slices still reach every rank),
   // each driven by its own host thread, and kernels of different slices overlap on
   // the GPU.  One lane when the arena is large (the kernels fill the GPU).
-  std::vector<qfx_ctx*> lanes_;
-  int device_ = 0;
+  std::vector<qfx_ctx*> lanes_;  // [lane * n_devices + device index]
+  std::vector<int> devices_;
   ExecStats stats_;
   bool profile_ = false;
   std::vector<qfx_profile_row> profile_rows_;

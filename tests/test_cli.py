@@ -63,3 +63,18 @@ def test_positional_and_flag_forms_agree():
              "-g", _cfg("grid", "test.txt"), "--memory=2GB")
     assert a.returncode == 0 and b.returncode == 0
     assert a.stdout == b.stdout
+
+
+@pytest.mark.gpu
+def test_devices_flag_deals_the_slices_over_contexts(golden):
+    a = _run(_cfg("circuits", "test.txt"), _cfg("ordering", "test.txt"), _cfg("grid", "test.txt"))
+    b = _run("-c", _cfg("circuits", "test.txt"), "-o", _cfg("ordering", "test.txt"),
+             "-g", _cfg("grid", "test.txt"), "--devices=0,0")
+    assert a.returncode == 0 and b.returncode == 0, b.stderr
+    va = [complex(*map(float, l.split(": ")[1].split())) for l in a.stdout.splitlines() if "-->" in l]
+    vb = [complex(*map(float, l.split(": ")[1].split())) for l in b.stdout.splitlines() if "-->" in l]
+    assert len(va) == len(vb) == len(golden["test"]["states"])
+    assert np.allclose(va, vb, rtol=0, atol=1e-6)
+    bad = _run("-c", _cfg("circuits", "test.txt"), "-o", _cfg("ordering", "test.txt"),
+               "-g", _cfg("grid", "test.txt"), "--devices=a,b")
+    assert bad.returncode == 2 and "Device list" in bad.stderr

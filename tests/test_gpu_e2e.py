@@ -332,3 +332,51 @@ def test_sycamore_m16_cut_aware_flatten_paths_agree(gpu_lib, monkeypatch):
     monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", "0")
     with pytest.raises(Exception, match="2\\^32"):
         gpu_lib.evaluate(*texts, memory_limit=64 << 30)
+
+
+def test_several_contexts_of_one_process_sum_to_the_golden(gpu_lib, golden):
+    """The single-process multi-GPU path (QFLEX_DEVICES / --devices): on a one-GPU box the
+    same device listed twice stands for two GPUs -- two arenas, two streams, two host
+    threads, host-side sum."""
+    import torch
+    n = torch.cuda.device_count()
+    devices = list(range(n)) if n > 1 else [0, 0]
+    for name in ("bristlecone_70_1-24-1_16slices", "sycamore_53_8_2slices_64amps"):
+        case = support.CASES[name]
+        p = gpu_lib.prepare(*support.case_texts(case), memory_limit=16 << 30, devices=devices)
+        amps = p.contract()
+        states, want = _amps(golden, name)
+        assert p.states == states and p.stats["lanes"] >= len(devices)
+        assert support.rel_err(amps, want) < TOL
+        p.close()
+
+
+def test_batch_of_final_states_on_a_resident_circuit(gpu_lib):
+    """f3: simulate() with a list of final states parses, plans and uploads once; each
+    further bitstring rewrites the closing deltas and re-runs the ms-scale flatten.  Must
+    equal one EvaluateCircuit per bitstring, and be much cheaper."""
+    import time
+    import qflex_b200
+    case = dict(circuit="sycamore_53_8_0.txt", ordering="sycamore_53.txt", grid="sycamore_53.txt",
+                cut_values=[[0, 1, 2, 3], [0], [0]] + [[0, 1]] * 6)
+    c, o, g = support.case_texts(case)
+    rng = np.random.default_rng(11)
+    finals = ["".join(rng.choice(["0", "1"], 53)) for _ in range(24)]
+    opts = dict(circuit=c.splitlines(), ordering=o.splitlines(), grid=g.splitlines(),
+                memory_limit=8 << 30)
+    qflex_b200.simulate(dict(opts, final_states=finals[:2]), lib=gpu_lib)  # warm
+    t0 = time.perf_counter()
+    batch = qflex_b200.simulate(dict(opts, final_states=finals), lib=gpu_lib)
+    t_batch = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    single = []
+    for f in finals:
+        single.extend(qflex_b200.simulate(dict(opts, final_state=f), lib=gpu_lib))
+    t_single = time.perf_counter() - t0
+    assert len(batch) == len(single) == 64 * len(finals)
+    assert [s for s, _ in batch] == [s for s, _ in single]
+    assert support.rel_err([a for _, a in batch], [a for _, a in single]) < 1e-6
+    assert np.linalg.norm([a for _, a in batch]) > 0
+    assert t_batch < t_single, (t_batch, t_single)
+    print("batched simulate: %.1f ms per state vs %.1f ms" % (1e3 * t_batch / len(finals),
+                                                              1e3 * t_single / len(finals)))

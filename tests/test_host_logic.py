@@ -350,3 +350,49 @@ def test_rank_shares_without_a_dealt_cut(emul, world, ordering):
     total = sum(p.contract(r, world) for r in range(world))
     assert support.rel_err(total, full) < 1e-12
     p.close()
+
+
+@pytest.mark.parametrize("name", ["bristlecone_70_1-12-1", "bristlecone_48_1-16-1",
+                                  "rect2x2_cutfree_0110", "test"])
+@pytest.mark.parametrize("devices", [[0, 1], [0, 1, 2, 3, 4, 5, 6, 7]])
+def test_one_process_driving_several_devices(emul, golden, name, devices):
+    """Multi-GPU inside the drop-in entry points (what QFLEX_DEVICES / --devices select):
+    every device holds the network, the slices are dealt over (lane, device), partial
+    amplitudes are summed on the host.  On the emulated ABI a device is just a context."""
+    case = support.CASES[name]
+    c, o, g = support.case_texts(case)
+    p = emul.prepare(c, o, g, case.get("initial", ""), case.get("final", ""),
+                     memory_limit=8 << 30, devices=devices)
+    amps = p.contract()
+    states, want = _amps(golden, name)
+    assert p.states == states
+    assert support.rel_err(amps, want) < TOL
+    assert p.stats["lanes"] >= len(devices)
+    one = emul.prepare(c, o, g, case.get("initial", ""), case.get("final", ""), memory_limit=8 << 30)
+    one.contract()
+    assert p.stats["leaves"] == one.stats["leaves"]  # every leaf exactly once
+    # ... and on top of a rank split: 2 ranks x these devices
+    parts = sum(p.contract(r, 2) for r in range(2))
+    assert support.rel_err(parts, want) < TOL
+    p.close()
+    one.close()
+
+
+def test_device_list_from_the_environment(emul, golden, monkeypatch):
+    """The reference-signature entry point EvaluateCircuit(QflexInput*) (and with it the
+    unmodified reference front-ends) picks its GPUs from QFLEX_DEVICES."""
+    import subprocess
+    import sys
+    cli = os.path.join(support.ROOT, "tests", "_build", "refsrc_emul", "qflex_refmain.x")
+    if not os.path.exists(cli):
+        pytest.skip("reference front-end not built (needs /root/reference)")
+    cfg = support.CONFIG
+    args = [cli, cfg + "/circuits/test.txt", cfg + "/ordering/test.txt", cfg + "/grid/test.txt"]
+    base = subprocess.run(args, stdout=subprocess.PIPE, text=True, env=dict(os.environ)).stdout
+    multi = subprocess.run(args, stdout=subprocess.PIPE, text=True,
+                           env=dict(os.environ, QFLEX_DEVICES="0,1,2")).stdout
+    assert base.strip() and [l.split(":")[0] for l in base.splitlines()] == \
+        [l.split(":")[0] for l in multi.splitlines()]
+    bad = subprocess.run(args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                         env=dict(os.environ, QFLEX_DEVICES="0;1"))
+    assert bad.returncode == 2 and "Device list" in bad.stderr
