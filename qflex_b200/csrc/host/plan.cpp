@@ -2,6 +2,8 @@
 #include "plan.h"
 
 #include <algorithm>
+#include <cstdlib>
+#include <functional>
 #include <cstring>
 #include <map>
 #include <set>
@@ -515,17 +517,74 @@ Plan BuildPlan(const QflexInput& input,
     std::vector<std::vector<std::vector<PlanStep>>> line_steps(
         I, std::vector<std::vector<PlanStep>>(J));
     std::vector<std::vector<SymTensor>> line_result(I, std::vector<SymTensor>(J));
+    // tree-ordered world lines (dynamic sites): per step, whether operand a / b is an
+    // intermediate (offset relative to the dyn region) or a gate tensor (absolute)
+    std::vector<std::vector<std::vector<std::pair<bool, bool>>>> line_rel(
+        I, std::vector<std::vector<std::pair<bool, bool>>>(J));
+    uint64_t max_dyn_tree = 0;
+    const bool tree_lines = [] {
+      const char* e = getenv("QFLEX_WORLDLINE_TREE");
+      return e == nullptr || e[0] != '0';
+    }();
     for (std::size_t i = 0; i < I; ++i)
       for (std::size_t j = 0; j < J; ++j) {
         if (is_off(i, j)) continue;
         if (net[i][j].chain.empty()) throw ERROR_MSG("Time-direction cannot be empty");
         SymTensor a = net[i][j].chain[0].sym;
         line_steps[i][j].reserve(net[i][j].chain.size());
-        for (std::size_t k = 1; k < net[i][j].chain.size(); ++k) {
-          line_steps[i][j].emplace_back();
-          a = make_contract(a, net[i][j].chain[k].sym, 0, &line_steps[i][j].back());
-          if (dynamic[i][j]) max_dyn_chain = std::max(max_dyn_chain, a.size());
-          else max_chain = std::max(max_chain, a.size());
+        if (dynamic[i][j] && tree_lines && net[i][j].chain.size() > 2) {
+          // A site flattened inside the slice loop pays for every byte of every
+          // intermediate once per slice.  Left to right, each of the last gates is a
+          // pass over the full-size tensor (Sycamore m=16: ~80 passes over 2^24
+          // elements per slice).  As a balanced tree -- split where the virtual-leg
+          // bits left and right are closest -- only the root writes a full-size
+          // tensor; the halves are about its square root.  Same factors, same
+          // contracted legs, same index order of the result (concatenation is
+          // associative); intermediates are bump-allocated in the dyn region.
+          const auto& chain = net[i][j].chain;
+          std::vector<int> bits_before(chain.size() + 1, 0);
+          for (std::size_t k = 0; k < chain.size(); ++k) {
+            int vb = 0;
+            for (const auto& ix : chain[k].sym.idx)
+              if (net[i][j].virt_to_bond.count(ix.name)) vb += ix.bits;
+            bits_before[k + 1] = bits_before[k] + vb;
+          }
+          uint64_t bump = 0;
+          auto& steps_out = line_steps[i][j];
+          auto& rel_out = line_rel[i][j];
+          std::function<SymTensor(std::size_t, std::size_t, bool*)> build =
+              [&](std::size_t lo, std::size_t hi, bool* is_rel) -> SymTensor {
+            if (hi - lo == 1) {
+              *is_rel = false;
+              return chain[lo].sym;
+            }
+            std::size_t mid = lo + 1;
+            int best = 1 << 30;
+            for (std::size_t m = lo + 1; m < hi; ++m) {
+              const int l = bits_before[m] - bits_before[lo], r = bits_before[hi] - bits_before[m];
+              const int d = std::abs(l - r) * 64 + (int)std::min<std::size_t>(63, m > (lo + hi) / 2 ? m - (lo + hi) / 2 : (lo + hi) / 2 - m);
+              if (d < best) best = d, mid = m;
+            }
+            bool lrel = false, rrel = false;
+            SymTensor L = build(lo, mid, &lrel);
+            SymTensor R = build(mid, hi, &rrel);
+            steps_out.emplace_back();
+            SymTensor C = make_contract(L, R, bump, &steps_out.back());
+            rel_out.push_back({lrel, rrel});
+            bump = align_up(bump + C.size());
+            *is_rel = true;
+            return C;
+          };
+          bool top_rel = false;
+          a = build(0, chain.size(), &top_rel);
+          max_dyn_tree = std::max(max_dyn_tree, bump);
+        } else {
+          for (std::size_t k = 1; k < net[i][j].chain.size(); ++k) {
+            line_steps[i][j].emplace_back();
+            a = make_contract(a, net[i][j].chain[k].sym, 0, &line_steps[i][j].back());
+            if (dynamic[i][j]) max_dyn_chain = std::max(max_dyn_chain, a.size());
+            else max_chain = std::max(max_chain, a.size());
+          }
         }
         line_result[i][j] = a;
         // final layout: [(o)] ++ bonds ordered by consumption
@@ -566,6 +625,7 @@ Plan BuildPlan(const QflexInput& input,
     // work region below belongs to the patches by then)
     const uint64_t dyn_ping = cursor, dyn_pong = cursor + align_up(max_dyn_chain);
     if (max_dyn_chain > 0) cursor = dyn_pong + align_up(max_dyn_chain);
+    cursor = std::max(cursor, dyn_ping + align_up(max_dyn_tree));  // (the two share the region)
     work_base = cursor;
     // Ping-pong buffers of the world-line products.  One pair PER SITE when that is
     // affordable (<= 2^26 elements = 512 MB in all): the chains are then independent
@@ -596,7 +656,22 @@ Plan BuildPlan(const QflexInput& input,
         if (chain.size() == 1) a = chain[0].sym;
         bool in_ping = false;
         uint64_t prev = chain[0].sym.off;
-        for (std::size_t k = 1; k < chain.size(); ++k) {
+        const bool as_tree = !line_rel[i][j].empty();
+        if (as_tree) {
+          for (std::size_t k = 0; k < line_steps[i][j].size(); ++k) {
+            PlanStep& st = line_steps[i][j][k];
+            st.level = 0;
+            st.chain = chain_id;
+            st.label = utils::concat("flatten (", i, ",", j, ") tree step ", k + 1);
+            if (line_rel[i][j][k].first) st.desc.off_a += dyn_ping;
+            if (line_rel[i][j][k].second) st.desc.off_b += dyn_ping;
+            st.desc.off_c += dyn_ping;
+            st.desc.precision = QFX_PREC_FFMA;
+            prev = st.desc.off_c;
+            out_steps.push_back(std::move(st));
+          }
+        }
+        for (std::size_t k = 1; k < chain.size() && !as_tree; ++k) {
           PlanStep& st = line_steps[i][j][k - 1];
           st.level = 0;
           st.chain = chain_id;
@@ -644,9 +719,21 @@ Plan BuildPlan(const QflexInput& input,
             if (ix.pos + b != dpos + b) identity = false;
           }
         }
+        static const bool fold_layout = [] {
+          const char* e = getenv("QFLEX_FOLD_LAYOUT");
+          return e != nullptr && e[0] == '1';
+        }();
         if (identity && out_steps.size() > first_step && chain.size() > 1) {
           // last world-line product can write the grid tensor directly
           out_steps.back().desc.off_c = site.off;
+        } else if (as_tree && fold_layout && out_steps.size() > first_step) {
+          // the root of the tree writes the grid tensor in its final layout: the
+          // permute (one more read + write of the full tensor per slice) is folded
+          // into the root's C bit table
+          qfx_contract_desc& d = out_steps.back().desc;
+          for (int q = 0; q < d.m_bits; ++q) d.c_m[q] = pm.dst_pos[d.c_m[q]];
+          for (int q = 0; q < d.n_bits; ++q) d.c_n[q] = pm.dst_pos[d.c_n[q]];
+          d.off_c = site.off;
         } else {
           pm.bytes = 16.0 * (double)(1ull << pm.n_bits);
           out_steps.push_back(std::move(pm));

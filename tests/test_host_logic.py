@@ -258,8 +258,19 @@ def test_cut_aware_flatten_is_bit_identical(emul, monkeypatch, name):
     monkeypatch.setenv("QFLEX_FUSE_BITS", "0")  # slice by slice, as the ordering is written
     r0, s0 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
     monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", "1")
+    monkeypatch.setenv("QFLEX_WORLDLINE_TREE", "0")  # world lines left to right, as the reference
     r1, s1 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
     assert r0 == r1
+    # default: the in-loop world lines are contracted as balanced trees (same factors,
+    # another association order: equal to rounding), optionally writing the grid tensor
+    # in its final layout from the root
+    for fold in ("0", "1"):
+        monkeypatch.setenv("QFLEX_WORLDLINE_TREE", "1")
+        monkeypatch.setenv("QFLEX_FOLD_LAYOUT", fold)
+        r2, s2 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
+        assert [s for s, _ in r2] == [s for s, _ in r0]
+        assert support.rel_err([a for _, a in r2], [a for _, a in r0]) < 1e-5
+        assert s2["bytes"] <= s1["bytes"]
     has_bond_cut = any(l.split("#")[0].strip().startswith("cut") and len(l.split(")")[1].split()) == 2
                        for l in texts[1].splitlines() if l.split("#")[0].strip())
     if has_bond_cut:
