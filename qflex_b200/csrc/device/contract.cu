@@ -490,9 +490,11 @@ __global__ void __launch_bounds__(kDotThreads)
 }
 
 // ---------------------------------------------------------------- stream_small
-// C[m, n] = sum_k A[m, k] * B[k, n] with N, K <= 4 and a long M: one world-line step
+// C[m, n] = sum_k A[m, k] * B[k, n] with N, K <= 8 and a long M: one world-line step
 // of a large grid tensor (cut-aware flatten of Sycamore m >= 14: 2^28..2^30 elements
-// times a 1- or 2-qubit gate).  Pure streaming, AI < 1 flop/B: the tiled GEMM spent
+// times a 1- or 2-qubit gate), or the expansion of a patch by a grid tensor with
+// bond dimension <= 8 (bristlecone 1-24-1: 2^24 x 8 x 8, AI 4 flop/B).  Pure
+// streaming: the tiled GEMM spent
 // its time on per-tile bookkeeping (0.95 TB/s).  One thread per m, m enumerated in
 // A-address order; the m bits are grouped into runs that are contiguous in both A and
 // C so that an address is a few shift-mask-or steps; B lives in shared memory.
@@ -505,27 +507,29 @@ struct StreamArgs {
   float2* C;
   int m_bits, n_bits, k_bits, n_seg;
   int c_vec;  // the n bits are C's lowest address bits and C's base is even: 16-byte stores
+  int a_vec;  // the k bits are A's lowest address bits and A's base is even: 16-byte loads
   StreamSeg seg[8];
-  int8_t a_k[2], b_k[2], b_n[2], c_n[2];
+  int8_t a_k[3], b_k[3], b_n[3], c_n[3];
 };
 
+template <int KB, int NB>
 __global__ void __launch_bounds__(256) stream_small(const __grid_constant__ StreamArgs g) {
-  __shared__ float2 Bs[16];
-  __shared__ unsigned long long ka[4], cn[4];
-  const int K = 1 << g.k_bits, N = 1 << g.n_bits;
+  constexpr int K = 1 << KB, N = 1 << NB;
+  __shared__ float2 Bs[K * N];
+  __shared__ unsigned long long ka[K], cn[N];
   if ((int)threadIdx.x < K * N) {
     const int k = threadIdx.x / N, n = threadIdx.x % N;
     unsigned long long o = 0;
-    for (int q = 0; q < g.k_bits; ++q) o |= (unsigned long long)((k >> q) & 1) << g.b_k[q];
-    for (int q = 0; q < g.n_bits; ++q) o |= (unsigned long long)((n >> q) & 1) << g.b_n[q];
+    for (int q = 0; q < KB; ++q) o |= (unsigned long long)((k >> q) & 1) << g.b_k[q];
+    for (int q = 0; q < NB; ++q) o |= (unsigned long long)((n >> q) & 1) << g.b_n[q];
     Bs[threadIdx.x] = g.B[o];
   }
-  if (threadIdx.x < 4) {
+  if (threadIdx.x < 8) {
     unsigned long long oa = 0, oc = 0;
-    for (int q = 0; q < g.k_bits; ++q) oa |= (unsigned long long)((threadIdx.x >> q) & 1) << g.a_k[q];
-    for (int q = 0; q < g.n_bits; ++q) oc |= (unsigned long long)((threadIdx.x >> q) & 1) << g.c_n[q];
-    ka[threadIdx.x] = oa;
-    cn[threadIdx.x] = oc;
+    for (int q = 0; q < KB; ++q) oa |= (unsigned long long)((threadIdx.x >> q) & 1) << g.a_k[q];
+    for (int q = 0; q < NB; ++q) oc |= (unsigned long long)((threadIdx.x >> q) & 1) << g.c_n[q];
+    if ((int)threadIdx.x < K) ka[threadIdx.x] = oa;
+    if ((int)threadIdx.x < N) cn[threadIdx.x] = oc;
   }
   __syncthreads();
   const unsigned long long M = 1ull << g.m_bits;
@@ -539,17 +543,30 @@ __global__ void __launch_bounds__(256) stream_small(const __grid_constant__ Stre
       ao |= f << g.seg[s].a_shift;
       co |= f << g.seg[s].c_shift;
     }
-    float2 a[4];
-    for (int k = 0; k < K; ++k) a[k & 3] = __ldg(A + (ao | ka[k]));
+    float2 a[K];
+    if (g.a_vec && K >= 2) {
+      // the k bits are A's lowest address bits: one row = K contiguous elements
+#pragma unroll
+      for (int k = 0; k < K; k += 2) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(A + ao + k));
+        a[k] = make_float2(v.x, v.y);
+        a[k + 1] = make_float2(v.z, v.w);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < K; ++k) a[k] = __ldg(A + (ao | ka[k]));
+    }
     float2 prev = make_float2(0.f, 0.f);
+#pragma unroll
     for (int n = 0; n < N; ++n) {
       float sx = 0.f, sy = 0.f;
+#pragma unroll
       for (int k = 0; k < K; ++k) {
         const float2 b = Bs[k * N + n];
-        sx = fmaf(a[k & 3].x, b.x, sx);
-        sx = fmaf(-a[k & 3].y, b.y, sx);
-        sy = fmaf(a[k & 3].x, b.y, sy);
-        sy = fmaf(a[k & 3].y, b.x, sy);
+        sx = fmaf(a[k].x, b.x, sx);
+        sx = fmaf(-a[k].y, b.y, sx);
+        sy = fmaf(a[k].x, b.y, sy);
+        sy = fmaf(a[k].y, b.x, sy);
       }
       if (!g.c_vec) {
         C[co | cn[n]] = make_float2(sx, sy);
@@ -559,6 +576,25 @@ __global__ void __launch_bounds__(256) stream_small(const __grid_constant__ Stre
         prev = make_float2(sx, sy);
       }
     }
+  }
+}
+
+template <int KB>
+void launch_stream_small_n(const StreamArgs& g, unsigned blocks, cudaStream_t stream) {
+  switch (g.n_bits) {
+    case 0: stream_small<KB, 0><<<blocks, 256, 0, stream>>>(g); break;
+    case 1: stream_small<KB, 1><<<blocks, 256, 0, stream>>>(g); break;
+    case 2: stream_small<KB, 2><<<blocks, 256, 0, stream>>>(g); break;
+    default: stream_small<KB, 3><<<blocks, 256, 0, stream>>>(g); break;
+  }
+}
+
+void launch_stream_small(const StreamArgs& g, unsigned blocks, cudaStream_t stream) {
+  switch (g.k_bits) {
+    case 0: launch_stream_small_n<0>(g, blocks, stream); break;
+    case 1: launch_stream_small_n<1>(g, blocks, stream); break;
+    case 2: launch_stream_small_n<2>(g, blocks, stream); break;
+    default: launch_stream_small_n<3>(g, blocks, stream); break;
   }
 }
 
@@ -893,8 +929,12 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
   }
 
   // ---------------- tiny N and K, long M: streaming kernel
-  if (!accumulate_amp && d.m_bits >= 16 && d.n_bits <= 2 && d.k_bits <= 2 &&
-      getenv("QFLEX_NO_STREAM") == nullptr) {
+  static const int stream_max_bits = [] {
+    const char* e = getenv("QFLEX_STREAM_BITS");
+    return e ? std::max(0, std::min(3, atoi(e))) : 3;
+  }();
+  if (!accumulate_amp && d.m_bits >= 16 && d.n_bits <= stream_max_bits &&
+      d.k_bits <= stream_max_bits && getenv("QFLEX_NO_STREAM") == nullptr) {
     StreamArgs g{};
     g.A = A;
     g.B = B;
@@ -912,6 +952,9 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     g.c_vec = (d.n_bits >= 1 && !(d.off_c & 1)) ? 1 : 0;
     for (int q = 0; q < d.n_bits; ++q)
       if (d.c_n[q] != q) g.c_vec = 0;
+    g.a_vec = (d.k_bits >= 1 && !(d.off_a & 1)) ? 1 : 0;
+    for (int q = 0; q < d.k_bits; ++q)
+      if (d.a_k[q] != q) g.a_vec = 0;
     bool ok = true;
     for (int i = 0; i < d.m_bits;) {
       int j = i + 1;
@@ -929,7 +972,7 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
       const unsigned long long M = 1ull << d.m_bits;
       const unsigned blocks =
           (unsigned)std::min<unsigned long long>(M / 256, 16ull * ctx->sm_count);
-      stream_small<<<blocks, 256, 0, ctx->stream>>>(g);
+      launch_stream_small(g, blocks, ctx->stream);
       QFX_CUDA(cudaGetLastError());
       ctx->stats.launches_gemm_ffma++;
       ctx->stats.launches_total++;

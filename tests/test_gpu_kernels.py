@@ -85,7 +85,9 @@ def test_contract_few_outputs_long_k_gemv(ctx, outs, k, seed, side):
 
 
 @pytest.mark.parametrize("m,n,k", [(16, 1, 1), (18, 2, 1), (17, 0, 2), (20, 2, 2), (16, 0, 0),
-                                   (19, 1, 2), (21, 1, 0), (1, 17, 1), (2, 18, 2)])
+                                   (19, 1, 2), (21, 1, 0), (1, 17, 1), (2, 18, 2), (16, 3, 3),
+                                   (18, 3, 2), (17, 2, 3), (20, 3, 3), (16, 0, 3), (16, 3, 0),
+                                   (3, 19, 3)])
 def test_contract_long_m_tiny_n_k_streaming(ctx, m, n, k):
     """World-line steps on large grid tensors (cut-aware flatten): N, K <= 4, long M."""
     rng = np.random.default_rng(77 * m + 10 * n + k)

@@ -98,3 +98,50 @@ def test_single_process_is_the_identity_collective(emul, golden):
     p.close()
     g = golden[name]
     assert support.rel_err(got, np.array(g["re"]) + 1j * np.array(g["im"])) < 1e-4
+
+
+BATCH_WORKER = r"""
+import json, os, sys
+sys.path.insert(0, %(root)r)
+import numpy as np
+import torch.distributed as dist
+from tests import support
+from qflex_b200 import sharded
+dist.init_process_group("gloo")
+lib = support.emulated_host_library()
+fix = json.load(open(os.path.join(%(root)r, "tests", "golden", "simulation_fixtures.json")))
+finals = %(finals)r
+p = lib.prepare(fix["circuit_test"], fix["ordering_with_cuts_test"], fix["grid_test"], "", finals[0])
+res = sharded.simulate_final_states(p, finals)
+p.close()
+print("RESULT " + json.dumps({"rank": dist.get_rank(), "states": [s for s, _ in res],
+      "re": [a.real for _, a in res], "im": [a.imag for _, a in res]}))
+dist.destroy_process_group()
+"""
+
+
+def test_final_states_dealt_over_ranks_and_gathered():
+    """A batch of output bitstrings on a resident circuit: bitstring i goes to rank
+    i % world, one all-gather returns all amplitudes in request order (5 states on 2
+    ranks: the padding of the short rank must not leak into the result)."""
+    import json as _json
+    from tests import statevector
+    fix = _json.load(open(os.path.join(support.ROOT, "tests", "golden", "simulation_fixtures.json")))
+    psi = statevector.final_state_vector(fix["circuit_test"])
+    finals = [bin(x)[2:].zfill(16) for x in (3, 40000, 65535, 1, 777)]
+    support.emulated_host_library()
+    port = _free_port()
+    code = BATCH_WORKER % dict(root=support.ROOT, finals=finals)
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r),
+                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), OMP_NUM_THREADS="2")
+        procs.append(subprocess.Popen([sys.executable, "-c", code], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    for p in procs:
+        out, err = p.communicate(timeout=300)
+        assert p.returncode == 0, err[-3000:]
+        got = json.loads([l for l in out.splitlines() if l.startswith("RESULT ")][-1][7:])
+        assert got["states"] == finals
+        for s, re_, im_ in zip(got["states"], got["re"], got["im"]):
+            assert abs(complex(re_, im_) - psi[int(s, 2)]) < 1e-6
