@@ -57,6 +57,15 @@ void* qflex_b200_prepare_sharded(const char* circuit_text, const char* ordering_
                                  const char* final_state, uint64_t memory_limit_bytes,
                                  int device, int precision, int world, char* err,
                                  uint64_t err_cap);
+/* A resident circuit planned for a BATCH of final states (qflex_b200_set_final_state):
+ * every qubit keeps its output leg on its grid tensor and the final state is a set of
+ * projection offsets, so another bitstring costs the contraction alone -- no upload,
+ * no flatten.  Falls back to the plain plan when the doubled grid tensors do not fit. */
+void* qflex_b200_prepare_batch(const char* circuit_text, const char* ordering_text,
+                               const char* grid_text, const char* initial_state,
+                               const char* final_state, uint64_t memory_limit_bytes,
+                               int device, int precision, int world, char* err,
+                               uint64_t err_cap);
 /* Same on SEVERAL GPUs driven by this one process: every listed device holds the
  * network, the slices of `rank` are dealt over them (one host thread per GPU), the
  * partial amplitudes are summed on the host.  The single-process form of multi-GPU

@@ -176,6 +176,8 @@ class HostLibrary:
             ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
             ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
             ctypes.c_char_p, ctypes.c_uint64]
+        c.qflex_b200_prepare_batch.restype = ctypes.c_void_p
+        c.qflex_b200_prepare_batch.argtypes = c.qflex_b200_prepare_sharded.argtypes
         c.qflex_b200_prepare_on.restype = ctypes.c_void_p
         c.qflex_b200_prepare_on.argtypes = [
             ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p,
@@ -210,10 +212,12 @@ class HostLibrary:
         self._c.qflex_b200_set_verbose(int(level))
 
     def prepare(self, circuit, ordering, grid, initial_state="", final_state="",
-                memory_limit=None, device=0, precision="auto", world=1, devices=None):
+                memory_limit=None, device=0, precision="auto", world=1, devices=None,
+                batch=False):
         """`world` = number of ranks the slices will be dealt over by contract(rank,
         world): the planner keeps at least that many slices apart.  `devices` = list of
-        GPUs THIS process drives (one host thread each; overrides `device`)."""
+        GPUs THIS process drives (one host thread each; overrides `device`).  `batch`:
+        plan for many final states (set_final_state then costs no upload / flatten)."""
         err = ctypes.create_string_buffer(1 << 16)
         if devices:
             arr = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
@@ -224,7 +228,8 @@ class HostLibrary:
             if not h:
                 raise QflexError(err.value.decode())
             return Prepared(self, h)
-        h = self._c.qflex_b200_prepare_sharded(
+        entry = self._c.qflex_b200_prepare_batch if batch else self._c.qflex_b200_prepare_sharded
+        h = entry(
             _text(circuit), _text(ordering), _text(grid), _text(initial_state),
             _text(final_state), _memory_bytes(memory_limit), device,
             PRECISIONS[precision], int(world), err, len(err))
@@ -322,7 +327,7 @@ def simulate(options, lib=None):
         prepared = lib.prepare(
             circuit, ordering, grid, initial[0], final[0],
             memory_limit=options.get("memory_limit"), device=options.get("device", 0),
-            precision=options.get("precision", "auto"), world=world)
+            precision=options.get("precision", "auto"), world=world, batch=True)
         try:
             result = []
             for n, state in enumerate(final):

@@ -107,6 +107,40 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
   if (input->initial_state.empty()) input->initial_state = std::string(n_active, '0');
 
   auto prepared = std::make_unique<PreparedCircuit>();
+  if (where.resident_finals) {
+    // one projected terminal cut per qubit the ordering does not cut itself, in front
+    // of everything else (a cut must precede the use of its tensor); value = the
+    // qubit's bit of the requested final state
+    std::vector<char> has_cut(input->grid.I * input->grid.J, 0);
+    for (const auto& op : ordering)
+      if (op.op_type == ContractionOperation::CUT && op.cut.tensors.size() == 1)
+        has_cut[op.cut.tensors[0][0] * input->grid.J + op.cut.tensors[0][1]] = 1;
+    std::vector<char> off(input->grid.I * input->grid.J, 0);
+    for (const auto& q : input->grid.qubits_off)
+      if (q.size() == 2 && q[0] < input->grid.I && q[1] < input->grid.J)
+        off[q[0] * input->grid.J + q[1]] = 1;
+    if (!input->final_state.empty() && input->final_state.size() != n_active)
+      throw ERROR_MSG("Size of final_conf: ", input->final_state.size(),
+                      ", must be equal to size of initial_conf: ", n_active, ".");
+    std::list<ContractionOperation> cuts;
+    std::size_t a = 0;
+    int id = 0;
+    for (std::size_t q = 0; q < off.size(); ++q) {
+      if (off[q]) continue;
+      if (has_cut[q]) {
+        prepared->state_cut.push_back(-1);
+      } else {
+        const char c = input->final_state.empty() ? '0' : input->final_state[a];
+        if (c != '0' && c != '1')
+          throw ERROR_MSG("Final state has non-binary character ", c, " at index ", a,
+                          "despite having no terminal cut there.");
+        cuts.emplace_back(CutIndex({get_qubit_coords(q, input->grid.J)}, {std::size_t(c - '0')}));
+        prepared->state_cut.push_back(id++);
+      }
+      ++a;
+    }
+    ordering.splice(ordering.begin(), cuts);
+  }
   std::vector<std::vector<std::size_t>> final_qubits;
   try {
     input->final_state =
@@ -265,6 +299,27 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
 
 void PreparedCircuit::SetFinalState(const std::string& final_state) {
   if (!session) throw ERROR_MSG("Circuit is not resident.");
+  if (!state_cut.empty()) {
+    // every non-output qubit carries a projected terminal cut: move the projections
+    if (final_state.size() != state_cut.size())
+      throw ERROR_MSG("Size of final_conf: ", final_state.size(),
+                      ", must be equal to size of initial_conf: ", state_cut.size(), ".");
+    for (std::size_t a = 0; a < state_cut.size(); ++a) {
+      if (state_cut[a] < 0) continue;
+      const char c = final_state[a];
+      if (c != '0' && c != '1')
+        throw ERROR_MSG("Final state has non-binary character ", c, " at index ", a,
+                        "despite having no terminal cut there.");
+      session->SetCutValue(state_cut[a], std::size_t(c - '0'));
+    }
+    for (std::string& s : output_states) {
+      std::string next = final_state;
+      for (std::size_t a = 0; a < state_cut.size(); ++a)
+        if (state_cut[a] < 0) next[a] = s[a];
+      s = std::move(next);
+    }
+    return;
+  }
   session->SetFinalState(final_state);
   for (std::string& s : output_states) {
     std::string next = final_state;

@@ -36,6 +36,12 @@ struct DevicePlacement {
   int rank = 0;
   int world = 1;
   int precision = QFX_PREC_AUTO;
+  // Plan for MANY final states on one resident circuit: every qubit without a terminal
+  // cut gets one, projected on its bit of the final state, so that its grid tensor
+  // keeps the output leg and another bitstring is only another set of projection
+  // offsets -- no upload, no flatten (PreparedCircuit::SetFinalState).  Grid tensors
+  // double in size; falls back to rewriting the closing deltas when that does not fit.
+  bool resident_finals = false;
 };
 
 std::vector<std::pair<std::string, std::complex<double>>> EvaluateCircuit(
@@ -50,6 +56,9 @@ struct PreparedCircuit {
   std::unique_ptr<Session> session;
   // positions (in the state strings) of the qubits with a terminal cut
   std::vector<std::size_t> output_positions;
+  // resident_finals: per position of the state strings, the plan cut that projects
+  // that qubit's output leg (-1: an output of the ordering itself)
+  std::vector<int> state_cut;
 
   // Moves the resident circuit to another final state (Session::SetFinalState) and
   // rewrites output_states: the terminal-cut positions keep enumerating their values,

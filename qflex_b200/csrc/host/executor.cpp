@@ -268,6 +268,12 @@ void Session::SetFinalState(const std::string& final_state) {
   Flatten();
 }
 
+void Session::SetCutValue(int cut, std::size_t value) {
+  if (cut < 0 || cut >= (int)plan_.cuts.size() || plan_.cuts[cut].values.size() != 1)
+    throw ERROR_MSG("Cut ", cut, " is not a single-valued projection.");
+  plan_.cuts[cut].values[0] = value;
+}
+
 void Session::Flatten() {
   // replicated on every rank and lane: site tensors are MB-scale.  Launches are
   // asynchronous, so the lanes' flattens overlap on the device.

@@ -138,6 +138,35 @@ void* qflex_b200_prepare_on(const char* circuit_text, const char* ordering_text,
   QFLEX_CAPI_CATCH(nullptr)
 }
 
+void* qflex_b200_prepare_batch(const char* circuit_text, const char* ordering_text,
+                               const char* grid_text, const char* initial_state,
+                               const char* final_state, uint64_t memory_limit_bytes,
+                               int device, int precision, int world, char* err,
+                               uint64_t err_cap) {
+  try {
+    if (memory_limit_bytes) qflex::global::memory_limit = memory_limit_bytes;
+    qflex::DevicePlacement where;
+    where.device = device;
+    where.precision = precision;
+    where.world = world < 1 ? 1 : world;
+    // first with the final state as projections of open output legs (another bitstring
+    // costs nothing but the contraction); if that plan does not fit, the plain one
+    // (another bitstring = rewritten deltas + flatten)
+    for (const bool projected : {true, false}) {
+      qflex::QflexInput input;
+      load_input(&input, circuit_text, ordering_text, grid_text, initial_state, final_state);
+      where.resident_finals = projected;
+      try {
+        return qflex::PrepareCircuit(&input, where).release();
+      } catch (const std::string&) {
+        if (!projected) throw;
+      }
+    }
+    return nullptr;
+  }
+  QFLEX_CAPI_CATCH(nullptr)
+}
+
 void* qflex_b200_prepare(const char* circuit_text, const char* ordering_text,
                          const char* grid_text, const char* initial_state,
                          const char* final_state, uint64_t memory_limit_bytes,

@@ -230,6 +230,9 @@ class Session {
   // contraction schedule are reused.  What a batch of final states needs
   // (src/pybind_main.cpp:49-73,111-113 parses such a list and rejects it).
   void SetFinalState(const std::string& final_state);
+  // A projected cut with a single value moves to another value (resident final states:
+  // the projection of an output leg; see DevicePlacement::resident_finals).
+  void SetCutValue(int cut, std::size_t value);
   void Contract(int rank, int world, std::vector<std::complex<double>>* amplitudes);
 
   const Plan& plan() const { return plan_; }

@@ -15,6 +15,7 @@
 
 #include <complex>
 #include <iostream>
+#include <memory>
 #include <sstream>
 #include <string>
 #include <utility>
@@ -132,7 +133,19 @@ Amplitudes simulate(const py::dict& options) {
     if (final_states.size() == 1) return qflex::EvaluateCircuit(&input, where, nullptr);
     // a batch of output bitstrings: one resident circuit, one delta rewrite +
     // flatten + contraction per state
-    auto prepared = qflex::PrepareCircuit(&input, where);
+    std::unique_ptr<qflex::PreparedCircuit> prepared;
+    {
+      // final states as projections of open output legs when that fits (another
+      // bitstring then costs the contraction alone), else rewritten deltas + flatten
+      qflex::QflexInput projected = input;
+      where.resident_finals = true;
+      try {
+        prepared = qflex::PrepareCircuit(&projected, where);
+      } catch (const std::string&) {
+        where.resident_finals = false;
+        prepared = qflex::PrepareCircuit(&input, where);
+      }
+    }
     std::vector<std::complex<double>> amplitudes;
     for (std::size_t s = 0; s < final_states.size(); ++s) {
       if (s) prepared->SetFinalState(final_states[s]);
