@@ -10,6 +10,7 @@
 
 #include <chrono>
 #include <iostream>
+#include <mutex>
 
 #include "errors.h"
 
@@ -24,6 +25,70 @@ std::size_t find_output_pos(const QflexInput* input, const std::vector<std::size
   for (const auto& q : input->grid.qubits_off)
     if (q.size() == 2 && q[0] * J + q[1] < target) ++skipped;
   return target - skipped;
+}
+
+// ---- plan memory (see PrepareCircuit)
+std::string PlanKey(const QflexInput& input, const std::vector<std::vector<std::size_t>>& final_qubits,
+                    const DevicePlacement& where) {
+  std::string key;
+  key.reserve(64 * 1024);
+  auto add = [&key](const std::string& s) {
+    key += s;
+    key += '\n';
+  };
+  add(utils::concat("grid ", input.grid.I, "x", input.grid.J));
+  for (const auto& q : input.grid.qubits_off) add(utils::concat("off ", q[0], ",", q[1]));
+  add(utils::concat("circuit ", input.circuit.num_active_qubits, " ", input.circuit.gates.size()));
+  for (const auto& g : input.circuit.gates) add(g.raw);
+  for (const auto& line : input.ordering.instructions) add(line);
+  add("initial " + input.initial_state);
+  // final state: only where a terminal cut makes it an output marker; the bits of the
+  // other qubits do not change the plan
+  std::string fs = input.final_state;
+  {
+    std::vector<char> is_output(fs.size(), 0);
+    const std::size_t J = input.grid.J;
+    for (const auto& q : final_qubits) {
+      std::size_t p = q[0] * J + q[1];
+      for (const auto& o : input.grid.qubits_off)
+        if (o.size() == 2 && o[0] * J + o[1] < q[0] * J + q[1]) --p;
+      if (p < is_output.size()) is_output[p] = 1;
+    }
+    for (std::size_t i = 0; i < fs.size(); ++i)
+      if (!is_output[i] && (fs[i] == '0' || fs[i] == '1')) fs[i] = 'b';
+  }
+  add("final " + fs);
+  add(utils::concat("memory ", global::memory_limit, " world ", where.world, " devices ",
+                    where.devices.size(), " finals ", (int)where.resident_finals));
+  for (const char* var : {"QFLEX_OPEN_OUTPUTS", "QFLEX_FUSE_BITS", "QFLEX_FUSE_TARGET_FLOPS",
+                          "QFLEX_CUT_AWARE_FLATTEN", "QFLEX_WORLDLINE_TREE", "QFLEX_FOLD_LAYOUT"}) {
+    const char* e = getenv(var);
+    add(utils::concat(var, "=", e ? e : ""));
+  }
+  return key;
+}
+
+std::mutex g_plan_mu;
+std::list<std::pair<std::string, Plan>> g_plans;  // most recent first
+constexpr std::size_t kPlansKept = 4;
+
+bool RecallPlan(const std::string& key, Plan* plan) {
+  if (const char* e = getenv("QFLEX_PLAN_MEMORY"); e != nullptr && e[0] == '0') return false;
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  for (auto it = g_plans.begin(); it != g_plans.end(); ++it)
+    if (it->first == key) {
+      g_plans.splice(g_plans.begin(), g_plans, it);
+      *plan = g_plans.front().second;
+      return true;
+    }
+  return false;
+}
+
+void RememberPlan(const std::string& key, const Plan& plan) {
+  if (const char* e = getenv("QFLEX_PLAN_MEMORY"); e != nullptr && e[0] == '0') return;
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  g_plans.emplace_front(key, plan);
+  while (g_plans.size() > kPlansKept) g_plans.pop_back();
 }
 
 double seconds_since(const std::chrono::steady_clock::time_point& t0) {
@@ -157,117 +222,145 @@ std::unique_ptr<PreparedCircuit> PrepareCircuit(QflexInput* input,
   // large), the same once more with the cut-aware flatten (BuildPlan, plan.h);
   // QFLEX_CUT_AWARE_FLATTEN=1 forces it, =0 forbids it.
   Plan plan;
-  int max_open = (int)final_qubits.size();
-  if (const char* e = getenv("QFLEX_OPEN_OUTPUTS")) max_open = std::min(max_open, std::max(0, atoi(e)));
-  const auto fits = [&](const Plan& p) {
-    return (double)p.arena_elems * sizeof(s_type) <= (double)global::memory_limit;
-  };
-  PlanCache cache;  // phase 1 of BuildPlan, shared by the searches below
-  auto plan_with = [&](bool cut_aware, Plan* result) {
-    bool planned = false;
-    auto try_open = [&](int n) {
-      try {
-        Plan p = BuildPlan(*input, ordering, final_qubits, n, cut_aware, 0, &cache);
-        if (p.open_outputs == 0 || !fits(p)) return false;
-        *result = std::move(p);
-        return true;
-      } catch (const std::string&) {
-        return false;
-      }
+  // Plans are remembered across calls (the reference's Python interface calls
+  // simulate() once per output bitstring, qflexcirq/interface/qflex_simulator.py:44-66:
+  // same circuit, grid and ordering every time).  The key is everything the plan
+  // depends on EXCEPT the bits of the final state on qubits without a terminal cut --
+  // those only select the closing delta tensors, which are patched on a hit.
+  const std::string plan_key = PlanKey(*input, final_qubits, where);
+  if (!RecallPlan(plan_key, &plan)) {
+    int max_open = (int)final_qubits.size();
+    if (const char* e = getenv("QFLEX_OPEN_OUTPUTS")) max_open = std::min(max_open, std::max(0, atoi(e)));
+    const auto fits = [&](const Plan& p) {
+      return (double)p.arena_elems * sizeof(s_type) <= (double)global::memory_limit;
     };
-    if (max_open > 0) {
-      planned = try_open(max_open);
-      if (!planned) {
-        int lo = 0, hi = max_open;  // lo fits (0 = projected), hi does not
-        while (hi - lo > 1) {
-          const int mid = (lo + hi) / 2;
-          if (try_open(mid)) lo = mid, planned = true;
-          else hi = mid;
+    PlanCache cache;  // phase 1 of BuildPlan, shared by the searches below
+    auto plan_with = [&](bool cut_aware, Plan* result) {
+      bool planned = false;
+      auto try_open = [&](int n) {
+        try {
+          Plan p = BuildPlan(*input, ordering, final_qubits, n, cut_aware, 0, &cache);
+          if (p.open_outputs == 0 || !fits(p)) return false;
+          *result = std::move(p);
+          return true;
+        } catch (const std::string&) {
+          return false;
+        }
+      };
+      if (max_open > 0) {
+        planned = try_open(max_open);
+        if (!planned) {
+          int lo = 0, hi = max_open;  // lo fits (0 = projected), hi does not
+          while (hi - lo > 1) {
+            const int mid = (lo + hi) / 2;
+            if (try_open(mid)) lo = mid, planned = true;
+            else hi = mid;
+          }
         }
       }
-    }
-    if (!planned) *result = BuildPlan(*input, ordering, final_qubits, 0, cut_aware, 0, &cache);
-    if (!fits(*result)) return;
+      if (!planned) *result = BuildPlan(*input, ordering, final_qubits, 0, cut_aware, 0, &cache);
+      if (!fits(*result)) return;
 
-    // Then undo as much of the bond-cut slicing as the memory limit allows (BuildPlan's
-    // fuse_bits: 2^f slices per pass of larger kernels), keeping at least one outer
-    // slice per rank of a multi-GPU run.  QFLEX_FUSE_BITS=<n> caps f, 0 = the ordering
-    // as written.  The arena grows monotonically with f, so bisect.
-    const int n_open = result->open_outputs;
-    int max_fuse = 62;
-    if (const char* e = getenv("QFLEX_FUSE_BITS")) max_fuse = std::max(0, atoi(e));
-    double slices = 1;
-    for (const auto& c : result->cuts)
-      if (!c.terminal) slices *= (double)std::max<std::size_t>(1, c.values.size());
-    const int ranks = std::max(1, where.world) * std::max<int>(1, (int)where.devices.size());
-    if (slices >= ranks) {
-      int cap = 0;
-      while (slices / (double)(uint64_t(2) << cap) >= ranks) ++cap;
-      max_fuse = std::min(max_fuse, cap);
-    }
-    if (max_fuse <= 0) return;
-    auto try_fuse = [&](int f, Plan* out) {
-      try {
-        Plan p = BuildPlan(*input, ordering, final_qubits, n_open, cut_aware, f, &cache);
-        if (p.open_outputs != n_open || !fits(p)) return false;
-        *out = std::move(p);
-        return true;
-      } catch (const std::string&) {
-        return false;
+      // Then undo as much of the bond-cut slicing as the memory limit allows (BuildPlan's
+      // fuse_bits: 2^f slices per pass of larger kernels), keeping at least one outer
+      // slice per rank of a multi-GPU run.  QFLEX_FUSE_BITS=<n> caps f, 0 = the ordering
+      // as written.  The arena grows monotonically with f, so bisect.
+      const int n_open = result->open_outputs;
+      int max_fuse = 62;
+      if (const char* e = getenv("QFLEX_FUSE_BITS")) max_fuse = std::max(0, atoi(e));
+      double slices = 1;
+      for (const auto& c : result->cuts)
+        if (!c.terminal) slices *= (double)std::max<std::size_t>(1, c.values.size());
+      const int ranks = std::max(1, where.world) * std::max<int>(1, (int)where.devices.size());
+      if (slices >= ranks) {
+        int cap = 0;
+        while (slices / (double)(uint64_t(2) << cap) >= ranks) ++cap;
+        max_fuse = std::min(max_fuse, cap);
       }
+      if (max_fuse <= 0) return;
+      auto try_fuse = [&](int f, Plan* out) {
+        try {
+          Plan p = BuildPlan(*input, ordering, final_qubits, n_open, cut_aware, f, &cache);
+          if (p.open_outputs != n_open || !fits(p)) return false;
+          *out = std::move(p);
+          return true;
+        } catch (const std::string&) {
+          return false;
+        }
+      };
+      // Fusing pays while the schedule is a stream of small launches; once the average
+      // contraction is large (>= ~1e11 flop, hundreds of microseconds on the tensor
+      // cores) it only grows the arena and the merges' K.  Every fused bit about doubles
+      // the work per launch: aim for the smallest f that reaches the target
+      // (QFLEX_FUSE_TARGET_FLOPS), back off by bisection when it does not fit.
+      double target = 1e11;
+      if (const char* e = getenv("QFLEX_FUSE_TARGET_FLOPS")) target = std::max(1.0, atof(e));
+      const double mean0 =
+          result->flops_per_pass / std::max<double>(1.0, (double)result->steps.size());
+      int want = 0;
+      while (want < max_fuse && std::ldexp(mean0, want) < target) ++want;
+      if (want <= 0) return;
+      Plan best;
+      int have = 0;
+      if (try_fuse(want, &best)) {
+        have = want;
+      } else {
+        int lo = 0, hi = want;  // lo fits, hi does not
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) / 2;
+          if (try_fuse(mid, &best)) lo = mid, have = mid;
+          else hi = mid;
+        }
+        // `best` holds the last successful try, which is lo (bisection only raises lo)
+      }
+      if (have > 0) *result = std::move(best);
     };
-    // Fusing pays while the schedule is a stream of small launches; once the average
-    // contraction is large (>= ~1e11 flop, hundreds of microseconds on the tensor
-    // cores) it only grows the arena and the merges' K.  Every fused bit about doubles
-    // the work per launch: aim for the smallest f that reaches the target
-    // (QFLEX_FUSE_TARGET_FLOPS), back off by bisection when it does not fit.
-    double target = 1e11;
-    if (const char* e = getenv("QFLEX_FUSE_TARGET_FLOPS")) target = std::max(1.0, atof(e));
-    const double mean0 =
-        result->flops_per_pass / std::max<double>(1.0, (double)result->steps.size());
-    int want = 0;
-    while (want < max_fuse && std::ldexp(mean0, want) < target) ++want;
-    if (want <= 0) return;
-    Plan best;
-    int have = 0;
-    if (try_fuse(want, &best)) {
-      have = want;
+    const char* ca_env = getenv("QFLEX_CUT_AWARE_FLATTEN");
+    const bool ca_forced = ca_env && ca_env[0] == '1', ca_forbidden = ca_env && ca_env[0] == '0';
+    if (ca_forced) {
+      plan_with(true, &plan);
     } else {
-      int lo = 0, hi = want;  // lo fits, hi does not
-      while (hi - lo > 1) {
-        const int mid = (lo + hi) / 2;
-        if (try_fuse(mid, &best)) lo = mid, have = mid;
-        else hi = mid;
-      }
-      // `best` holds the last successful try, which is lo (bisection only raises lo)
-    }
-    if (have > 0) *result = std::move(best);
-  };
-  const char* ca_env = getenv("QFLEX_CUT_AWARE_FLATTEN");
-  const bool ca_forced = ca_env && ca_env[0] == '1', ca_forbidden = ca_env && ca_env[0] == '0';
-  if (ca_forced) {
-    plan_with(true, &plan);
-  } else {
-    std::string first_error;
-    bool ok = false;
-    try {
-      plan_with(false, &plan);
-      ok = fits(plan);
-    } catch (const std::string& err_msg) {
-      first_error = err_msg;
-    }
-    if (!ok && !ca_forbidden) {
+      std::string first_error;
+      bool ok = false;
       try {
-        Plan second;
-        plan_with(true, &second);
-        if (first_error.empty() && !fits(second)) throw std::string("does not fit either");
-        plan = std::move(second);
-        ok = true;
-      } catch (const std::string&) {
-        // report the plain plan's outcome
+        plan_with(false, &plan);
+        ok = fits(plan);
+      } catch (const std::string& err_msg) {
+        first_error = err_msg;
       }
+      if (!ok && !ca_forbidden) {
+        try {
+          Plan second;
+          plan_with(true, &second);
+          if (first_error.empty() && !fits(second)) throw std::string("does not fit either");
+          plan = std::move(second);
+          ok = true;
+        } catch (const std::string&) {
+          // report the plain plan's outcome
+        }
+      }
+      if (!ok && !first_error.empty()) throw first_error;
     }
-    if (!ok && !first_error.empty()) throw first_error;
+    RememberPlan(plan_key, plan);
+  }
+  // closing deltas of THIS final state (a recalled plan carries another one's)
+  if (!where.resident_finals) {
+    const std::string& fs = input->final_state;
+    for (std::size_t a = 0; a < plan.final_delta_upload.size() && a < fs.size(); ++a) {
+      const int u = plan.final_delta_upload[a];
+      if (u < 0 || plan.uploads[u].data.size() != 2) continue;
+      plan.uploads[u].data[0] = s_type(fs[a] == '0' ? 1.f : 0.f, 0.f);
+      plan.uploads[u].data[1] = s_type(fs[a] == '1' ? 1.f : 0.f, 0.f);
+    }
+  } else {
+    // projected output legs: the values of the state cuts
+    std::size_t a = 0;
+    for (std::size_t q = 0; q < prepared->state_cut.size(); ++q, ++a) {
+      const int c = prepared->state_cut[q];
+      if (c >= 0 && c < (int)plan.cuts.size() && plan.cuts[c].values.size() == 1 &&
+          a < input->final_state.size())
+        plan.cuts[c].values[0] = std::size_t(input->final_state[a] - '0');
+    }
   }
   plan.precision = where.precision;
   for (auto& st : plan.steps) st.desc.precision = where.precision;

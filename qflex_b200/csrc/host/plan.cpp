@@ -721,7 +721,7 @@ Plan BuildPlan(const QflexInput& input,
         }
         static const bool fold_layout = [] {
           const char* e = getenv("QFLEX_FOLD_LAYOUT");
-          return e != nullptr && e[0] == '1';
+          return e == nullptr || e[0] != '0';
         }();
         if (identity && out_steps.size() > first_step && chain.size() > 1) {
           // last world-line product can write the grid tensor directly
