@@ -130,6 +130,29 @@ int qfx_contract(qfx_ctx* ctx, const qfx_contract_desc* desc);
 int qfx_contract_chains(qfx_ctx* ctx, const qfx_contract_desc* descs,
                         const int32_t* chain_first, int32_t n_chains);
 
+/* A RESIDENT program of chains whose operand bases depend on the cut values of the
+ * slice being contracted.  qfx_program_create copies the steps to the device once;
+ * qfx_program_run executes all chains in one launch with
+ *   off_a(step s) += sum over terms[term_first[2s] .. term_first[2s+1]) of
+ *                    ((cut_values[t.cut] >> t.from) & (2^t.width - 1)) << t.shift
+ * and likewise off_b with terms[term_first[2s+1] .. term_first[2s+2]).
+ * Replaces, for grid tensors next to cut bonds (flattened inside the slice loop by the
+ * cut-aware flatten), the per-gate multiply() calls of flatten_grid_of_tensors
+ * (src/read_circuit.cpp:560-580) applied to projected gate tensors
+ * (Tensor::project, src/tensor.cpp:280-316): ~2000 launches per slice become one. */
+typedef struct qfx_var_term {
+  int32_t cut, shift, from, width;
+} qfx_var_term;
+typedef struct qfx_program qfx_program;
+int qfx_program_create(qfx_ctx* ctx, const qfx_contract_desc* descs,
+                       const int32_t* chain_first, int32_t n_chains,
+                       const qfx_var_term* terms, const int32_t* term_first,
+                       qfx_program** program_out);
+#define QFX_MAX_CUT_VALUES 96
+int qfx_program_run(qfx_ctx* ctx, qfx_program* program, const uint32_t* cut_values,
+                    int32_t n_values);
+int qfx_program_destroy(qfx_ctx* ctx, qfx_program* program);
+
 /* Final scalar contraction (m_bits = n_bits = 0) accumulated in complex128 into
  * amplitude slot `slot`.  Replaces _multiply_vv + `(*amplitudes_)[output_index]
  * += *output->data()` (src/tensor.cpp:1027-1042,

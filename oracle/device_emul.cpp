@@ -153,6 +153,51 @@ int qfx_contract_chains(qfx_ctx* c, const qfx_contract_desc* d, const int32_t* f
       if (int rc = contract_impl(c, d + s, false, 0)) return rc;
   return QFX_OK;
 }
+struct qfx_program {
+  std::vector<qfx_contract_desc> descs;
+  std::vector<int32_t> chain_first, term_first;
+  std::vector<qfx_var_term> terms;
+};
+int qfx_program_create(qfx_ctx* c, const qfx_contract_desc* d, const int32_t* first, int32_t n,
+                       const qfx_var_term* terms, const int32_t* term_first, qfx_program** out) {
+  if (c == nullptr || d == nullptr || first == nullptr || n < 0 || term_first == nullptr || out == nullptr)
+    return fail("qfx_program_create: bad argument");
+  auto* p = new qfx_program();
+  const int n_steps = n ? first[n] : 0;
+  p->descs.assign(d, d + n_steps);
+  p->chain_first.assign(first, first + n + 1);
+  p->term_first.assign(term_first, term_first + 2 * n_steps + 1);
+  if (p->term_first.back() > 0) p->terms.assign(terms, terms + p->term_first.back());
+  *out = p;
+  return QFX_OK;
+}
+int qfx_program_run(qfx_ctx* c, qfx_program* p, const uint32_t* values, int32_t n_values) {
+  if (c == nullptr || p == nullptr) return fail("qfx_program_run: bad argument");
+  auto offset = [&](int first, int last, uint64_t* off) {
+    for (int t = first; t < last; ++t) {
+      const qfx_var_term& term = p->terms[t];
+      if (term.cut < 0 || term.cut >= n_values) return false;
+      uint64_t x = (uint64_t)values[term.cut] >> term.from;
+      if (term.width < 32) x &= (1ull << term.width) - 1ull;
+      *off += x << term.shift;
+    }
+    return true;
+  };
+  const uint64_t launches = c->stats.launches_total;
+  for (std::size_t s = 0; s < p->descs.size(); ++s) {
+    qfx_contract_desc d = p->descs[s];
+    if (!offset(p->term_first[2 * s], p->term_first[2 * s + 1], &d.off_a) ||
+        !offset(p->term_first[2 * s + 1], p->term_first[2 * s + 2], &d.off_b))
+      return fail("qfx_program_run: cut values missing for a var term");
+    if (int rc = contract_impl(c, &d, false, 0)) return rc;
+  }
+  c->stats.launches_total = launches + 1;  // one launch on the device
+  return QFX_OK;
+}
+int qfx_program_destroy(qfx_ctx*, qfx_program* p) {
+  delete p;
+  return QFX_OK;
+}
 int qfx_dot_accumulate(qfx_ctx* c, const qfx_contract_desc* d, uint64_t slot) {
   return contract_impl(c, d, true, slot);
 }

@@ -68,6 +68,9 @@ def load(path=DEFAULT_DEVICE_LIB):
     c.qfx_dot_accumulate.argtypes = [vp, ctypes.POINTER(ContractDesc), u64]
     c.qfx_contract_chains.argtypes = [vp, ctypes.POINTER(ContractDesc),
                                       ctypes.POINTER(ctypes.c_int32), i32]
+    c.qfx_program_create.argtypes = [vp, vp, vp, i32, vp, vp, ctypes.POINTER(vp)]
+    c.qfx_program_run.argtypes = [vp, vp, vp, i32]
+    c.qfx_program_destroy.argtypes = [vp, vp]
     c.qfx_trim_cache.argtypes = [ctypes.c_int]
     c.qfx_bind_thread.argtypes = [vp]
     c.qfx_scalar_accumulate.argtypes = [vp, u64, u64]

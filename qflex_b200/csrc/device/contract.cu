@@ -1278,8 +1278,27 @@ __device__ __forceinline__ void chain_point(const float2* __restrict__ A,
 // walks the remaining bits in Gray-code order (one XOR per operand per output),
 // four outputs per trip so that a late step's 2^16..2^20 outputs keep several loads
 // in flight per thread -- the block is alone on its SM and latency is all it pays.
+struct ChainVars {
+  const qfx_var_term* terms;   // nullptr: no slice-dependent bases
+  const int32_t* term_first;   // [2 * n_steps + 1]
+  uint32_t values[QFX_MAX_CUT_VALUES];
+};
+
+__device__ __forceinline__ unsigned long long chain_var_offset(const ChainVars& v, int first,
+                                                               int last) {
+  unsigned long long off = 0;
+  for (int t = first; t < last; ++t) {
+    const qfx_var_term term = v.terms[t];
+    unsigned long long x = (unsigned long long)v.values[term.cut] >> term.from;
+    if (term.width < 32) x &= (1ull << term.width) - 1ull;
+    off += x << term.shift;
+  }
+  return off;
+}
+
 __global__ void __launch_bounds__(1024)
-    contract_chains(float2* arena, const qfx_contract_desc* descs, const int32_t* chain_first) {
+    contract_chains(float2* arena, const qfx_contract_desc* descs, const int32_t* chain_first,
+                    const __grid_constant__ ChainVars vars) {
   __shared__ qfx_contract_desc d;
   __shared__ uint32_t xa[32], xb[32], xc[32], ka[64], kb[64];
   const int first = chain_first[blockIdx.x], last = chain_first[blockIdx.x + 1];
@@ -1289,6 +1308,14 @@ __global__ void __launch_bounds__(1024)
     for (int i = tid; i < (int)(sizeof(qfx_contract_desc) / 4); i += blockDim.x)
       reinterpret_cast<uint32_t*>(&d)[i] = reinterpret_cast<const uint32_t*>(descs + s)[i];
     __syncthreads();
+    if (vars.terms != nullptr && tid < 2) {
+      // projected gate tensors: this slice's base of operand a (tid 0) / b (tid 1)
+      const unsigned long long add = chain_var_offset(vars, vars.term_first[2 * s + tid],
+                                                      vars.term_first[2 * s + tid + 1]);
+      if (tid == 0) d.off_a += add;
+      else d.off_b += add;
+    }
+    if (vars.terms != nullptr) __syncthreads();
     const int nb = d.n_bits, tb = d.m_bits + d.n_bits;
     const unsigned K = 1u << d.k_bits;
     if ((int)tid < tb) {
@@ -1382,13 +1409,156 @@ extern "C" int qfx_contract_chains(qfx_ctx* ctx, const qfx_contract_desc* descs,
   QFX_CUDA(cudaMemcpyAsync(ws + desc_pad, chain_first, first_bytes, cudaMemcpyHostToDevice,
                            ctx->stream));
   QFX_CUDA(cudaStreamSynchronize(ctx->stream));  // pageable host buffers may be reused
+  ChainVars no_vars{};
   contract_chains<<<n_chains, 1024, 0, ctx->stream>>>(
       ctx->arena, reinterpret_cast<const qfx_contract_desc*>(ws),
-      reinterpret_cast<const int32_t*>(ws + desc_pad));
+      reinterpret_cast<const int32_t*>(ws + desc_pad), no_vars);
   QFX_CUDA(cudaGetLastError());
   ctx->stats.launches_gemm_ffma++;
   ctx->stats.launches_total++;
   ctx->stats.flops += flops;
   ctx->stats.bytes += bytes;
+  return QFX_OK;
+}
+
+
+// ---------------------------------------------------------------- resident programs
+struct qfx_program {
+  uint8_t* dev = nullptr;  // descs | chain_first | terms | term_first
+  size_t off_first = 0, off_terms = 0, off_term_first = 0;
+  int32_t n_chains = 0, n_steps = 0, n_terms = 0;
+  int32_t max_cut = -1;
+  double flops = 0, bytes = 0;
+};
+
+extern "C" int qfx_program_create(qfx_ctx* ctx, const qfx_contract_desc* descs,
+                                  const int32_t* chain_first, int32_t n_chains,
+                                  const qfx_var_term* terms, const int32_t* term_first,
+                                  qfx_program** program_out) {
+  if (ctx == nullptr || descs == nullptr || chain_first == nullptr || n_chains < 0 ||
+      term_first == nullptr || program_out == nullptr) {
+    qfx_set_error("qfx_program_create: bad argument");
+    return QFX_ERR_ARG;
+  }
+  *program_out = nullptr;
+  const int n_steps = n_chains ? chain_first[n_chains] : 0;
+  const int n_terms = term_first[2 * n_steps];
+  if (n_terms > 0 && terms == nullptr) {
+    qfx_set_error("qfx_program_create: terms missing");
+    return QFX_ERR_ARG;
+  }
+  qfx_program* p = new (std::nothrow) qfx_program();
+  if (p == nullptr) {
+    qfx_set_error("qfx_program_create: host allocation failed");
+    return QFX_ERR_OOM;
+  }
+  p->n_chains = n_chains;
+  p->n_steps = n_steps;
+  p->n_terms = n_terms;
+  for (int c = 0; c < n_chains; ++c)
+    if (chain_first[c] > chain_first[c + 1] || chain_first[c] < 0) {
+      delete p;
+      qfx_set_error("qfx_program_create: chain_first must be non-decreasing");
+      return QFX_ERR_ARG;
+    }
+  for (int s = 0; s < n_steps; ++s) {
+    const qfx_contract_desc& d = descs[s];
+    bool ok = d.m_bits >= 0 && d.n_bits >= 0 && d.k_bits >= 0 && d.k_bits <= 6 &&
+              d.m_bits + d.n_bits <= 26;
+    const uint64_t mask_a = ok ? operand_mask(d.a_m, d.m_bits, d.a_k, d.k_bits) : ~0ull;
+    const uint64_t mask_b = ok ? operand_mask(d.b_k, d.k_bits, d.b_n, d.n_bits) : ~0ull;
+    const uint64_t mask_c = ok ? operand_mask(d.c_m, d.m_bits, d.c_n, d.n_bits) : ~0ull;
+    ok = ok && mask_a != ~0ull && mask_b != ~0ull && mask_c != ~0ull &&
+         d.off_c + mask_c + 1 <= ctx->arena_elems && term_first[2 * s] <= term_first[2 * s + 1] &&
+         term_first[2 * s + 1] <= term_first[2 * s + 2];
+    if (!ok) {
+      delete p;
+      qfx_set_error("qfx_program_create: a step is not a small contraction inside the arena "
+                    "(k <= 6 bits, result <= 2^26 elements, positions distinct and < 32)");
+      return QFX_ERR_ARG;
+    }
+    const double M = (double)(1ull << d.m_bits), N = (double)(1ull << d.n_bits),
+                 K = (double)(1ull << d.k_bits);
+    p->flops += 8.0 * M * N * K;
+    p->bytes += 8.0 * (M * K + K * N + M * N);
+  }
+  for (int t = 0; t < n_terms; ++t) {
+    if (terms[t].cut < 0 || terms[t].cut >= QFX_MAX_CUT_VALUES || terms[t].shift < 0 ||
+        terms[t].shift > 40 || terms[t].from < 0 || terms[t].from > 31 || terms[t].width < 0) {
+      delete p;
+      qfx_set_error("qfx_program_create: bad var term");
+      return QFX_ERR_ARG;
+    }
+    p->max_cut = std::max(p->max_cut, terms[t].cut);
+  }
+  auto pad = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t b_desc = pad((size_t)n_steps * sizeof(qfx_contract_desc));
+  const size_t b_first = pad((size_t)(n_chains + 1) * sizeof(int32_t));
+  const size_t b_terms = pad((size_t)std::max(n_terms, 1) * sizeof(qfx_var_term));
+  const size_t b_tf = pad((size_t)(2 * n_steps + 1) * sizeof(int32_t));
+  p->off_first = b_desc;
+  p->off_terms = b_desc + b_first;
+  p->off_term_first = b_desc + b_first + b_terms;
+  cudaSetDevice(ctx->device);
+  if (cudaMalloc(&p->dev, b_desc + b_first + b_terms + b_tf) != cudaSuccess) {
+    cudaGetLastError();
+    delete p;
+    qfx_set_error("out of device memory allocating a chain program");
+    return QFX_ERR_OOM;
+  }
+  cudaError_t e = cudaMemcpyAsync(p->dev, descs, (size_t)n_steps * sizeof(qfx_contract_desc),
+                                  cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(p->dev + p->off_first, chain_first, (size_t)(n_chains + 1) * sizeof(int32_t),
+                        cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess && n_terms > 0)
+    e = cudaMemcpyAsync(p->dev + p->off_terms, terms, (size_t)n_terms * sizeof(qfx_var_term),
+                        cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(p->dev + p->off_term_first, term_first,
+                        (size_t)(2 * n_steps + 1) * sizeof(int32_t), cudaMemcpyHostToDevice,
+                        ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) {
+    cudaFree(p->dev);
+    delete p;
+    return qfx_fail_cuda(e, "qfx_program_create (upload)");
+  }
+  *program_out = p;
+  return QFX_OK;
+}
+
+extern "C" int qfx_program_run(qfx_ctx* ctx, qfx_program* p, const uint32_t* cut_values,
+                               int32_t n_values) {
+  if (ctx == nullptr || p == nullptr || n_values < 0 || n_values > QFX_MAX_CUT_VALUES ||
+      (n_values > 0 && cut_values == nullptr) || p->max_cut >= n_values) {
+    qfx_set_error("qfx_program_run: bad argument (cut values missing for a var term?)");
+    return QFX_ERR_ARG;
+  }
+  if (p->n_chains == 0) return QFX_OK;
+  qfx_prof_scope prof_scope(ctx, 2, p->n_steps, p->n_chains, 0, p->flops, p->bytes);
+  ChainVars v{};
+  v.terms = reinterpret_cast<const qfx_var_term*>(p->dev + p->off_terms);
+  v.term_first = reinterpret_cast<const int32_t*>(p->dev + p->off_term_first);
+  for (int i = 0; i < n_values; ++i) v.values[i] = cut_values[i];
+  contract_chains<<<p->n_chains, 1024, 0, ctx->stream>>>(
+      ctx->arena, reinterpret_cast<const qfx_contract_desc*>(p->dev),
+      reinterpret_cast<const int32_t*>(p->dev + p->off_first), v);
+  QFX_CUDA(cudaGetLastError());
+  ctx->stats.launches_gemm_ffma++;
+  ctx->stats.launches_total++;
+  ctx->stats.flops += p->flops;
+  ctx->stats.bytes += p->bytes;
+  return QFX_OK;
+}
+
+extern "C" int qfx_program_destroy(qfx_ctx* ctx, qfx_program* p) {
+  if (p == nullptr) return QFX_OK;
+  if (ctx != nullptr) {
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+  }
+  if (p->dev) cudaFree(p->dev);
+  delete p;
   return QFX_OK;
 }

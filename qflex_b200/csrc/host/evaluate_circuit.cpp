@@ -61,7 +61,8 @@ std::string PlanKey(const QflexInput& input, const std::vector<std::vector<std::
   add(utils::concat("memory ", global::memory_limit, " world ", where.world, " devices ",
                     where.devices.size(), " finals ", (int)where.resident_finals));
   for (const char* var : {"QFLEX_OPEN_OUTPUTS", "QFLEX_FUSE_BITS", "QFLEX_FUSE_TARGET_FLOPS",
-                          "QFLEX_CUT_AWARE_FLATTEN", "QFLEX_WORLDLINE_TREE", "QFLEX_FOLD_LAYOUT"}) {
+                          "QFLEX_CUT_AWARE_FLATTEN", "QFLEX_WORLDLINE_TREE", "QFLEX_FOLD_LAYOUT",
+                          "QFLEX_LINE_PROGRAMS"}) {
     const char* e = getenv(var);
     add(utils::concat(var, "=", e ? e : ""));
   }

@@ -31,8 +31,9 @@ double now_s() {
 
 class Runner {
  public:
-  Runner(const Plan& plan, qfx_ctx* ctx, int rank, int world)
-      : plan_(plan), ctx_(ctx), rank_(rank), world_(world),
+  Runner(const Plan& plan, qfx_ctx* ctx, int rank, int world,
+         const std::vector<qfx_program*>* programs = nullptr)
+      : plan_(plan), ctx_(ctx), rank_(rank), world_(world), programs_(programs),
         values_(plan.cuts.size(), 0) {
     // Slices are dealt to ranks at the shallowest cut levels whose combined
     // fan-out reaches the number of ranks.
@@ -96,6 +97,15 @@ class Runner {
       case PlanStep::PERMUTE:
         check(qfx_permute(ctx_, st.src, st.dst, st.n_bits, st.dst_pos), "qfx_permute");
         break;
+      case PlanStep::PROGRAM: {
+        if (programs_ == nullptr || st.program < 0 || st.program >= (int)programs_->size())
+          throw ERROR_MSG("Chain program ", st.program, " is not resident on this lane.");
+        uint32_t values[QFX_MAX_CUT_VALUES];
+        const int n = (int)std::min<std::size_t>(values_.size(), QFX_MAX_CUT_VALUES);
+        for (int c = 0; c < n; ++c) values[c] = (uint32_t)values_[c];
+        check(qfx_program_run(ctx_, (*programs_)[st.program], values, n), "qfx_program_run");
+        break;
+      }
     }
   }
 
@@ -122,6 +132,7 @@ class Runner {
   const Plan& plan_;
   qfx_ctx* ctx_;
   int rank_, world_;
+  const std::vector<qfx_program*>* programs_;
   int share_levels_ = 0;
   std::vector<std::size_t> values_;
   uint64_t leaves_ = 0;
@@ -200,22 +211,39 @@ Session::Session(Plan plan, std::vector<int> devices)
       }
       lanes_.insert(lanes_.end(), round.begin(), round.end());
     }
+    programs_.assign(lanes_.size(), {});
+    for (std::size_t l = 0; l < lanes_.size(); ++l) {
+      check(qfx_bind_thread(lanes_[l]), "qfx_bind_thread");
+      for (const ChainProgram& p : plan_.programs) {
+        qfx_program* h = nullptr;
+        check(qfx_program_create(lanes_[l], p.descs.data(), p.chain_first.data(),
+                                 (int32_t)p.chain_first.size() - 1, p.terms.data(),
+                                 p.term_first.data(), &h),
+              "qfx_program_create");
+        programs_[l].push_back(h);
+      }
+    }
     Upload();
     const double t1 = now_s();
     stats_.seconds_upload = t1 - t0;
     Flatten();
     stats_.seconds_flatten = now_s() - t1;
   } catch (...) {
-    for (qfx_ctx* c : lanes_) qfx_destroy(c);
-    lanes_.clear();
-    ctx_ = nullptr;
+    ReleaseDevice();
     throw;
   }
 }
 
-Session::~Session() {
+void Session::ReleaseDevice() {
+  for (std::size_t l = 0; l < programs_.size() && l < lanes_.size(); ++l)
+    for (qfx_program* p : programs_[l]) qfx_program_destroy(lanes_[l], p);
+  programs_.clear();
   for (qfx_ctx* c : lanes_) qfx_destroy(c);
+  lanes_.clear();
+  ctx_ = nullptr;
 }
+
+Session::~Session() { ReleaseDevice(); }
 
 void Session::Upload() {
   // The gate tensors sit next to each other at the start of the arena (plan.cpp):
@@ -321,7 +349,7 @@ void Session::ContractLane(int lane, int rank, int world, std::vector<double>* a
   check(qfx_stats_reset(ctx), "qfx_stats_reset");
   if (profile_) check(qfx_profile_begin(ctx), "qfx_profile_begin");
   check(qfx_timer_start(ctx), "qfx_timer_start");
-  Runner runner(plan_, ctx, rank, world);
+  Runner runner(plan_, ctx, rank, world, &programs_[lane]);
   runner.run(plan_.steps);
   float ms = 0.f;
   check(qfx_timer_stop_ms(ctx, &ms), "qfx_timer_stop_ms");

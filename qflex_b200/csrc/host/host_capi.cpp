@@ -80,6 +80,7 @@ const char* kind_name(qflex::PlanStep::Kind k) {
     case qflex::PlanStep::SCALAR_ACCUMULATE: return "scalar";
     case qflex::PlanStep::TENSOR_ACCUMULATE: return "amps";
     case qflex::PlanStep::PERMUTE: return "permute";
+    case qflex::PlanStep::PROGRAM: return "program";
   }
   return "?";
 }
@@ -238,9 +239,9 @@ long qflex_b200_describe(void* prepared, char* out, uint64_t cap) {
   auto dump = [&](const char* phase, const std::vector<qflex::PlanStep>& steps) {
     for (const auto& st : steps) {
       ss << phase << ' ' << st.level << ' ' << kind_name(st.kind) << ' '
-         << (st.kind == qflex::PlanStep::PERMUTE ? st.n_bits : st.desc.m_bits) << ' '
+         << (st.kind == qflex::PlanStep::PERMUTE || st.kind == qflex::PlanStep::PROGRAM ? st.n_bits : st.desc.m_bits) << ' '
          << st.desc.n_bits << ' ' << st.desc.k_bits << ' ' << st.label;
-      if (st.kind != qflex::PlanStep::PERMUTE) {
+      if (st.kind != qflex::PlanStep::PERMUTE && st.kind != qflex::PlanStep::PROGRAM) {
         // operand bit tables (debugging aid for kernel work)
         auto tab = [&](const char* name, const int8_t* t, int n) {
           ss << ' ' << name << '=';

@@ -519,9 +519,26 @@ Plan BuildPlan(const QflexInput& input,
     std::vector<std::vector<SymTensor>> line_result(I, std::vector<SymTensor>(J));
     // tree-ordered world lines (dynamic sites): per step, whether operand a / b is an
     // intermediate (offset relative to the dyn region) or a gate tensor (absolute)
-    std::vector<std::vector<std::vector<std::pair<bool, bool>>>> line_rel(
-        I, std::vector<std::vector<std::pair<bool, bool>>>(J));
+    // region of operand a / operand b / the result: 0 = a gate tensor (absolute
+    // offset), 1 = the dyn region shared by all dynamic sites (large results, sites run
+    // one after the other), 2 = the site's own small region (results <= kSmallLine
+    // elements whose whole subtree is small: those steps of ALL dynamic sites run as
+    // one resident program, qfx_program_run, one block per site)
+    struct LineRel {
+      uint8_t a, b, c;
+    };
+    constexpr uint64_t kSmallLine = uint64_t(1) << 13;
+    std::vector<std::vector<std::vector<LineRel>>> line_rel(
+        I, std::vector<std::vector<LineRel>>(J));
+    std::vector<std::vector<uint64_t>> line_small_need(I, std::vector<uint64_t>(J, 0));
     uint64_t max_dyn_tree = 0;
+    bool line_programs = true;
+    if (const char* e = getenv("QFLEX_LINE_PROGRAMS")) line_programs = e[0] != '0';
+    {
+      std::size_t n_cut_ops = 0;
+      for (const auto& op : ordering) n_cut_ops += op.op_type == ContractionOperation::CUT;
+      if (n_cut_ops > QFX_MAX_CUT_VALUES) line_programs = false;  // values travel as kernel arguments
+    }
     const bool tree_lines = [] {
       const char* e = getenv("QFLEX_WORLDLINE_TREE");
       return e == nullptr || e[0] != '0';
@@ -549,13 +566,14 @@ Plan BuildPlan(const QflexInput& input,
               if (net[i][j].virt_to_bond.count(ix.name)) vb += ix.bits;
             bits_before[k + 1] = bits_before[k] + vb;
           }
-          uint64_t bump = 0;
+          uint64_t bump = 0, bump_small = 0;
           auto& steps_out = line_steps[i][j];
           auto& rel_out = line_rel[i][j];
-          std::function<SymTensor(std::size_t, std::size_t, bool*)> build =
-              [&](std::size_t lo, std::size_t hi, bool* is_rel) -> SymTensor {
+          const std::size_t n_gates = chain.size();
+          std::function<SymTensor(std::size_t, std::size_t, int*)> build =
+              [&](std::size_t lo, std::size_t hi, int* region) -> SymTensor {
             if (hi - lo == 1) {
-              *is_rel = false;
+              *region = 0;
               return chain[lo].sym;
             }
             std::size_t mid = lo + 1;
@@ -565,19 +583,27 @@ Plan BuildPlan(const QflexInput& input,
               const int d = std::abs(l - r) * 64 + (int)std::min<std::size_t>(63, m > (lo + hi) / 2 ? m - (lo + hi) / 2 : (lo + hi) / 2 - m);
               if (d < best) best = d, mid = m;
             }
-            bool lrel = false, rrel = false;
-            SymTensor L = build(lo, mid, &lrel);
-            SymTensor R = build(mid, hi, &rrel);
+            int lreg = 0, rreg = 0;
+            SymTensor L = build(lo, mid, &lreg);
+            SymTensor R = build(mid, hi, &rreg);
             steps_out.emplace_back();
-            SymTensor C = make_contract(L, R, bump, &steps_out.back());
-            rel_out.push_back({lrel, rrel});
-            bump = align_up(bump + C.size());
-            *is_rel = true;
+            // small = small result, small subtrees, a short contraction, not the root
+            // (the root may be given the grid tensor's layout below)
+            PlanStep probe;
+            const SymTensor sized = make_contract(L, R, 0, &probe);
+            const bool small = line_programs && sized.size() <= kSmallLine && lreg != 1 &&
+                               rreg != 1 && probe.desc.k_bits <= 6 && !(lo == 0 && hi == n_gates);
+            uint64_t& cursor_c = small ? bump_small : bump;
+            SymTensor C = make_contract(L, R, cursor_c, &steps_out.back());
+            rel_out.push_back({(uint8_t)lreg, (uint8_t)rreg, (uint8_t)(small ? 2 : 1)});
+            cursor_c = align_up(cursor_c + C.size());
+            *region = small ? 2 : 1;
             return C;
           };
-          bool top_rel = false;
-          a = build(0, chain.size(), &top_rel);
+          int top_region = 0;
+          a = build(0, chain.size(), &top_region);
           max_dyn_tree = std::max(max_dyn_tree, bump);
+          line_small_need[i][j] = bump_small;
         } else {
           for (std::size_t k = 1; k < net[i][j].chain.size(); ++k) {
             line_steps[i][j].emplace_back();
@@ -626,6 +652,18 @@ Plan BuildPlan(const QflexInput& input,
     const uint64_t dyn_ping = cursor, dyn_pong = cursor + align_up(max_dyn_chain);
     if (max_dyn_chain > 0) cursor = dyn_pong + align_up(max_dyn_chain);
     cursor = std::max(cursor, dyn_ping + align_up(max_dyn_tree));  // (the two share the region)
+    std::vector<std::vector<uint64_t>> line_small_base(I, std::vector<uint64_t>(J, 0));
+    for (std::size_t i = 0; i < I; ++i)
+      for (std::size_t j = 0; j < J; ++j)
+        if (line_small_need[i][j] > 0) {
+          line_small_base[i][j] = cursor;
+          cursor = align_up(cursor + line_small_need[i][j]);
+        }
+    // the small world-line steps of all dynamic sites: one resident program
+    ChainProgram line_program;
+    line_program.chain_first.push_back(0);
+    line_program.term_first.push_back(0);
+    double program_flops = 0, program_bytes = 0;
     work_base = cursor;
     // Ping-pong buffers of the world-line products.  One pair PER SITE when that is
     // affordable (<= 2^26 elements = 512 MB in all): the chains are then independent
@@ -658,18 +696,36 @@ Plan BuildPlan(const QflexInput& input,
         uint64_t prev = chain[0].sym.off;
         const bool as_tree = !line_rel[i][j].empty();
         if (as_tree) {
+          const uint64_t base_of[3] = {0, dyn_ping, line_small_base[i][j]};
+          bool in_program = false;
           for (std::size_t k = 0; k < line_steps[i][j].size(); ++k) {
             PlanStep& st = line_steps[i][j][k];
+            const LineRel rel = line_rel[i][j][k];
             st.level = 0;
             st.chain = chain_id;
             st.label = utils::concat("flatten (", i, ",", j, ") tree step ", k + 1);
-            if (line_rel[i][j][k].first) st.desc.off_a += dyn_ping;
-            if (line_rel[i][j][k].second) st.desc.off_b += dyn_ping;
-            st.desc.off_c += dyn_ping;
+            st.desc.off_a += base_of[rel.a];
+            st.desc.off_b += base_of[rel.b];
+            st.desc.off_c += base_of[rel.c];
             st.desc.precision = QFX_PREC_FFMA;
+            if (rel.c == 2) {
+              // into the program: descriptor + the slice-dependent base terms
+              line_program.descs.push_back(st.desc);
+              for (const std::vector<VarTerm>* var : {&st.var_a, &st.var_b}) {
+                for (const VarTerm& v : *var)
+                  line_program.terms.push_back(
+                      qfx_var_term{v.cut, v.shift, v.from, std::min(v.width, 32)});
+                line_program.term_first.push_back((int32_t)line_program.terms.size());
+              }
+              program_flops += st.flops;
+              program_bytes += st.bytes;
+              in_program = true;
+              continue;
+            }
             prev = st.desc.off_c;
             out_steps.push_back(std::move(st));
           }
+          if (in_program) line_program.chain_first.push_back((int32_t)line_program.descs.size());
         }
         for (std::size_t k = 1; k < chain.size() && !as_tree; ++k) {
           PlanStep& st = line_steps[i][j][k - 1];
@@ -740,6 +796,18 @@ Plan BuildPlan(const QflexInput& input,
         }
       }
 
+    if (!line_program.descs.empty()) {
+      PlanStep run;
+      run.kind = PlanStep::PROGRAM;
+      run.program = (int)plan.programs.size();
+      run.n_bits = (int)line_program.descs.size();
+      run.flops = program_flops;
+      run.bytes = program_bytes;
+      run.label = utils::concat("world-line program: ", line_program.descs.size(), " steps of ",
+                                line_program.chain_first.size() - 1, " sites");
+      plan.programs.push_back(std::move(line_program));
+      dyn_steps.insert(dyn_steps.begin(), std::move(run));
+    }
     if (cache != nullptr) {
       cache->valid = true;
       cache->cut_aware = cut_aware_flatten;

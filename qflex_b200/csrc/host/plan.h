@@ -83,7 +83,7 @@ struct SymTensor {
 };
 
 struct PlanStep {
-  enum Kind { CONTRACT, DOT_ACCUMULATE, SCALAR_ACCUMULATE, TENSOR_ACCUMULATE, PERMUTE };
+  enum Kind { CONTRACT, DOT_ACCUMULATE, SCALAR_ACCUMULATE, TENSOR_ACCUMULATE, PERMUTE, PROGRAM };
   Kind kind = CONTRACT;
   int level = 0;  // number of cuts that precede this step in the ordering
   int chain = -1; // flatten: world-line (grid site) this step belongs to
@@ -98,6 +98,8 @@ struct PlanStep {
   uint64_t scalar_off = 0;
   std::vector<VarTerm> var_scalar;
   uint32_t slot_stride[QFX_MAX_BITS] = {0};
+  // PROGRAM: index into Plan::programs (n_bits = its number of steps)
+  int program = -1;
   // bookkeeping
   double flops = 0, bytes = 0;
   std::string label;
@@ -116,6 +118,16 @@ struct PlanCut {
   int fused_bits = 0;
 };
 
+// Chains of small contractions kept resident on the device (qfx_program_create) and run
+// in one launch per slice with the slice's cut values (qfx_program_run): the small
+// world-line steps of the grid tensors that are flattened inside the slice loop.
+struct ChainProgram {
+  std::vector<qfx_contract_desc> descs;
+  std::vector<int32_t> chain_first;   // [n_chains + 1]
+  std::vector<qfx_var_term> terms;
+  std::vector<int32_t> term_first;    // [2 * n_steps + 1]: a-terms, b-terms per step
+};
+
 struct PlanUpload {
   uint64_t off = 0;
   std::vector<s_type> data;
@@ -126,6 +138,7 @@ struct Plan {
   std::vector<PlanStep> flatten_steps;   // network -> one tensor per site
   std::vector<PlanStep> steps;           // schedule, ordered by level
   std::vector<PlanCut> cuts;
+  std::vector<ChainProgram> programs;
   uint64_t arena_elems = 0;
   uint64_t n_amplitudes = 1;
   // final layout of every site tensor (for tests / parity with
@@ -248,6 +261,7 @@ class Session {
  private:
   // Upload + flatten into one lane's arena; one lane's share of Contract().
   void PrepareLane(qfx_ctx* ctx);
+  void ReleaseDevice();
   void ContractLane(int lane, int rank, int world, std::vector<double>* amps,
                     ExecStats* stats, std::vector<qfx_profile_row>* rows);
 
@@ -261,6 +275,7 @@ class Session {
   // each driven by its own host thread, and kernels of different slices overlap on
   // the GPU.  One lane when the arena is large (the kernels fill the GPU).
   std::vector<qfx_ctx*> lanes_;  // [lane * n_devices + device index]
+  std::vector<std::vector<qfx_program*>> programs_;  // [lane][program of the plan]
   std::vector<int> devices_;
   ExecStats stats_;
   bool profile_ = false;

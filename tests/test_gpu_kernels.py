@@ -372,3 +372,76 @@ def test_headline_shape_full_size_rows_against_oracle(ctx):
         want = A[r].astype(np.complex128) @ B
         worst = max(worst, support.rel_err(got, want))
     assert worst < 2e-5, worst
+
+
+def test_resident_program_of_chains_with_slice_dependent_bases(ctx):
+    """qfx_program_create / qfx_program_run: chains of small contractions kept on the
+    device, operand bases moved per run by bit fields of the cut values (projected gate
+    tensors of the cut-aware flatten) -- against the same steps issued one by one
+    through qfx_contract with the bases resolved on the host, and the oracle."""
+    import ctypes
+    from qflex_b200 import _device
+    lib = _device.load()
+    rng = np.random.default_rng(77)
+    n_chains, steps_per_chain = 5, 4
+    # arena: a pool of 8 "gate" tensors of 4x2x2 (16 elements: leading index = projected
+    # leg with 4 values), then per chain two ping-pong buffers of 64 elements
+    gates = _rand(8 * 16, rng)
+    ctx.reserve(8 * 16 + n_chains * 2 * 64 + 64)
+    ctx.upload(0, gates)
+    seeds = _rand(n_chains * 4, rng)
+    descs, chain_first, terms, term_first = [], [0], [], [0]
+    plain = []  # (chain, desc fields, var a, var b) for the one-by-one run
+    for c in range(n_chains):
+        ping = 8 * 16 + c * 128
+        pong = ping + 64
+        ctx.upload(ping, np.concatenate([seeds[4 * c: 4 * c + 4], np.zeros(60, np.complex64)]))
+        src, dst = ping, pong
+        for s_ in range(steps_per_chain):
+            g = int(rng.integers(0, 8))
+            # running tensor [m(1 bit) | k(1 bit)] x gate slice [k | n]: C = [m | n]
+            d = _device.make_desc(src, 16 * g, dst, [1], [1], [0], [0], [0], [1])
+            cut = int(rng.integers(0, 3))
+            frm = int(rng.integers(0, 2))
+            va = []
+            vb = [(cut, 2, frm, 2)]  # gate base += ((value >> frm) & 3) << 2
+            descs.append(d)
+            for var in (va, vb):
+                terms.extend(var)
+                term_first.append(len(terms))
+            plain.append((d, va, vb))
+            src, dst = dst, src
+        chain_first.append(len(descs))
+    DescArr = _device.ContractDesc * len(descs)
+
+    class VarTerm(ctypes.Structure):
+        _fields_ = [("cut", ctypes.c_int32), ("shift", ctypes.c_int32), ("from_", ctypes.c_int32),
+                    ("width", ctypes.c_int32)]
+    tarr = (VarTerm * max(1, len(terms)))(*[VarTerm(*t) for t in terms])
+    prog = ctypes.c_void_p()
+    rc = lib.qfx_program_create(ctx.h, DescArr(*descs), (ctypes.c_int32 * len(chain_first))(*chain_first),
+                                n_chains, tarr, (ctypes.c_int32 * len(term_first))(*term_first),
+                                ctypes.byref(prog))
+    assert rc == 0, lib.qfx_last_error()
+    for values in ([0, 0, 0], [3, 1, 2], [5, 7, 6]):
+        # reference: one by one with host-resolved bases
+        for c in range(n_chains):
+            ctx.upload(8 * 16 + c * 128, np.concatenate([seeds[4 * c: 4 * c + 4], np.zeros(124, np.complex64)]))
+        for d, va, vb in plain:
+            d2 = _device.ContractDesc.from_buffer_copy(d)
+            for (cut, shift, frm, width) in vb:
+                d2.off_b += ((values[cut] >> frm) & ((1 << width) - 1)) << shift
+            ctx.contract(d2)
+        want = ctx.download(8 * 16, n_chains * 128)
+        for c in range(n_chains):
+            ctx.upload(8 * 16 + c * 128, np.concatenate([seeds[4 * c: 4 * c + 4], np.zeros(124, np.complex64)]))
+        before = ctx.stats()["launches_total"]
+        rc = lib.qfx_program_run(ctx.h, prog, (ctypes.c_uint32 * 3)(*values), 3)
+        assert rc == 0, lib.qfx_last_error()
+        assert ctx.stats()["launches_total"] - before == 1
+        got = ctx.download(8 * 16, n_chains * 128)
+        assert np.array_equal(got, want), values
+        assert np.linalg.norm(got) > 0
+    # a var term that names a cut the caller did not pass is refused
+    assert lib.qfx_program_run(ctx.h, prog, (ctypes.c_uint32 * 1)(0), 1) != 0
+    assert lib.qfx_program_destroy(ctx.h, prog) == 0

@@ -255,6 +255,8 @@ def test_cut_aware_flatten_is_bit_identical(emul, monkeypatch, name):
     case = support.CASES[name]
     texts = support.case_texts(case)
     args = (case.get("initial", ""), case.get("final", ""))
+    has_bond_cut = any(l.split("#")[0].strip().startswith("cut") and len(l.split(")")[1].split()) == 2
+                       for l in texts[1].splitlines() if l.split("#")[0].strip())
     monkeypatch.setenv("QFLEX_FUSE_BITS", "0")  # slice by slice, as the ordering is written
     r0, s0 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
     monkeypatch.setenv("QFLEX_CUT_AWARE_FLATTEN", "1")
@@ -264,13 +266,22 @@ def test_cut_aware_flatten_is_bit_identical(emul, monkeypatch, name):
     # default: the in-loop world lines are contracted as balanced trees (same factors,
     # another association order: equal to rounding), optionally writing the grid tensor
     # in its final layout from the root
-    for fold in ("0", "1"):
+    seen = {}
+    for fold, programs in (("0", "0"), ("1", "0"), ("0", "1"), ("1", "1")):
         monkeypatch.setenv("QFLEX_WORLDLINE_TREE", "1")
         monkeypatch.setenv("QFLEX_FOLD_LAYOUT", fold)
+        # the small tree steps of all in-loop sites as ONE resident program per slice
+        # (qfx_program_run): the same arithmetic in the same order, fewer launches
+        monkeypatch.setenv("QFLEX_LINE_PROGRAMS", programs)
         r2, s2 = emul.evaluate(*texts, *args, memory_limit=8 << 30)
         assert [s for s, _ in r2] == [s for s, _ in r0]
         assert support.rel_err([a for _, a in r2], [a for _, a in r0]) < 1e-5
         assert s2["bytes"] <= s1["bytes"]
+        seen[(fold, programs)] = (r2, s2)
+    for fold in ("0", "1"):
+        assert seen[(fold, "1")][0] == seen[(fold, "0")][0]
+        if has_bond_cut:
+            assert seen[(fold, "1")][1]["launches"] < seen[(fold, "0")][1]["launches"]
     has_bond_cut = any(l.split("#")[0].strip().startswith("cut") and len(l.split(")")[1].split()) == 2
                        for l in texts[1].splitlines() if l.split("#")[0].strip())
     if has_bond_cut:
