@@ -457,6 +457,18 @@ def main():
     barrier()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
     e2e_value = st["flops_job"] * e2e_steps / e2e_wall / 1e12
+    # the same call with the plan memory off (every call parses AND plans from scratch;
+    # above, calls after the first recall the plan of the identical previous call)
+    os.environ["QFLEX_PLAN_MEMORY"] = "0"
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(2):
+        res2, _ = lib.evaluate(c, o, g, memory_limit=w["memory"], device=local_rank, rank=rank,
+                               world=world, precision=args.precision)
+        reducer.allreduce(np.array([a for _, a in res2]))
+    barrier()
+    e2e_cold_ms = 1e3 * max_over_ranks(time.perf_counter() - t0) / 2
+    del os.environ["QFLEX_PLAN_MEMORY"]
     h2d = gate_upload_bytes(c) + len(c) + len(o) + len(g)
     parity = float(np.linalg.norm(full - amps) / max(np.linalg.norm(amps), 1e-300))
 
@@ -565,6 +577,9 @@ def main():
         "e2e": dict({"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d,
                      "d2h_bytes_per_step": 16 * n_amps, "steps": e2e_steps,
                      "ms_per_step": 1e3 * e2e_wall / e2e_steps,
+                     "plan_memory": "on: calls after the first recall the plan of the identical "
+                                    "previous call (parse, upload, flatten, contract still run)",
+                     "ms_per_step_planning_every_call": e2e_cold_ms,
                      "parity_vs_resident_run": parity}, **parity_ref),
         "gpu_launches": total_launches,
         "clocks": clocks, "roofline": roof, "step_roofline_frac": step_frac,

@@ -11,8 +11,8 @@ The numeric path is hand-written sm_100a CUDA behind the C ABI in
 include/qflex_b200.h; there is no CPU fallback.
 """
 from ._host import (HostLibrary, Prepared, QflexError, default_library,  # noqa: F401
-                    simulate, restrict_cuts, STAT_NAMES)
+                    simulate, restrict_cuts, trim_device_cache, STAT_NAMES)
 from . import _device as device  # noqa: F401
 
 __all__ = ["simulate", "HostLibrary", "Prepared", "QflexError", "default_library",
-           "device", "STAT_NAMES", "restrict_cuts"]
+           "device", "STAT_NAMES", "restrict_cuts", "trim_device_cache"]

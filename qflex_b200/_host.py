@@ -343,6 +343,14 @@ def simulate(options, lib=None):
         return []
 
 
+def trim_device_cache(device=0):
+    """Returns the device buffers parked by closed circuits (one arena and one workspace
+    per GPU are kept for the next evaluation: repeated EvaluateCircuit calls then skip a
+    multi-GB cudaMalloc) to the driver.  Call it when other code needs the memory."""
+    from . import _device
+    return _device.load().qfx_trim_cache(int(device))
+
+
 _default = None
 
 

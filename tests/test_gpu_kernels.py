@@ -440,7 +440,8 @@ def test_resident_program_of_chains_with_slice_dependent_bases(ctx):
         assert rc == 0, lib.qfx_last_error()
         assert ctx.stats()["launches_total"] - before == 1
         got = ctx.download(8 * 16, n_chains * 128)
-        assert np.array_equal(got, want), values
+        # (another kernel sums the two products in another order: equal to rounding)
+        assert support.rel_err(got, want) < 1e-6, values
         assert np.linalg.norm(got) > 0
     # a var term that names a cut the caller did not pass is refused
     assert lib.qfx_program_run(ctx.h, prog, (ctypes.c_uint32 * 1)(0), 1) != 0
