@@ -598,6 +598,76 @@ void launch_stream_small(const StreamArgs& g, unsigned blocks, cudaStream_t stre
   }
 }
 
+// ---------------------------------------------------------------- outer_small
+// C[m, n] = sum_k A[m, k] * B[k, n] with K <= 4 and BOTH free sides long, both operands
+// small next to the result (the root of a tree-ordered world line: 2^12 x 2^12 x 2,
+// two 64-KB halves, a 128-MB result written in the grid tensor's final layout).  Pure
+// write streaming, so the work is enumerated in C-ADDRESS order: thread t owns the two
+// elements 2t, 2t+1 (one 16-byte store); a run of C address bits that is a run of m
+// bits in A (or of n bits in B) turns into one shift-mask-or; A and B come from L1/L2
+// (neighbouring threads read neighbouring or identical addresses).  The tiled GEMM
+// reached 1.9 TB/s on these (scattered C tiles, K = 2 per tile pass).
+struct OuterSeg {
+  int start, len, a_shift, b_shift;  // C address bits [start, start+len): bits of A (b_shift < 0) or of B
+};
+struct OuterArgs {
+  const float2* A;
+  const float2* B;
+  float2* C;
+  int c_bits, k_bits, n_seg;
+  int low_is_a;             // C address bit 0 is an m bit (else an n bit)
+  unsigned low_delta;       // its offset in A (or B)
+  OuterSeg seg[16];         // C address bits >= 1
+  int8_t a_k[2], b_k[2];
+};
+
+template <int KB>
+__global__ void __launch_bounds__(256) outer_small(const __grid_constant__ OuterArgs g) {
+  constexpr int K = 1 << KB;
+  __shared__ unsigned ka[K], kb[K];
+  if ((int)threadIdx.x < K) {
+    unsigned oa = 0, ob = 0;
+    for (int q = 0; q < KB; ++q) {
+      oa |= ((threadIdx.x >> q) & 1u) << g.a_k[q];
+      ob |= ((threadIdx.x >> q) & 1u) << g.b_k[q];
+    }
+    ka[threadIdx.x] = oa;
+    kb[threadIdx.x] = ob;
+  }
+  __syncthreads();
+  const unsigned long long pairs = 1ull << (g.c_bits - 1);
+  const float2* __restrict__ A = g.A;
+  const float2* __restrict__ B = g.B;
+  for (unsigned long long t = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; t < pairs;
+       t += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long c = t << 1;
+    unsigned ao = 0, bo = 0;
+    for (int s = 0; s < g.n_seg; ++s) {
+      const unsigned f = (unsigned)(c >> g.seg[s].start) & ((1u << g.seg[s].len) - 1u);
+      if (g.seg[s].b_shift < 0) ao |= f << g.seg[s].a_shift;
+      else bo |= f << g.seg[s].b_shift;
+    }
+    const unsigned ao1 = g.low_is_a ? ao | g.low_delta : ao;
+    const unsigned bo1 = g.low_is_a ? bo : bo | g.low_delta;
+    float x0 = 0.f, y0 = 0.f, x1 = 0.f, y1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const float2 a0 = __ldg(A + (ao | ka[k])), b0 = __ldg(B + (bo | kb[k]));
+      const float2 a1 = g.low_is_a ? __ldg(A + (ao1 | ka[k])) : a0;
+      const float2 b1 = g.low_is_a ? b0 : __ldg(B + (bo1 | kb[k]));
+      x0 = fmaf(a0.x, b0.x, x0);
+      x0 = fmaf(-a0.y, b0.y, x0);
+      y0 = fmaf(a0.x, b0.y, y0);
+      y0 = fmaf(a0.y, b0.x, y0);
+      x1 = fmaf(a1.x, b1.x, x1);
+      x1 = fmaf(-a1.y, b1.y, x1);
+      y1 = fmaf(a1.x, b1.y, y1);
+      y1 = fmaf(a1.y, b1.x, y1);
+    }
+    *reinterpret_cast<float4*>(g.C + c) = make_float4(x0, y0, x1, y1);
+  }
+}
+
 // ---------------------------------------------------------------- gemv_rows
 // out[m] = sum_k A[m,k] * B[k] with 2..64 outputs and a long K, A dense: the tail of a
 // schedule whose output indices stayed open (the last merge yields all 2^k amplitudes).
@@ -926,6 +996,64 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     rc = qfx_launch_contract_tc_fused(ctx, d, A, B, C, &done);
     if (rc || done) return rc;
     if (d.n_bits >= 5 && d.k_bits >= 5) return qfx_launch_contract_tc(ctx, d, A, B, C);
+  }
+
+  // ---------------- K <= 4, both free sides long, small operands: C-ordered outer product
+  if (!accumulate_amp && d.k_bits <= 2 && d.n_bits >= 4 && d.m_bits + d.n_bits >= 18 &&
+      d.m_bits + d.k_bits <= 21 && d.n_bits + d.k_bits <= 21 && !(d.off_c & 1) &&
+      getenv("QFLEX_NO_OUTER") == nullptr) {
+    const int c_bits = d.m_bits + d.n_bits;
+    // owner of every C address bit: (is_a, position in that operand)
+    std::vector<int> own_a(c_bits, -1), own_b(c_bits, -1);
+    bool dense = true;
+    for (int i = 0; i < d.m_bits; ++i) {
+      if (d.c_m[i] >= c_bits) dense = false;
+      else own_a[d.c_m[i]] = d.a_m[i];
+    }
+    for (int i = 0; i < d.n_bits; ++i) {
+      if (d.c_n[i] >= c_bits) dense = false;
+      else own_b[d.c_n[i]] = d.b_n[i];
+    }
+    if (dense) {
+      OuterArgs g{};
+      g.A = A;
+      g.B = B;
+      g.C = C;
+      g.c_bits = c_bits;
+      g.k_bits = d.k_bits;
+      for (int q = 0; q < d.k_bits; ++q) g.a_k[q] = d.a_k[q], g.b_k[q] = d.b_k[q];
+      g.low_is_a = own_a[0] >= 0 ? 1 : 0;
+      g.low_delta = 1u << (g.low_is_a ? own_a[0] : own_b[0]);
+      bool ok = true;
+      for (int p = 1; p < c_bits;) {
+        const bool is_a = own_a[p] >= 0;
+        const int first = is_a ? own_a[p] : own_b[p];
+        int q = p + 1;
+        while (q < c_bits && (own_a[q] >= 0) == is_a &&
+               (is_a ? own_a[q] : own_b[q]) == first + (q - p))
+          ++q;
+        if (g.n_seg == 16) {
+          ok = false;
+          break;
+        }
+        g.seg[g.n_seg++] = OuterSeg{p, q - p, is_a ? first : 0, is_a ? -1 : first};
+        p = q;
+      }
+      if (ok) {
+        const unsigned long long pairs = 1ull << (c_bits - 1);
+        const unsigned blocks =
+            (unsigned)std::min<unsigned long long>((pairs + 255) / 256, 16ull * ctx->sm_count);
+        switch (d.k_bits) {
+          case 0: outer_small<0><<<blocks, 256, 0, ctx->stream>>>(g); break;
+          case 1: outer_small<1><<<blocks, 256, 0, ctx->stream>>>(g); break;
+          default: outer_small<2><<<blocks, 256, 0, ctx->stream>>>(g); break;
+        }
+        QFX_CUDA(cudaGetLastError());
+        ctx->stats.launches_gemm_ffma++;
+        ctx->stats.launches_total++;
+        return QFX_OK;
+      }
+    }
   }
 
   // ---------------- tiny N and K, long M: streaming kernel

@@ -446,3 +446,25 @@ def test_resident_program_of_chains_with_slice_dependent_bases(ctx):
     # a var term that names a cut the caller did not pass is refused
     assert lib.qfx_program_run(ctx.h, prog, (ctypes.c_uint32 * 1)(0), 1) != 0
     assert lib.qfx_program_destroy(ctx.h, prog) == 0
+
+
+@pytest.mark.parametrize("m,n,k", [(10, 9, 1), (12, 12, 1), (9, 10, 2), (11, 8, 0), (13, 6, 2), (4, 15, 1)])
+def test_contract_small_k_long_m_and_n_output_ordered(ctx, m, n, k):
+    """Roots of the tree-ordered world lines: K <= 4, both free sides long, the result
+    written in an arbitrary (grid tensor) layout -- enumerated in C-address order."""
+    rng = np.random.default_rng(31 * m + 7 * n + k)
+    # result layout in groups of bits (bonds), alternately from the two operands
+    order = []
+    am, bn = list(range(m)), list(range(n))
+    while am or bn:
+        for src, tag in ((am, "m"), (bn, "n")):
+            take = int(rng.integers(1, 5))
+            order += [(tag, src.pop(0)) for _ in range(min(take, len(src)))]
+    c_m, c_n = [0] * m, [0] * n
+    for pos, (tag, i) in enumerate(order):
+        (c_m if tag == "m" else c_n)[i] = pos
+    pa, pb = rng.permutation(m + k), rng.permutation(n + k)
+    t = dict(a_m=sorted(int(x) for x in pa[:m]), a_k=[int(x) for x in pa[m:]],
+             b_n=sorted(int(x) for x in pb[:n]), b_k=[int(x) for x in pb[n:]], c_m=c_m, c_n=c_n)
+    assert _run_contract(ctx, t, rng) < TOL
+    assert _run_contract(ctx, _random_tables(rng, m, n, k), rng) < TOL
