@@ -621,50 +621,86 @@ struct OuterArgs {
   int8_t a_k[2], b_k[2];
 };
 
+// A block works on tiles of 2^12 consecutive C elements (2048 pairs): the operand
+// offsets of C address bits 1..11 come from two 6-bit / 5-bit tables in shared memory
+// (built once per block), those of the bits above from the run list, once per tile.
 template <int KB>
 __global__ void __launch_bounds__(256) outer_small(const __grid_constant__ OuterArgs g) {
   constexpr int K = 1 << KB;
   __shared__ unsigned ka[K], kb[K];
-  if ((int)threadIdx.x < K) {
+  __shared__ unsigned lo_a[64], lo_b[64], mid_a[32], mid_b[32];  // C bits 1..6, 7..11
+  __shared__ unsigned tile_a, tile_b;
+  const unsigned tid = threadIdx.x;
+  if ((int)tid < K) {
     unsigned oa = 0, ob = 0;
     for (int q = 0; q < KB; ++q) {
-      oa |= ((threadIdx.x >> q) & 1u) << g.a_k[q];
-      ob |= ((threadIdx.x >> q) & 1u) << g.b_k[q];
+      oa |= ((tid >> q) & 1u) << g.a_k[q];
+      ob |= ((tid >> q) & 1u) << g.b_k[q];
     }
-    ka[threadIdx.x] = oa;
-    kb[threadIdx.x] = ob;
+    ka[tid] = oa;
+    kb[tid] = ob;
   }
-  __syncthreads();
-  const unsigned long long pairs = 1ull << (g.c_bits - 1);
+  if (tid >= 64 && tid < 64 + 96) {
+    // offsets of a group of low C address bits, from the run list
+    const unsigned e = tid - 64, idx = e < 64 ? e : e - 64;
+    const unsigned long long c = e < 64 ? (unsigned long long)idx << 1 : (unsigned long long)idx << 7;
+    const unsigned long long mask = e < 64 ? 0x7eull : 0xf80ull;
+    unsigned oa = 0, ob = 0;
+    for (int s = 0; s < g.n_seg; ++s)
+      for (int q = 0; q < g.seg[s].len; ++q) {
+        const int p = g.seg[s].start + q;
+        if (!((mask >> p) & 1ull) || !((c >> p) & 1ull)) continue;
+        if (g.seg[s].b_shift < 0) oa |= 1u << (g.seg[s].a_shift + q);
+        else ob |= 1u << (g.seg[s].b_shift + q);
+      }
+    if (e < 64) lo_a[idx] = oa, lo_b[idx] = ob;
+    else mid_a[idx] = oa, mid_b[idx] = ob;
+  }
+  const unsigned long long tiles = g.c_bits > 12 ? 1ull << (g.c_bits - 12) : 1ull;
+  const unsigned pairs_in_tile = g.c_bits > 12 ? 2048u : 1u << (g.c_bits - 1);
   const float2* __restrict__ A = g.A;
   const float2* __restrict__ B = g.B;
-  for (unsigned long long t = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; t < pairs;
-       t += (unsigned long long)gridDim.x * blockDim.x) {
-    const unsigned long long c = t << 1;
-    unsigned ao = 0, bo = 0;
-    for (int s = 0; s < g.n_seg; ++s) {
-      const unsigned f = (unsigned)(c >> g.seg[s].start) & ((1u << g.seg[s].len) - 1u);
-      if (g.seg[s].b_shift < 0) ao |= f << g.seg[s].a_shift;
-      else bo |= f << g.seg[s].b_shift;
+  for (unsigned long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned long long c = tile << 12;
+      unsigned oa = 0, ob = 0;
+      for (int s = 0; s < g.n_seg; ++s) {
+        // the part of the run at C address bits >= 12
+        int start = g.seg[s].start, len = g.seg[s].len, skip = 0;
+        if (start + len <= 12) continue;
+        if (start < 12) skip = 12 - start;
+        const unsigned f = (unsigned)(c >> (start + skip)) & ((1u << (len - skip)) - 1u);
+        if (g.seg[s].b_shift < 0) oa |= f << (g.seg[s].a_shift + skip);
+        else ob |= f << (g.seg[s].b_shift + skip);
+      }
+      tile_a = oa;
+      tile_b = ob;
     }
-    const unsigned ao1 = g.low_is_a ? ao | g.low_delta : ao;
-    const unsigned bo1 = g.low_is_a ? bo : bo | g.low_delta;
-    float x0 = 0.f, y0 = 0.f, x1 = 0.f, y1 = 0.f;
+    __syncthreads();
+    const unsigned ta = tile_a, tb = tile_b;
+#pragma unroll 2
+    for (unsigned p = tid; p < pairs_in_tile; p += 256) {
+      const unsigned ao = ta | lo_a[p & 63u] | mid_a[p >> 6], bo = tb | lo_b[p & 63u] | mid_b[p >> 6];
+      const unsigned ao1 = g.low_is_a ? ao | g.low_delta : ao;
+      const unsigned bo1 = g.low_is_a ? bo : bo | g.low_delta;
+      float x0 = 0.f, y0 = 0.f, x1 = 0.f, y1 = 0.f;
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const float2 a0 = __ldg(A + (ao | ka[k])), b0 = __ldg(B + (bo | kb[k]));
-      const float2 a1 = g.low_is_a ? __ldg(A + (ao1 | ka[k])) : a0;
-      const float2 b1 = g.low_is_a ? b0 : __ldg(B + (bo1 | kb[k]));
-      x0 = fmaf(a0.x, b0.x, x0);
-      x0 = fmaf(-a0.y, b0.y, x0);
-      y0 = fmaf(a0.x, b0.y, y0);
-      y0 = fmaf(a0.y, b0.x, y0);
-      x1 = fmaf(a1.x, b1.x, x1);
-      x1 = fmaf(-a1.y, b1.y, x1);
-      y1 = fmaf(a1.x, b1.y, y1);
-      y1 = fmaf(a1.y, b1.x, y1);
+      for (int k = 0; k < K; ++k) {
+        const float2 a0 = __ldg(A + (ao | ka[k])), b0 = __ldg(B + (bo | kb[k]));
+        const float2 a1 = g.low_is_a ? __ldg(A + (ao1 | ka[k])) : a0;
+        const float2 b1 = g.low_is_a ? b0 : __ldg(B + (bo1 | kb[k]));
+        x0 = fmaf(a0.x, b0.x, x0);
+        x0 = fmaf(-a0.y, b0.y, x0);
+        y0 = fmaf(a0.x, b0.y, y0);
+        y0 = fmaf(a0.y, b0.x, y0);
+        x1 = fmaf(a1.x, b1.x, x1);
+        x1 = fmaf(-a1.y, b1.y, x1);
+        y1 = fmaf(a1.x, b1.y, y1);
+        y1 = fmaf(a1.y, b1.x, y1);
+      }
+      *reinterpret_cast<float4*>(g.C + (tile << 12) + 2ull * p) = make_float4(x0, y0, x1, y1);
     }
-    *reinterpret_cast<float4*>(g.C + c) = make_float4(x0, y0, x1, y1);
   }
 }
 
@@ -1040,9 +1076,8 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
         p = q;
       }
       if (ok) {
-        const unsigned long long pairs = 1ull << (c_bits - 1);
-        const unsigned blocks =
-            (unsigned)std::min<unsigned long long>((pairs + 255) / 256, 16ull * ctx->sm_count);
+        const unsigned long long tiles = c_bits > 12 ? 1ull << (c_bits - 12) : 1ull;
+        const unsigned blocks = (unsigned)std::min<unsigned long long>(tiles, 8ull * ctx->sm_count);
         switch (d.k_bits) {
           case 0: outer_small<0><<<blocks, 256, 0, ctx->stream>>>(g); break;
           case 1: outer_small<1><<<blocks, 256, 0, ctx->stream>>>(g); break;
@@ -1111,6 +1146,40 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
   // ---------------- a few outputs on one side, long K, dense big operand: linear GEMV
   if (!accumulate_amp && d.n_bits == 0 && d.m_bits >= 1 && d.m_bits <= 6 && d.k_bits >= 10 &&
       mask_a_dense(d) && !(d.off_a & 1) && getenv("QFLEX_NO_GEMV") == nullptr) {
+    // The big operand is read linearly; the vector is read at the addresses its own
+    // layout gives the same k.  When the two layouts order the k bits differently those
+    // reads scatter (7x7 tails: 2^24-element vector, 3.0 of 6.4 TB/s).  For long K the
+    // vector is first permuted into the big operand's k order (one extra read + write
+    // of the SMALL side, 1/2^m of the big one).
+    static const bool gemv_permute = [] {
+      const char* e = getenv("QFLEX_GEMV_PERMUTE");
+      return e == nullptr || e[0] != '0';
+    }();
+    size_t b_perm_bytes = 0;
+    {
+      bool same_order = true;
+      std::vector<int> by_a(d.k_bits);
+      for (int i = 0; i < d.k_bits; ++i) by_a[i] = i;
+      std::sort(by_a.begin(), by_a.end(), [&](int x, int y) { return d.a_k[x] < d.a_k[y]; });
+      for (int i = 0; i + 1 < d.k_bits; ++i)
+        if (d.b_k[by_a[i]] > d.b_k[by_a[i + 1]]) same_order = false;
+      uint64_t mask_b_dense = 0;
+      for (int i = 0; i < d.k_bits; ++i) mask_b_dense |= 1ull << d.b_k[i];
+      const bool b_dense = mask_b_dense == (1ull << d.k_bits) - 1ull;
+      if (gemv_permute && !same_order && b_dense && d.k_bits >= 18) {
+        b_perm_bytes = sizeof(float2) << d.k_bits;
+        int8_t dst_pos[QFX_MAX_BITS];
+        for (int r = 0; r < d.k_bits; ++r) dst_pos[d.b_k[by_a[r]]] = (int8_t)r;
+        int ks0 = 0;  // (same split as below: the reduce workspace sits behind the copy)
+        int rc = qfx_ensure_ws(ctx, b_perm_bytes + (sizeof(double2) << (d.m_bits + 12)));
+        if (rc) return rc;
+        (void)ks0;
+        rc = qfx_launch_permute_ptr(ctx, B, reinterpret_cast<float2*>(ctx->ws), d.k_bits, dst_pos);
+        if (rc) return rc;
+        B = reinterpret_cast<const float2*>(ctx->ws);
+        for (int r = 0; r < d.k_bits; ++r) d.b_k[by_a[r]] = (int8_t)r;
+      }
+    }
     GemvArgs g{};
     g.A = A;
     g.B = B;
@@ -1135,9 +1204,10 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     int ks = 0;
     while (ks < g.n_hk - 4 && (1ll << (g.n_hm + ks)) < 8ll * ctx->sm_count) ++ks;
     g.ks_bits = ks;
-    int rc = qfx_ensure_ws(ctx, sizeof(double2) << (d.m_bits + ks));
+    int rc = qfx_ensure_ws(ctx, b_perm_bytes + (sizeof(double2) << (d.m_bits + ks)));
     if (rc) return rc;
-    g.ws = reinterpret_cast<double2*>(ctx->ws);
+    if (b_perm_bytes) g.B = reinterpret_cast<const float2*>(ctx->ws);  // (ws may not move: sized above)
+    g.ws = reinterpret_cast<double2*>(reinterpret_cast<uint8_t*>(ctx->ws) + b_perm_bytes);
     dim3 grid(1u << g.n_hm, 1u << ks);
     gemv_rows<<<grid, 256, 0, ctx->stream>>>(g);
     QFX_CUDA(cudaGetLastError());

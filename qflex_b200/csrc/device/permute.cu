@@ -94,6 +94,12 @@ int qfx_launch_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
     qfx_set_error("qfx_permute: source and destination overlap");
     return QFX_ERR_ARG;
   }
+  return qfx_launch_permute_ptr(ctx, ctx->arena + src_off, ctx->arena + dst_off, n_bits, dst_pos);
+}
+
+// Same on raw device pointers (dst_pos already validated: a permutation of 0..n_bits-1).
+int qfx_launch_permute_ptr(qfx_ctx* ctx, const float2* src, float2* dst, int n_bits,
+                           const int8_t* dst_pos) {
   // tile = low source bits U pre-images of low destination bits, padded with
   // further low source bits up to kTileBits
   std::vector<char> in_tile(n_bits, 0);
@@ -113,8 +119,8 @@ int qfx_launch_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
       ++t;
     }
   PermArgs g{};
-  g.src = ctx->arena + src_off;
-  g.dst = ctx->arena + dst_off;
+  g.src = src;
+  g.dst = dst;
   g.n_bits = n_bits;
   g.t_bits = t;
   g.o_bits = n_bits - t;

@@ -83,5 +83,7 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& d, const 
 // permute.cu
 int qfx_launch_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
                        int n_bits, const int8_t* dst_pos);
+int qfx_launch_permute_ptr(qfx_ctx* ctx, const float2* src, float2* dst, int n_bits,
+                           const int8_t* dst_pos);
 
 #endif  // QFX_INTERNAL_H_
