@@ -473,8 +473,12 @@ bool make_map_a(CUtensorMap* map, const float2* A, const qfx_contract_desc& d, i
   if (bits[0].addr != 0) return false;
   // runs of consecutive addresses (first run <= 7 bits: 2 * 2^7 floats = 256 box limit)
   std::vector<std::pair<int, int>> runs;  // (first addr, length)
+  static const int run0_cap = [] {
+    const char* e = getenv("QFLEX_MAP_RUN0_CAP");
+    return e ? std::max(1, std::min(7, atoi(e))) : 7;
+  }();
   for (size_t s = 0; s < bits.size(); ++s) {
-    const int cap = runs.size() == 1 ? 7 : 8;
+    const int cap = runs.size() == 1 ? run0_cap : 8;
     if (!runs.empty() && runs.back().first + runs.back().second == bits[s].addr &&
         runs.back().second < cap)
       runs.back().second++;
