@@ -68,6 +68,7 @@ struct FusedArgs {
                       // of the A tile: columns 32..63 of the bf16 row); two accumulators per stage
   int stagger_ns;     // tc_pair: start delay per pair index (tuning experiment)
   int blocked;        // tc_pair: each pair owns a contiguous range of tiles (else interleaved)
+  int one_arrive;     // tc_pair: one barrier arrive per CTA (not per warp) for "A converted" / "accumulator drained"
   int ksplit;         // tc_fused split-K: work items = tiles * ksplit, kblocks = k blocks per item
   float2* part;       // split-K partial results [ksplit][M][N] (natural layout)
   int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads (timing experiments)

@@ -149,10 +149,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < MAX_SA; ++s) {
       mbar_init(a_full(s), 1);
-      mbar_init(a_empty(s), CONV_WARPS);
+      mbar_init(a_empty(s), g.one_arrive ? 1 : CONV_WARPS);
     }
     for (int s = 0; s < MAX_SC; ++s) {
-      mbar_init(c_full(s), 2 * CONV_WARPS);
+      mbar_init(c_full(s), g.one_arrive ? 2 : 2 * CONV_WARPS);
       mbar_init(c_empty(s), 1);
     }
     for (int s = 0; s < MAX_SB; ++s) {
@@ -161,7 +161,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
     }
     for (int s = 0; s < MAX_ACC; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 2 * 8);
+      mbar_init(tempty_bar(s), g.one_arrive ? 2 : 2 * 8);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -270,7 +270,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
               for (int kk = 0; kk < nkk; ++kk)
                 umma2_bf16(d_tmem, dAh + 2 * (2 * h + kk), dBh + 2 * kk, idesc, 1u);
               if (h == 1) umma2_commit(c_empty(cs));
-              umma2_commit(tfull_bar(acc));
+              // one "accumulators full" commit per stage: both m tiles are drained after
+              // the second one's MMAs anyway (2^24 x 16 x 16: 0.910 -> 0.884 ms)
+              if (h == 1) umma2_commit(tfull_bar(acc));
             }
           }
           if (++cs == g.sc) {
@@ -400,10 +402,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
           }
         }
         fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          mbar_arrive_leader(c_full(cs));
-          mbar_arrive(a_empty(as));
+        if (g.one_arrive) {
+          // ONE (remote) arrive per CTA and stage instead of one per converter warp:
+          // arrivals from the peer CTA are serialised at the leader's barrier, and 8 of
+          // them per 16-KB stage bounded the K = 16 classes (tools/dbg_sweep.sh)
+          asm volatile("bar.sync 1, %0;" ::"n"(CONV_WARPS * 32) : "memory");
+          if (ctid == 0) {
+            mbar_arrive_leader(c_full(cs));
+            mbar_arrive(a_empty(as));
+          }
+        } else {
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive_leader(c_full(cs));
+            mbar_arrive(a_empty(as));
+          }
         }
         if (++as == g.sa) {
           as = 0;
@@ -463,7 +476,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         }
         const int acc = set * subs + sub;
         float sum[8][16];
-        mbar_wait_spin(tfull_bar(acc), set_phase);
+        mbar_wait_spin(tfull_bar(g.dual ? set * 2 + 1 : acc), set_phase);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) +
                                (uint32_t)(acc * bn + half * half_cols);
@@ -484,8 +497,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
             }
         }
         tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+        if (g.one_arrive) {
+          asm volatile("bar.sync 2, %0;" ::"n"(8 * 32) : "memory");
+          if (warp == EPI_WARP0 && lane == 0) mbar_arrive_leader(tempty_bar(acc));
+        } else {
+          __syncwarp();
+          if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+        }
         if (STORE == 2 && t_stores) {
           const unsigned long long mb = mtile * BM + m_local_b;
           unsigned long long rb = 0;
@@ -688,6 +706,10 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
     if (g.sc < MAX_SC && g.sc < g.sa && total() + a16 <= SMEM_LIMIT) { ++g.sc; grew = true; }
   }
   if (const char* e = getenv("QFLEX_PAIR_BLOCKED")) g.blocked = atoi(e);
+  // (experiment, off: one barrier arrive per CTA instead of one per warp -- fewer remote
+  // arrivals, but the extra named barrier costs more than they do: 0.892 -> 0.911 ms)
+  g.one_arrive = 0;
+  if (const char* e = getenv("QFLEX_PAIR_ONE_ARRIVE")) g.one_arrive = atoi(e) != 0;
   // start stagger: the pairs otherwise run in lockstep and hit HBM with synchronized
   // load / store bursts (2^20 x 256 x 256: 0.947 -> 0.926 ms); only when a pair has
   // enough tiles for the start delay (<= one tile time for the last pair) to pay off
