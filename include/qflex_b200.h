@@ -121,6 +121,22 @@ typedef struct qfx_contract_desc {
 
 int qfx_contract(qfx_ctx* ctx, const qfx_contract_desc* desc);
 
+/* The same contraction on the CTA-pair tensor-core kernel with NO device allocation:
+ * the kernel's scratch (the smaller operand split into bf16 hi / mid) lives in a
+ * static device array of 1 MiB instead of the context's workspace, so the call issues
+ * no cudaMalloc / cudaFree (CUDA graph capture, serving loops, harnesses that forbid
+ * allocation).  No counterpart in the reference.
+ * Operands are arena offsets as for qfx_contract (the arena is the
+ * caller's, reserved beforehand).  Limits: the smaller operand holds at most
+ * 2^QFX_STATIC_MAX_B_BITS elements with n_bits <= 8 and k_bits <= 8 (after the larger
+ * free side is made the rows), and the shape must be one the pair kernel takes
+ * (m_bits >= 8 with 2^m_bits / 256 >= number of SM pairs, n_bits >= 4, k_bits >= 4);
+ * anything else is QFX_ERR_ARG with the reason in qfx_last_error().  All calls on one
+ * GPU share the array: calls that overlap on the device (different contexts or
+ * streams) race; calls on one context serialise on its stream and are safe. */
+#define QFX_STATIC_MAX_B_BITS 16
+int qfx_contract_pair_static(qfx_ctx* ctx, const qfx_contract_desc* desc);
+
 /* n_chains independent chains of small contractions in ONE launch: chain c is the
  * steps descs[chain_first[c] .. chain_first[c+1]) executed in order (a step may
  * read what earlier steps of ITS chain wrote; chains must not touch each

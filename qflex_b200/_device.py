@@ -65,6 +65,7 @@ def load(path=DEFAULT_DEVICE_LIB):
     c.qfx_download.argtypes = [vp, u64, vp, u64]
     c.qfx_copy.argtypes = [vp, u64, u64, u64]
     c.qfx_contract.argtypes = [vp, ctypes.POINTER(ContractDesc)]
+    c.qfx_contract_pair_static.argtypes = [vp, ctypes.POINTER(ContractDesc)]
     c.qfx_dot_accumulate.argtypes = [vp, ctypes.POINTER(ContractDesc), u64]
     c.qfx_contract_chains.argtypes = [vp, ctypes.POINTER(ContractDesc),
                                       ctypes.POINTER(ctypes.c_int32), i32]
@@ -136,6 +137,11 @@ class Context:
 
     def contract(self, desc):
         self._ck(self.c.qfx_contract(self.h, ctypes.byref(desc)))
+
+    def contract_pair_static(self, desc):
+        """qfx_contract_pair_static: the CTA-pair kernel with its scratch in a static
+        device array (no device allocation inside the call)."""
+        self._ck(self.c.qfx_contract_pair_static(self.h, ctypes.byref(desc)))
 
     def dot_accumulate(self, desc, slot):
         self._ck(self.c.qfx_dot_accumulate(self.h, ctypes.byref(desc), slot))

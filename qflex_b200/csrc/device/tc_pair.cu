@@ -593,15 +593,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 }  // namespace
 
 // Roles already swapped (m_bits >= n_bits).  *done = false: not applicable (the
-// caller tries tc_fused next).
-int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2* A,
-                                const float2* B, float2* C, bool* done) {
+// caller tries tc_fused next).  `scratch` = where B' hi/mid go: nullptr = the context's
+// workspace (grown on demand), else a caller-owned buffer of >= 2 * N * K * 8 bytes
+// (qfx_contract_pair_static below).
+static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2* A,
+                       const float2* B, float2* C, bool* done, uint8_t* scratch) {
   *done = false;
-  static const bool disabled = [] {
-    const char* e = getenv("QFLEX_TC_PAIR");
-    return e != nullptr && atoi(e) == 0;
-  }();
-  if (disabled) return QFX_OK;
   qfx_contract_desc d = din;
   if (d.m_bits < 8 || d.n_bits < 4 || d.k_bits < 4 || d.n_bits > 8 || d.k_bits > 8) return QFX_OK;
   const uint64_t M = 1ull << d.m_bits, N = 1ull << d.n_bits, K = 1ull << d.k_bits;
@@ -730,9 +727,13 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
 
   // workspace: B' hi/mid (2N x 2K bf16 each)
   const size_t b_bytes = (size_t)N * K * 8;
-  int rc = qfx_ensure_ws(ctx, 2 * b_bytes + 4096);
-  if (rc) return rc;
-  uint8_t* ws = reinterpret_cast<uint8_t*>(ctx->ws);
+  int rc = QFX_OK;
+  uint8_t* ws = scratch;
+  if (ws == nullptr) {
+    rc = qfx_ensure_ws(ctx, 2 * b_bytes + 4096);
+    if (rc) return rc;
+    ws = reinterpret_cast<uint8_t*>(ctx->ws);
+  }
   uint32_t* b_hi = reinterpret_cast<uint32_t*>(ws);
   uint32_t* b_mid = reinterpret_cast<uint32_t*>(ws + b_bytes);
   rc = qfx_launch_split(ctx, B, 1, d.b_n, d.n_bits, d.b_k, d.k_bits, b_hi, b_mid);
@@ -764,5 +765,119 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, cons
   ctx->stats.launches_gemm_tc_pair++;
   ctx->stats.launches_total++;
   *done = true;
+  return QFX_OK;
+}
+
+int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2* A,
+                                const float2* B, float2* C, bool* done) {
+  *done = false;
+  static const bool disabled = [] {
+    const char* e = getenv("QFLEX_TC_PAIR");
+    return e != nullptr && atoi(e) == 0;
+  }();
+  if (disabled) return QFX_OK;
+  return launch_pair(ctx, din, A, B, C, done, nullptr);
+}
+
+// ---------------------------------------------------------------- no-allocation entry
+// qfx_contract_pair_static: the CTA-pair kernel above with its scratch (the small
+// operand split into bf16 hi / mid, 2 x N x K x 8 bytes) in a file-scope device array
+// instead of the context's cudaMalloc'ed workspace, for callers that may not allocate
+// (CUDA graph capture, serving loops).  No counterpart in the reference.
+// Every GPU that loads the library holds the array
+// (1 MiB) until exit.  The split kernel rewrites every byte the pair kernel reads, so
+// nothing has to start at zero; all calls share the array, so calls that overlap on
+// the GPU (different contexts / streams on one device) race.
+static __device__ __align__(256) unsigned char
+    qfx_pair_static_scratch[2ull * 8ull << QFX_STATIC_MAX_B_BITS];
+
+extern "C" int qfx_contract_pair_static(qfx_ctx* ctx, const qfx_contract_desc* din) {
+  if (ctx == nullptr || din == nullptr) {
+    qfx_set_error("qfx_contract_pair_static: null argument");
+    return QFX_ERR_ARG;
+  }
+  qfx_contract_desc d = *din;
+  if (d.m_bits < 0 || d.n_bits < 0 || d.k_bits < 0 || d.m_bits + d.k_bits > 32 ||
+      d.n_bits + d.k_bits > 32 || d.m_bits + d.n_bits > 32) {
+    qfx_set_error("qfx_contract_pair_static: operand rank out of range (max 32 bits each)");
+    return QFX_ERR_ARG;
+  }
+  auto span_of = [](const int8_t* p, int np, const int8_t* q, int nq, uint64_t* span) {
+    uint64_t seen = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+      const int8_t* v = pass ? q : p;
+      const int n = pass ? nq : np;
+      for (int i = 0; i < n; ++i) {
+        if (v[i] < 0 || v[i] >= 32 || ((seen >> v[i]) & 1ull)) return false;
+        seen |= 1ull << v[i];
+      }
+    }
+    *span = seen + 1;
+    return true;
+  };
+  uint64_t sa, sb, sc;
+  if (!span_of(d.a_m, d.m_bits, d.a_k, d.k_bits, &sa) ||
+      !span_of(d.b_k, d.k_bits, d.b_n, d.n_bits, &sb) ||
+      !span_of(d.c_m, d.m_bits, d.c_n, d.n_bits, &sc)) {
+    qfx_set_error("qfx_contract_pair_static: bit positions of an operand must be distinct and < 32");
+    return QFX_ERR_ARG;
+  }
+  if (d.off_a + sa > ctx->arena_elems || d.off_b + sb > ctx->arena_elems ||
+      d.off_c + sc > ctx->arena_elems) {
+    qfx_set_error("qfx_contract_pair_static: operand outside the arena");
+    return QFX_ERR_ARG;
+  }
+  if ((d.off_a < d.off_c + sc && d.off_c < d.off_a + sa) ||
+      (d.off_b < d.off_c + sc && d.off_c < d.off_b + sb)) {
+    qfx_set_error("qfx_contract_pair_static: C overlaps an input operand");
+    return QFX_ERR_ARG;
+  }
+  if (d.n_bits > d.m_bits) {  // the larger free side plays the rows (as qfx_contract does)
+    std::swap(d.off_a, d.off_b);
+    std::swap(d.m_bits, d.n_bits);
+    for (int i = 0; i < QFX_MAX_BITS; ++i) {
+      std::swap(d.a_m[i], d.b_n[i]);
+      std::swap(d.c_m[i], d.c_n[i]);
+      std::swap(d.a_k[i], d.b_k[i]);
+    }
+  }
+  if (d.n_bits + d.k_bits > QFX_STATIC_MAX_B_BITS || d.n_bits > 8 || d.k_bits > 8) {
+    qfx_set_error("qfx_contract_pair_static: the smaller operand (2^" +
+                  std::to_string(d.n_bits + d.k_bits) + " elements, n_bits " +
+                  std::to_string(d.n_bits) + ", k_bits " + std::to_string(d.k_bits) +
+                  ") exceeds the static scratch: at most 2^" +
+                  std::to_string(QFX_STATIC_MAX_B_BITS) +
+                  " elements with n_bits <= 8 and k_bits <= 8");
+    return QFX_ERR_ARG;
+  }
+  QFX_CUDA(cudaSetDevice(ctx->device));
+  // In host code the array's name is a host-side stand-in: its device address is
+  // looked up once per device, with that device current.
+  static qfx_per_device_once looked_up;
+  static uint8_t* scratch_of[64] = {};
+  if (ctx->device < 0 || ctx->device >= 64) {
+    qfx_set_error("qfx_contract_pair_static: device index out of range");
+    return QFX_ERR_ARG;
+  }
+  if (looked_up.need(ctx->device)) {
+    void* p = nullptr;
+    QFX_CUDA(cudaGetSymbolAddress(&p, qfx_pair_static_scratch));
+    scratch_of[ctx->device] = static_cast<uint8_t*>(p);
+    looked_up.mark(ctx->device);
+  }
+  bool done = false;
+  int rc = launch_pair(ctx, d, ctx->arena + d.off_a, ctx->arena + d.off_b, ctx->arena + d.off_c,
+                       &done, scratch_of[ctx->device]);
+  if (rc) return rc;
+  if (!done) {
+    qfx_set_error("qfx_contract_pair_static: shape outside the CTA-pair kernel's range "
+                  "(needs m_bits >= 8 with 2^m_bits / 256 >= SM pairs, 4 <= n_bits <= 8, "
+                  "4 <= k_bits <= 8, TMA-addressable A)");
+    return QFX_ERR_ARG;
+  }
+  const double M = (double)(1ull << d.m_bits), N = (double)(1ull << d.n_bits),
+               K = (double)(1ull << d.k_bits);
+  ctx->stats.flops += 8.0 * M * N * K;
+  ctx->stats.bytes += 8.0 * (M * K + K * N + M * N);
   return QFX_OK;
 }
