@@ -198,6 +198,17 @@ int qfx_amps_download(qfx_ctx* ctx, double* host_re_im, uint64_t n_amps);
 int qfx_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
                 int32_t n_bits, const int8_t* dst_pos);
 
+/* Index permutation for axes of ARBITRARY dimensions (not powers of two, unit axes):
+ * the tensor at src_off is row-major over dims[0..rank) (last axis fastest); new axis j
+ * of the result at dst_off is old axis new_order[j].  Replaces Tensor::reorder ->
+ * _naive_reorder (src/tensor.cpp:377-492), the branch the reference takes when a
+ * dimension is not 2^k.  The circuit pipeline never produces such tensors; provided
+ * so that a Tensor-level port has the whole reorder family.  src and dst must not
+ * overlap; rank <= QFX_MAX_RANK. */
+#define QFX_MAX_RANK 24
+int qfx_reorder_general(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off, int32_t rank,
+                        const uint32_t* dims, const int32_t* new_order);
+
 /* Timing helpers (CUDA events on the context stream). */
 int qfx_timer_start(qfx_ctx* ctx);
 int qfx_timer_stop_ms(qfx_ctx* ctx, float* ms_out);

@@ -79,6 +79,7 @@ def load(path=DEFAULT_DEVICE_LIB):
     c.qfx_amps_reserve.argtypes = [vp, u64]
     c.qfx_amps_download.argtypes = [vp, vp, u64]
     c.qfx_permute.argtypes = [vp, u64, u64, i32, vp]
+    c.qfx_reorder_general.argtypes = [vp, u64, u64, i32, vp, vp]
     c.qfx_timer_start.argtypes = [vp]
     c.qfx_timer_stop_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     c.qfx_stats_get.argtypes = [vp, ctypes.POINTER(Stats)]
@@ -152,6 +153,12 @@ class Context:
     def tensor_accumulate(self, off, slot_stride, slot=0):
         st = (ctypes.c_uint32 * max(1, len(slot_stride)))(*slot_stride)
         self._ck(self.c.qfx_tensor_accumulate(self.h, off, len(slot_stride), st, slot))
+
+    def reorder_general(self, src, dst, dims, new_order):
+        """qfx_reorder_general: axes of arbitrary dimensions (Tensor::_naive_reorder)."""
+        d = (ctypes.c_uint32 * max(1, len(dims)))(*dims)
+        o = (ctypes.c_int32 * max(1, len(new_order)))(*new_order)
+        self._ck(self.c.qfx_reorder_general(self.h, src, dst, len(dims), d, o))
 
     def permute(self, src, dst, dst_pos):
         p = (ctypes.c_int8 * max(1, len(dst_pos)))(*dst_pos)

@@ -153,3 +153,93 @@ int qfx_launch_permute_ptr(qfx_ctx* ctx, const float2* src, float2* dst, int n_b
   ctx->stats.launches_total++;
   return QFX_OK;
 }
+
+// ---------------------------------------------------------------- general dimensions
+// Tensor::_naive_reorder (reference src/tensor.cpp:377-492): axes of arbitrary
+// (non-power-of-two, unit) dimensions.  The pipeline never produces such tensors --
+// every index of a circuit network has dimension 2^k -- so this is the plain form:
+// one thread per DESTINATION element (coalesced writes), the source offset rebuilt
+// from the mixed-radix digits of the destination offset (gathered reads).
+namespace {
+struct GeneralReorderArgs {
+  const float2* src;
+  float2* dst;
+  unsigned long long total;
+  int rank;
+  uint32_t new_dim[QFX_MAX_RANK];            // dimension of new axis j
+  unsigned long long src_stride[QFX_MAX_RANK];  // source stride of new axis j
+};
+
+__global__ void reorder_general_kernel(const __grid_constant__ GeneralReorderArgs g) {
+  const unsigned long long step = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long o = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+       o < g.total; o += step) {
+    unsigned long long rest = o, s = 0;
+    for (int j = g.rank - 1; j >= 0; --j) {
+      const unsigned long long digit = rest % g.new_dim[j];
+      rest /= g.new_dim[j];
+      s += digit * g.src_stride[j];
+    }
+    g.dst[o] = g.src[s];
+  }
+}
+}  // namespace
+
+extern "C" int qfx_reorder_general(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off, int32_t rank,
+                                   const uint32_t* dims, const int32_t* new_order) {
+  if (ctx == nullptr || (rank > 0 && (dims == nullptr || new_order == nullptr))) {
+    qfx_set_error("qfx_reorder_general: null argument");
+    return QFX_ERR_ARG;
+  }
+  if (rank <= 0) {
+    // reference: "Number of indices cannot be zero." (src/tensor.cpp:393)
+    qfx_set_error("qfx_reorder_general: Number of indices cannot be zero.");
+    return QFX_ERR_ARG;
+  }
+  if (rank > QFX_MAX_RANK) {
+    qfx_set_error("qfx_reorder_general: rank above QFX_MAX_RANK");
+    return QFX_ERR_ARG;
+  }
+  unsigned long long total = 1;
+  uint32_t seen = 0;
+  for (int i = 0; i < rank; ++i) {
+    if (dims[i] == 0 || total > (1ull << 40) / dims[i]) {
+      qfx_set_error("qfx_reorder_general: bad dimension");
+      return QFX_ERR_ARG;
+    }
+    total *= dims[i];
+    if (new_order[i] < 0 || new_order[i] >= rank || ((seen >> new_order[i]) & 1u)) {
+      qfx_set_error("qfx_reorder_general: new_order is not a permutation of the axes");
+      return QFX_ERR_ARG;
+    }
+    seen |= 1u << new_order[i];
+  }
+  if (src_off + total > ctx->arena_elems || dst_off + total > ctx->arena_elems) {
+    qfx_set_error("qfx_reorder_general: operand outside the arena");
+    return QFX_ERR_ARG;
+  }
+  if (src_off < dst_off + total && dst_off < src_off + total) {
+    qfx_set_error("qfx_reorder_general: source and destination overlap");
+    return QFX_ERR_ARG;
+  }
+  unsigned long long old_stride[QFX_MAX_RANK];
+  old_stride[rank - 1] = 1;
+  for (int i = rank - 1; i > 0; --i) old_stride[i - 1] = old_stride[i] * dims[i];
+  GeneralReorderArgs g{};
+  g.src = ctx->arena + src_off;
+  g.dst = ctx->arena + dst_off;
+  g.total = total;
+  g.rank = rank;
+  for (int j = 0; j < rank; ++j) {
+    g.new_dim[j] = dims[new_order[j]];
+    g.src_stride[j] = old_stride[new_order[j]];
+  }
+  const unsigned blocks = (unsigned)std::min<unsigned long long>((total + 255) / 256,
+                                                                 16ull * ctx->sm_count);
+  reorder_general_kernel<<<blocks, 256, 0, ctx->stream>>>(g);
+  QFX_CUDA(cudaGetLastError());
+  ctx->stats.launches_permute++;
+  ctx->stats.launches_total++;
+  ctx->stats.bytes += 16.0 * (double)total;
+  return QFX_OK;
+}

@@ -154,11 +154,14 @@ int choose_lanes(const Plan& plan, int n_devices) {
   if (arena_bytes > 2048.0 * 1048576.0) {
     lanes = 1;
     // larger arenas whose schedule is still a stream of small launches (cut-aware
-    // flatten of Sycamore m=16: ~2600 world-line steps per slice, 2e8 flop each):
-    // lanes as long as they fit in 64 GB together
+    // flatten of Sycamore m=16: ~150 launches per slice of ~1e10 flop, tens of
+    // microseconds each, with dependent launches back to back: 139 TFLOP/s on one
+    // lane, 157-159 on 2, 4 or 8): a few lanes as long as they fit in 64 GB together.
+    // The headline class (bristlecone_70 1-32-1, 7x7 1-32-1: ~8e10 flop per launch)
+    // fills the GPU from one lane.
     const double per_launch = plan.flops_per_pass / std::max<double>(1.0, (double)plan.steps.size());
-    if (per_launch < 1e9)
-      lanes = (int)std::min<double>(8.0, (65536.0 * 1048576.0) / arena_bytes);
+    if (per_launch < 3e10)
+      lanes = (int)std::min<double>(4.0, (65536.0 * 1048576.0) / arena_bytes);
   }
   lanes = (int)std::min<uint64_t>((uint64_t)std::max(lanes, 1), std::max<uint64_t>(1, slices / 2));
   // the memory limit bounds ALL scratch of the run (reference --memory,

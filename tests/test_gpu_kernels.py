@@ -468,3 +468,38 @@ def test_contract_small_k_long_m_and_n_output_ordered(ctx, m, n, k):
              b_n=sorted(int(x) for x in pb[:n]), b_k=[int(x) for x in pb[n:]], c_m=c_m, c_n=c_n)
     assert _run_contract(ctx, t, rng) < TOL
     assert _run_contract(ctx, _random_tables(rng, m, n, k), rng) < TOL
+
+
+@pytest.mark.parametrize("dims,order", [([3, 2, 5], [2, 0, 1]), ([2, 4, 3, 1], [3, 1, 0, 2]),
+                                        ([6, 7], [1, 0]), ([5, 1, 2, 3, 2], [4, 2, 0, 3, 1]),
+                                        ([3, 3, 3, 3], [0, 1, 2, 3]), ([12, 10, 9], [1, 2, 0]),
+                                        ([7, 33, 5, 64, 3], [3, 0, 4, 1, 2]), ([1], [0]),
+                                        ([2] * 12, [5, 0, 11, 3, 7, 1, 9, 2, 10, 4, 8, 6])])
+def test_reorder_general_dimensions(ctx, dims, order):
+    """qfx_reorder_general (Tensor::_naive_reorder, src/tensor.cpp:377-492): bit-exact
+    against the oracle's transpose (itself pinned to the reference in tests/test_oracle.py)."""
+    rng = np.random.default_rng(sum(dims) + len(dims))
+    total = int(np.prod(dims))
+    data = _rand(total, rng)
+    idx = ["a%d" % i for i in range(len(dims))]
+    want, _ = ko.reorder_named(data, idx, dims, [idx[p] for p in order])
+    ctx.reserve(2 * total + 64)
+    ctx.upload(3, data)
+    ctx.upload(total + 16, np.zeros(total, dtype=np.complex64))
+    ctx.reorder_general(3, total + 16, dims, order)
+    assert np.array_equal(ctx.download(total + 16, total), want)
+    assert np.array_equal(ctx.download(3, total), data)
+
+
+def test_reorder_general_rejects_bad_arguments(ctx):
+    ctx.reserve(1 << 12)
+    with pytest.raises(Exception, match="cannot be zero"):
+        ctx.reorder_general(0, 100, [], [])
+    with pytest.raises(Exception, match="permutation"):
+        ctx.reorder_general(0, 100, [3, 2], [0, 0])
+    with pytest.raises(Exception, match="overlap"):
+        ctx.reorder_general(0, 5, [3, 2], [1, 0])
+    with pytest.raises(Exception, match="outside the arena"):
+        ctx.reorder_general(0, 1 << 39, [1 << 20, 1 << 19], [1, 0])  # (a parked arena may be larger than asked)
+    with pytest.raises(Exception, match="bad dimension"):
+        ctx.reorder_general(0, 100, [3, 0], [1, 0])

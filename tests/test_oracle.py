@@ -75,3 +75,27 @@ def test_oracle_permute_matches_reference_reorder(nbits, seed):
     assert np.array_equal(got, want)
     named, _ = ko.reorder_named(data, idx, dims, new_idx)
     assert np.array_equal(named, want)
+
+
+GENERAL_REORDERS = [([3, 2, 5], [2, 0, 1]), ([2, 4, 3, 1], [3, 1, 0, 2]), ([6, 7], [1, 0]),
+                    ([5, 1, 2, 3, 2], [4, 2, 0, 3, 1]), ([3, 3, 3, 3], [0, 1, 2, 3]),
+                    ([4, 3, 256], [1, 2, 0]), ([3, 1024], [1, 0])]
+
+
+@pytest.mark.skipif(not support.reference_available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("dims,order", GENERAL_REORDERS)
+def test_oracle_reorder_general_dimensions_matches_reference(dims, order):
+    """Non-power-of-two dimensions take Tensor::_naive_reorder in the reference
+    (src/tensor.cpp:377-492); the oracle's transpose is pinned to it here, and the CUDA
+    qfx_reorder_general to the oracle in tests/test_gpu_kernels.py.  Sizes are <= 1024
+    or multiples of 1024: the reference walks the tensor in blocks of MAX_RIGHT_DIM = 1024
+    and copies a full block even when fewer elements remain (src/tensor.cpp:474-478), so
+    e.g. {12, 10, 9} reads past its scratch and is not a usable golden."""
+    rng = np.random.default_rng(sum(dims))
+    idx = ["a%d" % i for i in range(len(dims))]
+    new_idx = [idx[p] for p in order]
+    data = _rand(int(np.prod(dims)), rng)
+    want = support.reference_reorder(data, idx, dims, new_idx)
+    got, new_dims = ko.reorder_named(data, idx, dims, new_idx)
+    assert new_dims == [dims[p] for p in order]
+    assert np.array_equal(got, want)
