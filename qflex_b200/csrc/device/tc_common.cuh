@@ -66,12 +66,13 @@ struct FusedArgs {
                       // tiles run group by group, m-major inside, so a group's B' slab stays in L2
   int dual;           // tc_pair, K = 16: a stage carries TWO m tiles (m bit 7 rides as a fifth k bit
                       // of the A tile: columns 32..63 of the bf16 row); two accumulators per stage
+  int dual_epi;       // tc_pair dual: epilogue warps 0-3 / 4-7 drain accumulator 0 / 1, a whole row per thread
   int stagger_ns;     // tc_pair: start delay per pair index (tuning experiment)
   int blocked;        // tc_pair: each pair owns a contiguous range of tiles (else interleaved)
   int one_arrive;     // tc_pair: one barrier arrive per CTA (not per warp) for "A converted" / "accumulator drained"
   int ksplit;         // tc_fused split-K: work items = tiles * ksplit, kblocks = k blocks per item
   float2* part;       // split-K partial results [ksplit][M][N] (natural layout)
-  int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads (timing experiments)
+  int dbg;            // QFLEX_FUSED_DBG: 1 no convert, 2 no C stores, 4 no MMA, 8 no TMEM loads, 64 no A loads (timing experiments)
   int8_t c_m[QFX_MAX_BITS], c_n[QFX_MAX_BITS];
   // Compensation of the tensor core's accumulation bias (tc_debias_scale below): what
   // is read from a TMEM accumulator is multiplied by scale_full (an accumulator that

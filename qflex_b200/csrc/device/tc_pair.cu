@@ -161,7 +161,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
     }
     for (int s = 0; s < MAX_ACC; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), g.one_arrive ? 2 : 2 * 8);
+      mbar_init(tempty_bar(s), g.one_arrive ? 2 : (g.dual_epi ? 2 * 4 : 2 * 8));
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -202,9 +202,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
                                                            : 0u);
           if (lane == 0) {
             mbar_wait_spin(a_empty(stage), phase ^ 1u);
-            mbar_expect_tx(a_full(stage), g.a32_bytes);
-            tma_load_a(&tmA, g.a_rank, a_full(stage), a32_base + (uint32_t)stage * g.a32_bytes,
-                       (int)off16);
+            if (g.dbg & 64) {  // timing experiment: handshakes only, no A traffic
+              mbar_arrive(a_full(stage));
+            } else {
+              mbar_expect_tx(a_full(stage), g.a32_bytes);
+              tma_load_a(&tmA, g.a_rank, a_full(stage), a32_base + (uint32_t)stage * g.a32_bytes,
+                         (int)off16);
+            }
           }
           if (++stage == g.sa) {
             stage = 0;
@@ -460,6 +464,72 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
       for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
     }
+    if (STORE == 0 && g.dual_epi) {
+      // K = 16 (dual stages): the two accumulators of a stage are two m tiles that become
+      // ready together.  The kernel is bound by the epilogue's per-accumulator round trip
+      // (wait, TMEM load, release, ~1300 clocks of mostly fixed cost for 16 floats per
+      // thread; profiles/pair_skeleton_r2z*.log: with every load, MMA and store disabled
+      // the handshakes alone take 0.70 of the 0.88 ms).  So warps 0-3 drain accumulator
+      // 0 and warps 4-7 accumulator 1, each thread a WHOLE row (bn floats): one round
+      // trip per warp and stage instead of two.
+      const int h = half;
+      const int np = bn >> 4;
+      const float scale = g.scale_full;
+      for (int t = t_begin; t < t_end; t += t_step) {
+        const unsigned long long mtile = (2ull * (unsigned long long)t + rank) * 2 + (unsigned)h;
+        const unsigned long long m = mtile * BM + m_local;
+        unsigned long long row_off = 0;
+        if (g.c_natural) {
+          row_off = m * N;
+        } else {
+          for (int q = 0; q < g.m_bits; ++q) row_off |= ((m >> q) & 1ull) << g.c_m[q];
+        }
+        const int acc = set * 2 + h;
+        float sum[8][16];
+        mbar_wait_spin(tfull_bar(set * 2 + 1), set_phase);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(lane_group * 32) << 16) + (uint32_t)(acc * bn);
+#pragma unroll
+        for (int p = 0; p < 8; ++p)
+          if (p < np && !(g.dbg & 8)) tmem_ld16_async(t_row + (uint32_t)(p * 16), sum[p]);
+        tmem_wait_ld();
+#pragma unroll
+        for (int p = 0; p < 8; ++p)
+          if (p < np && !(g.dbg & 8)) tmem_reg_fence(sum[p]);
+#pragma unroll
+        for (int p = 0; p < 8; ++p)
+          if (p < np) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) sum[p][j] *= scale;
+          }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          if (p < np && !(g.dbg & 2)) {
+            const unsigned long long n0 = (unsigned long long)(p * 8);
+            if (g.c_natural) {
+              float* dst = reinterpret_cast<float*>(g.C + row_off + n0);
+              stg256(dst, &sum[p][0]);
+              stg256(dst + 8, &sum[p][8]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const unsigned long long n = n0 + j;
+                unsigned long long co = 0;
+                for (int q = 0; q < g.n_bits; ++q) co |= ((n >> q) & 1ull) << g.c_n[q];
+                g.C[row_off + co] = make_float2(sum[p][2 * j], sum[p][2 * j + 1]);
+              }
+            }
+          }
+        }
+        if (++set == g.acc_stages) {
+          set = 0;
+          set_phase ^= 1u;
+        }
+      }
+    } else
     for (int t = t_begin; t < t_end; t += t_step) {
       for (int sub = 0; sub < subs; ++sub) {
         // dual: the two accumulators are two m tiles; else the n tiles of one m tile
@@ -754,6 +824,11 @@ static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2*
     attr.mark(ctx->device);
   }
   const int grid = 2 * std::min(g.tiles, n_pairs);
+  static const bool dual_epi_off = [] {
+    const char* e = getenv("QFLEX_PAIR_DUAL_EPI");
+    return e != nullptr && atoi(e) == 0;
+  }();
+  g.dual_epi = (g.dual && !g.one_arrive && !dual_epi_off && pick_store_mode(g, C) == 0) ? 1 : 0;
   switch (pick_store_mode(g, C)) {
     case 1: tc_pair_bf16x3<1><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
     case 2: tc_pair_bf16x3<2><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;

@@ -178,6 +178,27 @@ def test_pair_kernel_scattered_c_and_repeatability(ctx):
     assert ctx.stats()["launches_gemm_tc_pair"] == before + 2
 
 
+@pytest.mark.parametrize("m,n,k,groups,c_layout", [
+    (17, 5, 4, None, "natural"), (17, 6, 4, (1,), "natural"), (18, 4, 4, (2,), "natural"),
+    (17, 4, 4, (1,), "scattered"), (17, 6, 4, None, "scattered"), (17, 5, 4, (3,), "n_high_m_low"),
+])
+def test_pair_kernel_dual_stage_epilogue(ctx, m, n, k, groups, c_layout):
+    """K = 16 (dual stages): epilogue warps 0-3 / 4-7 drain the stage's two accumulators,
+    one whole C row per thread (16, 32 and 64 complex columns), natural and scattered C."""
+    rng = np.random.default_rng(52000 + 100 * m + 10 * n + k + len(c_layout))
+    t = _natural(m, n, k) if groups is None else _grouped(m, n, k, groups)
+    if c_layout == "scattered":
+        pc = [int(x) for x in rng.permutation(m + n)]
+        t["c_m"], t["c_n"] = pc[:m], pc[m:]
+    elif c_layout == "n_high_m_low":  # n bits above bit 5: C address bits 0, 1 are not lane rows
+        t["c_n"] = list(range(m, m + n))
+        t["c_m"] = [int(x) for x in rng.permutation(m)]
+    before = ctx.stats()["launches_gemm_tc_pair"]
+    err, used = _run(ctx, t, rng)
+    assert err < TOL_TC
+    assert ctx.stats()["launches_gemm_tc_pair"] == before + 1
+
+
 # ---- split-K in tc_fused.cu: few output tiles, long K (the final merges)
 @pytest.mark.parametrize("m,n,k,scatter", [(10, 8, 12, False), (9, 6, 13, True), (8, 8, 14, False),
                                            (12, 8, 12, True)])

@@ -1,0 +1,9 @@
+cd $GRAFT_REPO_ROOT; mkdir -p gpurun_out
+export QFLEX_KB_NOPERM=1
+timeout 900 python -m pytest tests/test_gpu_tensorcore.py tests/test_zz_no_alloc.py -m gpu -q -x 2>&1 | tail -4
+{
+for e in 1 0; do echo "dual_epi=$e"; QFLEX_PAIR_DUAL_EPI=$e timeout 120 python tools/kernel_bench.py 24,4,4 22,4,4 20,4,4 20,5,4 20,6,4 2>&1 | grep -E '"gemm"|"mixed"'; done
+echo "skeleton dual_epi"; QFLEX_FUSED_DBG=79 timeout 120 python tools/kernel_bench.py 24,4,4 2>&1 | grep -E '"gemm"'
+for d in 1 2 4 8 15; do echo "dbg=$d"; QFLEX_FUSED_DBG=$d timeout 120 python tools/kernel_bench.py 24,4,4 2>&1 | grep -E '"gemm"'; done
+} > gpurun_out/r2z4_sweep.log 2>&1
+cat gpurun_out/r2z4_sweep.log
