@@ -480,13 +480,20 @@ def main():
     lib.evaluate(c, o, g, memory_limit=w["memory"], device=local_rank, rank=rank, world=world,
                  precision=args.precision)  # warm-up (allocator, module load)
     barrier()
+    e2e_sampler = ClockSampler(local_rank)
+    if rank == 0:
+        e2e_sampler.start()
+    e2e_calls_ms = []
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
+        t_call = time.perf_counter()
         res, st = lib.evaluate(c, o, g, memory_limit=w["memory"], device=local_rank, rank=rank,
                                world=world, precision=args.precision)
         full = reducer.allreduce(np.array([a for _, a in res]))
+        e2e_calls_ms.append(round(1e3 * (time.perf_counter() - t_call), 1))
     barrier()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
+    e2e_clocks = e2e_sampler.stop() if rank == 0 else None
     e2e_value = st["flops_job"] * e2e_steps / e2e_wall / 1e12
     # the same call with the plan memory off (every call parses AND plans from scratch;
     # above, calls after the first recall the plan of the identical previous call)
@@ -608,6 +615,7 @@ def main():
         "e2e": dict({"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d,
                      "d2h_bytes_per_step": 16 * n_amps, "steps": e2e_steps,
                      "ms_per_step": 1e3 * e2e_wall / e2e_steps,
+                     "ms_per_call_rank0": e2e_calls_ms, "clocks": e2e_clocks,
                      "plan_memory": "on: calls after the first recall the plan of the identical "
                                     "previous call (parse, upload, flatten, contract still run)",
                      "ms_per_step_planning_every_call": e2e_cold_ms,

@@ -66,6 +66,7 @@ struct FusedArgs {
                       // tiles run group by group, m-major inside, so a group's B' slab stays in L2
   int dual;           // tc_pair, K = 16: a stage carries TWO m tiles (m bit 7 rides as a fifth k bit
                       // of the A tile: columns 32..63 of the bf16 row); two accumulators per stage
+  int lag;            // tc_pair, two n tiles: n tile 1 runs one k block behind n tile 0 (sc >= 3)
   int dual_epi;       // tc_pair dual: epilogue warps 0-3 / 4-7 drain accumulator 0 / 1, a whole row per thread
   int stagger_ns;     // tc_pair: start delay per pair index (tuning experiment)
   int blocked;        // tc_pair: each pair owns a contiguous range of tiles (else interleaved)

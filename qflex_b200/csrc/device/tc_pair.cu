@@ -22,6 +22,8 @@
 // the peer (converters: A ready; B producer: expect_tx + TMA complete_tx;
 // epilogue: accumulator drained); barriers that release buffers are signalled
 // in both CTAs by a multicast tcgen05.commit.
+#include <cstdio>
+
 #include "tc_common.cuh"
 
 namespace {
@@ -93,6 +95,19 @@ __device__ __forceinline__ void umma2_commit(uint32_t bar) {
       ::"r"(bar), "h"((uint16_t)3)
       : "memory");
 }
+
+// timing experiment (QFLEX_FUSED_DBG & 256): clocks the MMA issuer of pair 0 spends in
+// each of its waits (lagged schedule only), written to g.part
+#define MMA_TIMED(slot, stmt)                 \
+  do {                                        \
+    if (prof) {                               \
+      const long long t0_ = clock64();        \
+      stmt;                                   \
+      wt[slot] += clock64() - t0_;            \
+    } else {                                  \
+      stmt;                                   \
+    }                                         \
+  } while (0)
 
 // FusedArgs fields as in tc_fused.cu, except: tiles = number of 256-row pair
 // tiles, b_slot_bytes = bn/2 * 128 (this CTA's half), acc_stages = number of
@@ -222,23 +237,31 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       int slot = 0;
       uint32_t phase = 0;
       const int half_rows = bn >> 1;
+      auto load_b = [&](int kb, int nt) {
+#pragma unroll
+        for (int part = 0; part < 2; ++part) {
+          if (!g.b_resident) mbar_wait_spin(b_empty(slot), phase ^ 1u);
+          mbar_expect_tx_leader(b_full(slot), g.b_slot_bytes);
+          tma_load_2d_pair(part == 0 ? &tmBm : &tmBh, b_full(slot),
+                           b_base + (uint32_t)slot * g.b_slot_bytes, kb * BK,
+                           nt * bn + (int)rank * half_rows);
+          if (++slot == g.sb) {
+            slot = 0;
+            phase ^= 1u;
+          }
+        }
+      };
       for (int t = t_begin; t < t_end; t += t_step) {
         if (g.b_resident && t != t_begin) break;
-        for (int kb = 0; kb < g.kblocks; ++kb) {
-          for (int nt = 0; nt < g.tiles_n; ++nt) {
-#pragma unroll
-            for (int part = 0; part < 2; ++part) {
-              if (!g.b_resident) mbar_wait_spin(b_empty(slot), phase ^ 1u);
-              mbar_expect_tx_leader(b_full(slot), g.b_slot_bytes);
-              tma_load_2d_pair(part == 0 ? &tmBm : &tmBh, b_full(slot),
-                               b_base + (uint32_t)slot * g.b_slot_bytes, kb * BK,
-                               nt * bn + (int)rank * half_rows);
-              if (++slot == g.sb) {
-                slot = 0;
-                phase ^= 1u;
-              }
-            }
+        if (g.lag) {  // same order as the MMA issuer's lagged schedule (below)
+          for (int kb = 0; kb < g.kblocks; ++kb) {
+            load_b(kb, 0);
+            if (kb >= 1) load_b(kb - 1, 1);
           }
+          load_b(g.kblocks - 1, 1);
+        } else {
+          for (int kb = 0; kb < g.kblocks; ++kb)
+            for (int nt = 0; nt < g.tiles_n; ++nt) load_b(kb, nt);
         }
       }
     } else if (warp == 1 && rank == 0) {
@@ -287,6 +310,82 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
             set = 0;
             set_phase ^= 1u;
           }
+        }
+      } else if (g.lag) {
+        // Two n tiles (N' = 512: the whole TMEM): both accumulators used to complete
+        // within one sub-step (12 MMAs, ~1500 clocks) of each other at the end of a tile,
+        // and the next tile's first MMAs then waited for the drains -- ~3300 clocks of
+        // TMEM reads per accumulator plus the stores of the first before the second is
+        // touched: ~8100 of a tile's ~32900 clocks (tools: QFLEX_FUSED_DBG=256 runs,
+        // profiles/pair_skeleton_r2z2.log).  Here n tile 1 runs ONE k block behind n
+        // tile 0 and catches up at the end of the tile, so that accumulator 0 is
+        // drained behind the last two sub-steps of n tile 1, and accumulator 1 behind
+        // the first two of the next tile's n tile 0.  An A' stage lives one step longer
+        // (released after n tile 1's use): sc >= 3.
+        int csb = 0;  // stage of n tile 1's k block (already waited for by n tile 0)
+        const bool prof = (g.dbg & 256) && blockIdx.x == 0;
+        long long wt[4] = {0, 0, 0, 0};
+        const long long role_t0 = clock64();
+        auto sub_step = [&](int kb, int nt, int stage, bool last_use) {
+          const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)stage * 2 * A16_TILE);
+          const uint64_t dAm = dAh + (uint64_t)(A16_TILE >> 4);
+          const int acc = set * 2 + nt;
+          if (kb == 0) MMA_TIMED(nt, mbar_wait_cluster(tempty_bar(acc), set_phase ^ 1u));
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
+          const uint32_t first_acc = kb == 0 ? 0u : 1u;
+          const uint64_t dBm = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
+          MMA_TIMED(2, mbar_wait_cluster(b_full(bs), bph));
+          tc_fence_after();
+          if (leader) {
+            for (int kk = 0; kk < nkk; ++kk)
+              umma2_bf16(d_tmem, dAh + 2 * kk, dBm + 2 * kk, idesc, kk == 0 ? first_acc : 1u);
+            if (!g.b_resident) umma2_commit(b_empty(bs));
+          }
+          if (++bs == g.sb) {
+            bs = 0;
+            bph ^= g.b_resident ? 0u : 1u;
+          }
+          const uint64_t dBh = smem_desc_sw128(b_base + (uint32_t)bs * g.b_slot_bytes);
+          MMA_TIMED(2, mbar_wait_cluster(b_full(bs), bph));
+          tc_fence_after();
+          if (leader) {
+            for (int kk = 0; kk < nkk; ++kk)
+              umma2_bf16(d_tmem, dAm + 2 * kk, dBh + 2 * kk, idesc, 1u);
+            for (int kk = 0; kk < nkk; ++kk)
+              umma2_bf16(d_tmem, dAh + 2 * kk, dBh + 2 * kk, idesc, 1u);
+            if (!g.b_resident) umma2_commit(b_empty(bs));
+            if (last_use) umma2_commit(c_empty(stage));
+            if (kb == g.kblocks - 1) umma2_commit(tfull_bar(acc));
+          }
+          if (++bs == g.sb) {
+            bs = 0;
+            bph ^= g.b_resident ? 0u : 1u;
+          }
+        };
+        for (int t = t_begin; t < t_end; t += t_step) {
+          for (int kb = 0; kb < g.kblocks; ++kb) {
+            MMA_TIMED(3, mbar_wait_cluster(c_full(cs), cph));
+            sub_step(kb, 0, cs, false);
+            if (++cs == g.sc) {
+              cs = 0;
+              cph ^= 1u;
+            }
+            if (kb >= 1) {
+              sub_step(kb - 1, 1, csb, true);
+              if (++csb == g.sc) csb = 0;
+            }
+          }
+          sub_step(g.kblocks - 1, 1, csb, true);
+          if (++csb == g.sc) csb = 0;
+          if (++set == g.acc_stages) {
+            set = 0;
+            set_phase ^= 1u;
+          }
+        }
+        if (prof && lane == 0) {
+          long long* out = reinterpret_cast<long long*>(g.part);
+          out[0] = clock64() - role_t0;
+          for (int i = 0; i < 4; ++i) out[1 + i] = wt[i];
         }
       } else
       for (int t = t_begin; t < t_end; t += t_step) {
@@ -496,15 +595,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
         for (int p = 0; p < 8; ++p)
           if (p < np && !(g.dbg & 8)) tmem_reg_fence(sum[p]);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
 #pragma unroll
         for (int p = 0; p < 8; ++p)
           if (p < np) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) sum[p][j] *= scale;
           }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
           if (p < np && !(g.dbg & 2)) {
@@ -557,15 +656,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
         for (int p = 0; p < 8; ++p)
           if (p < npieces && !(g.dbg & 8)) tmem_reg_fence(sum[p]);
-        {
-          const float scale = g.scale_full;  // accumulation-bias compensation
-#pragma unroll
-          for (int p = 0; p < 8; ++p)
-            if (p < npieces) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) sum[p][j] *= scale;
-            }
-        }
         tc_fence_before();
         if (g.one_arrive) {
           asm volatile("bar.sync 2, %0;" ::"n"(8 * 32) : "memory");
@@ -573,6 +663,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         } else {
           __syncwarp();
           if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+        }
+        {
+          // accumulation-bias compensation: registers only, so AFTER the accumulator is
+          // released (the MMA issuer waits for that release at the start of a tile)
+          const float scale = g.scale_full;
+#pragma unroll
+          for (int p = 0; p < 8; ++p)
+            if (p < npieces) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) sum[p][j] *= scale;
+            }
         }
         if (STORE == 2 && t_stores) {
           const unsigned long long mb = mtile * BM + m_local_b;
@@ -754,7 +855,14 @@ static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2*
   const int fixed = SMEM_FIXED;
   const int slot = (int)g.b_slot_bytes, a32 = (int)g.a32_bytes, a16 = 2 * A16_TILE;
   const int slots_per_kb = 2 * g.tiles_n;
-  g.sc = 2;
+  static const int lag_env = [] {
+    const char* e = getenv("QFLEX_PAIR_LAG");
+    return e ? atoi(e) : 1;
+  }();
+  // (only when the two accumulators fill TMEM: with N' = 256 there are two accumulator
+  // sets and the lag only costs B' slots -- 2^20 x 128 x 256: 0.51 -> 0.60 ms)
+  g.lag = (lag_env != 0 && !g.dual && g.tiles_n == 2 && g.acc_stages == 1 && g.kblocks >= 2) ? 1 : 0;
+  g.sc = g.lag ? 3 : 2;
   g.sa = 2;
   g.sb = slots_per_kb;
   g.b_resident = (slots_per_kb * g.kblocks <= MAX_SB) ? 1 : 0;
@@ -765,6 +873,10 @@ static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2*
     g.sb = slots_per_kb;
   }
   if (g.dual && !g.b_resident) return QFX_OK;  // (cannot happen: 2 slots of <= 8 KB)
+  if (g.lag && (g.sb > MAX_SB || total() > SMEM_LIMIT)) {  // no room for the third A' stage
+    g.lag = 0;
+    g.sc = 2;
+  }
   if (g.sb > MAX_SB || total() > SMEM_LIMIT) return QFX_OK;
   for (bool grew = true; grew;) {
     grew = false;
@@ -829,12 +941,25 @@ static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2*
     return e != nullptr && atoi(e) == 0;
   }();
   g.dual_epi = (g.dual && !g.one_arrive && !dual_epi_off && pick_store_mode(g, C) == 0) ? 1 : 0;
+  static long long* prof_buf = nullptr;  // timing experiment only (QFLEX_FUSED_DBG & 256)
+  if (g.dbg & 256) {
+    if (prof_buf == nullptr) QFX_CUDA(cudaMalloc(&prof_buf, 8 * sizeof(long long)));
+    QFX_CUDA(cudaMemsetAsync(prof_buf, 0, 8 * sizeof(long long), ctx->stream));
+    g.part = reinterpret_cast<float2*>(prof_buf);
+  }
   switch (pick_store_mode(g, C)) {
     case 1: tc_pair_bf16x3<1><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
     case 2: tc_pair_bf16x3<2><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
     default: tc_pair_bf16x3<0><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
   }
   QFX_CUDA(cudaGetLastError());
+  if ((g.dbg & 256) && g.lag) {
+    long long h[8];
+    QFX_CUDA(cudaStreamSynchronize(ctx->stream));
+    QFX_CUDA(cudaMemcpy(h, prof_buf, sizeof(h), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "pair-prof MMA issuer: %lld clk; waits: accumulator 0 %lld, accumulator 1 %lld, "
+            "B slots %lld, A stage %lld\n", h[0], h[1], h[2], h[3], h[4]);
+  }
   ctx->stats.launches_gemm_tc++;
   ctx->stats.launches_gemm_tc_fused++;
   ctx->stats.launches_gemm_tc_pair++;

@@ -1,8 +1,8 @@
 #!/bin/bash
 # ncu launch list of the bench command (gpu__time_duration per launch, clocks untouched).
 # The first bench.py run (no ncu) must exit 0 before this is called.
-ncu --metrics gpu__time_duration.sum --clock-control none -c 7000 --csv \
-    --log-file gpurun_out/launches_full.csv python bench.py --workload bristlecone_70_1-32-1_weak --steps 1 --warmup 3 --no-cpu-baseline \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 20000 --csv \
+    --log-file gpurun_out/launches_full.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline \
     > gpurun_out/launches_bench.log 2>&1
 python - <<'PY'
 import csv, collections
@@ -20,8 +20,8 @@ for r in rows[1:]:
     a[0] += 1; a[1] += v
 tot = sum(a[1] for a in agg.values())
 with open("gpurun_out/launches_summary.txt", "w") as f:
-    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none: python bench.py --workload bristlecone_70_1-32-1_weak --steps 1 --warmup 3 --no-cpu-baseline\n")
-    f.write("# (8 slices per pass: prepare + flatten + 3 warm-up + 1 timed + 1 profiled pass + 6 e2e calls; per-launch times are cold-cache, serialised)\n")
+    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none -c 20000: python bench.py --steps 1 --warmup 1 --no-cpu-baseline\n")
+    f.write("# (default workload, 64 slices per pass, ~8000 launches per pass; the first 20000 launches = flatten + warm-up + timed + part of the profiled pass; per-launch times are cold-cache, serialised)\n")
     f.write("%-60s %8s %12s %7s\n" % ("kernel", "launches", "total_us", "share"))
     for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         f.write("%-60s %8d %12.1f %6.1f%%\n" % (k[:60], a[0], a[1], 100 * a[1] / tot))
