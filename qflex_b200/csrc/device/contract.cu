@@ -1029,6 +1029,8 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
     bool done = false;
     int rc = qfx_launch_contract_tc_pair(ctx, d, A, B, C, &done);
     if (rc || done) return rc;
+    rc = qfx_launch_contract_tc_pairlong(ctx, d, A, B, C, &done);
+    if (rc || done) return rc;
     rc = qfx_launch_contract_tc_fused(ctx, d, A, B, C, &done);
     if (rc || done) return rc;
     if (d.n_bits >= 5 && d.k_bits >= 5) return qfx_launch_contract_tc(ctx, d, A, B, C);

@@ -80,6 +80,8 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& d, const
 // tc_pair.cu (CTA-pair variant for k, n <= 8 bits and >= 74 256-row tiles; same contract)
 int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& d, const float2* A,
                                 const float2* B, float2* C, bool* done);
+int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& d, const float2* A,
+                                    const float2* B, float2* C, bool* done);
 // permute.cu
 int qfx_launch_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
                        int n_bits, const int8_t* dst_pos);

@@ -604,6 +604,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
             for (int j = 0; j < 16; ++j) sum[p][j] *= scale;
           }
+        if (g.c_natural && np >= 2 && !(g.dbg & 128)) {
+          // natural C: transpose inside every quad so that each store instruction
+          // writes full 128-byte lines (8 per warp) instead of 32 sectors in 32 lines
+          float* tile_c = reinterpret_cast<float*>(g.C + mtile * BM * N);
+#pragma unroll
+          for (int pp = 0; pp < 4; ++pp) {
+            if (2 * pp < np && !(g.dbg & 2)) {
+              quad_transpose(sum[2 * pp], sum[2 * pp + 1], lane);
+              float* dst = tile_c + 8 * (lane & 3) + pp * 32;
+              stg256(dst + 2ull * mq[0] * N, &sum[2 * pp][0]);
+              stg256(dst + 2ull * mq[1] * N, &sum[2 * pp][8]);
+              stg256(dst + 2ull * mq[2] * N, &sum[2 * pp + 1][0]);
+              stg256(dst + 2ull * mq[3] * N, &sum[2 * pp + 1][8]);
+            }
+          }
+        } else
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
           if (p < np && !(g.dbg & 2)) {

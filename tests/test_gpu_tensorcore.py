@@ -199,6 +199,31 @@ def test_pair_kernel_dual_stage_epilogue(ctx, m, n, k, groups, c_layout):
     assert ctx.stats()["launches_gemm_tc_pair"] == before + 1
 
 
+# ---- CTA-pair kernel for long K / wide N (tc_pairlong.cu): k > 8 bits or n > 8 bits and
+# at least two waves of 256-row work items
+@pytest.mark.parametrize("m,n,k,groups,c_layout", [
+    (14, 9, 9, None, "natural"),        # 4 n tiles, 16 k blocks (4 chunks)
+    (15, 8, 10, (0, 2, 4), "natural"),  # 2 n tiles, 32 k blocks, grouped A layout
+    (16, 6, 9, None, "natural"),        # one n tile of 128 columns: 4 accumulator stages
+    (14, 12, 5, None, "natural"),       # wide N, one k block
+    (15, 9, 6, (1, 3), "scattered"),    # k blocks = 2 < chunk
+    (14, 10, 9, None, "transposed"),
+    (16, 9, 11, None, "natural"),       # 64 k blocks: the bias compensation of 16 chunks
+])
+def test_pair_kernel_long_k_wide_n(ctx, m, n, k, groups, c_layout):
+    rng = np.random.default_rng(61000 + 100 * m + 10 * n + k)
+    t = _natural(m, n, k) if groups is None else _grouped(m, n, k, groups)
+    if c_layout == "scattered":
+        pc = [int(x) for x in rng.permutation(m + n)]
+        t["c_m"], t["c_n"] = pc[:m], pc[m:]
+    elif c_layout == "transposed":
+        t["c_m"], t["c_n"] = list(range(m)), list(range(m, m + n))
+    before = ctx.stats()["launches_gemm_tc_pair"]
+    err, used = _run(ctx, t, rng)
+    assert err < TOL_TC
+    assert ctx.stats()["launches_gemm_tc_pair"] == before + 1, used
+
+
 # ---- split-K in tc_fused.cu: few output tiles, long K (the final merges)
 @pytest.mark.parametrize("m,n,k,scatter", [(10, 8, 12, False), (9, 6, 13, True), (8, 8, 14, False),
                                            (12, 8, 12, True)])
