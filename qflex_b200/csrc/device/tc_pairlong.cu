@@ -484,7 +484,11 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
   }();
   if (!enabled) return QFX_OK;
   qfx_contract_desc d = din;
-  if (d.m_bits < 8 || d.n_bits < 4 || d.k_bits < 5) return QFX_OK;
+  static const int min_k_bits = [] {
+    const char* e = getenv("QFLEX_TC_PAIRLONG_MINK");
+    return e ? atoi(e) : 5;  // K = 16: 2^16 x 2^12 x 16 gains 6 %, 2^18 x 512 x 16 and
+  }();                       // 2^20 x 1024 x 16 lose 2-4 % against tc_fused: left there
+  if (d.m_bits < 8 || d.n_bits < 4 || d.k_bits < std::max(4, min_k_bits)) return QFX_OK;
   if (d.n_bits <= 8 && d.k_bits <= 8) return QFX_OK;
   {
     std::vector<int> idx(d.k_bits);
@@ -505,7 +509,7 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
   g.tiles_n = (int)((2 * N) / g.bn);
   g.tiles = (int)((M / (2 * BM)) * g.tiles_n);
   if (g.tiles < 2 * n_pairs) return QFX_OK;
-  g.kb_bits = 5;
+  g.kb_bits = std::min(5, (int)d.k_bits);
   g.tile_bits = 7 + g.kb_bits;
   uint64_t span = 0;
   for (int i = 0; i < d.m_bits; ++i) span |= 1ull << d.a_m[i];
@@ -518,8 +522,8 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
   g.ksplit = 1;
   g.m_bits = d.m_bits;
   g.n_bits = d.n_bits;
-  g.kblocks = (int)((2 * K) / BK);
-  g.nkk = 4;
+  g.kblocks = (int)std::max<uint64_t>(1, (2 * K) / BK);
+  g.nkk = (int)std::min<uint64_t>(4, (2 * K) / 16);
   g.chunk = ctx->tc_chunk > 0 ? ctx->tc_chunk : 4;
   g.nchunks = (g.kblocks + g.chunk - 1) / g.chunk;
   {
