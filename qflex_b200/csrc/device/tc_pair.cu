@@ -958,6 +958,7 @@ static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2*
   }();
   g.dual_epi = (g.dual && !g.one_arrive && !dual_epi_off && pick_store_mode(g, C) == 0) ? 1 : 0;
   static long long* prof_buf = nullptr;  // timing experiment only (QFLEX_FUSED_DBG & 256)
+  if (scratch != nullptr) g.dbg &= ~256;  // (the no-allocation entry point never allocates)
   if (g.dbg & 256) {
     if (prof_buf == nullptr) QFX_CUDA(cudaMalloc(&prof_buf, 8 * sizeof(long long)));
     QFX_CUDA(cudaMemsetAsync(prof_buf, 0, 8 * sizeof(long long), ctx->stream));
