@@ -1027,9 +1027,10 @@ int qfx_launch_contract(qfx_ctx* ctx, const qfx_contract_desc* din,
   // ---------------- compute-bound classes: tcgen05 split-bf16 path
   if (!accumulate_amp && d.precision != QFX_PREC_FFMA && qfx_tc_eligible(d)) {
     bool done = false;
-    int rc = qfx_launch_contract_tc_pair(ctx, d, A, B, C, &done);
+    // (tc_pairlong first: it declines what tc_pair does better)
+    int rc = qfx_launch_contract_tc_pairlong(ctx, d, A, B, C, &done);
     if (rc || done) return rc;
-    rc = qfx_launch_contract_tc_pairlong(ctx, d, A, B, C, &done);
+    rc = qfx_launch_contract_tc_pair(ctx, d, A, B, C, &done);
     if (rc || done) return rc;
     rc = qfx_launch_contract_tc_fused(ctx, d, A, B, C, &done);
     if (rc || done) return rc;

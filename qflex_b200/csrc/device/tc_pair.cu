@@ -280,13 +280,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
         const uint64_t dBh = smem_desc_sw128(b_base + g.b_slot_bytes);
         mbar_wait_cluster(b_full(0), 0u);
         mbar_wait_cluster(b_full(1), 0u);
+        const bool prof = (g.dbg & 256) && blockIdx.x == 0;
+        long long wt[4] = {0, 0, 0, 0};
+        const long long role_t0 = clock64();
         for (int t = t_begin; t < t_end; t += t_step) {
           const uint64_t dAh = smem_desc_sw128(a16_base + (uint32_t)cs * 2 * A16_TILE);
           const uint64_t dAm = dAh + (uint64_t)(A16_TILE >> 4);
-          mbar_wait_cluster(c_full(cs), cph);
+          MMA_TIMED(3, mbar_wait_cluster(c_full(cs), cph));
           for (int h = 0; h < 2; ++h) {
             const int acc = set * 2 + h;
-            mbar_wait_cluster(tempty_bar(acc), set_phase ^ 1u);
+            MMA_TIMED(h, mbar_wait_cluster(tempty_bar(acc), set_phase ^ 1u));
             const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
             tc_fence_after();
             if (leader) {
@@ -310,6 +313,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
             set = 0;
             set_phase ^= 1u;
           }
+        }
+        if (prof && lane == 0) {
+          long long* out = reinterpret_cast<long long*>(g.part);
+          out[0] = clock64() - role_t0;
+          for (int i = 0; i < 4; ++i) out[1 + i] = wt[i];
         }
       } else if (g.lag) {
         // Two n tiles (N' = 512: the whole TMEM): both accumulators used to complete
@@ -970,7 +978,7 @@ static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2*
     default: tc_pair_bf16x3<0><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
   }
   QFX_CUDA(cudaGetLastError());
-  if ((g.dbg & 256) && g.lag) {
+  if ((g.dbg & 256) && (g.lag || g.dual)) {
     long long h[8];
     QFX_CUDA(cudaStreamSynchronize(ctx->stream));
     QFX_CUDA(cudaMemcpy(h, prof_buf, sizeof(h), cudaMemcpyDeviceToHost));

@@ -16,6 +16,8 @@
 // groups whose B' slab stays in L2 (as tc_fused).  Barriers as in tc_pair.cu: what the
 // MMA warp waits on lives in the leader CTA and is arrived on remotely by the peer;
 // buffer releases are multicast tcgen05.commit.
+#include <cmath>
+
 #include "tc_common.cuh"
 
 namespace {
@@ -471,6 +473,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 
 }  // namespace
 
+// tc_pair.cu's tile is 256 rows x ALL of N' (up to 512 columns).  When the tiles are few
+// waves over the pairs and the last wave is mostly empty (2^16 x 256 x 256: 256 tiles over
+// 74 pairs = 3.46 waves, 4 are paid), the same contraction as (256 rows x 256 columns)
+// work items of this kernel wastes less: 512 items = 6.92 waves.
+static bool din_takes_pair_tail(const qfx_contract_desc& d, int n_pairs) {
+  static const int mode = [] {
+    const char* e = getenv("QFLEX_TC_PAIRLONG_TAIL");
+    return e ? atoi(e) : 1;
+  }();
+  if (mode == 0 || d.n_bits != 8 || d.k_bits < 5) return false;  // two n tiles of 256 columns
+  const double tiles = (double)(1ull << d.m_bits) / 256.0;
+  if (tiles < n_pairs || tiles > 8.0 * n_pairs) return false;
+  const double eff_pair = tiles / n_pairs / std::ceil(tiles / n_pairs);
+  const double eff_long = 2.0 * tiles / n_pairs / std::ceil(2.0 * tiles / n_pairs);
+  return mode == 2 || eff_long > eff_pair + 0.08;
+}
+
 // Roles already swapped (m_bits >= n_bits).  *done = false: not applicable (the caller
 // tries tc_fused next): shapes the pair kernel of tc_pair.cu takes (k, n <= 8 bits),
 // fewer than two waves of 256-row work items (tc_fused splits K for those), or an A
@@ -489,7 +508,8 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
     return e ? atoi(e) : 5;  // K = 16: 2^16 x 2^12 x 16 gains 6 %, 2^18 x 512 x 16 and
   }();                       // 2^20 x 1024 x 16 lose 2-4 % against tc_fused: left there
   if (d.m_bits < 8 || d.n_bits < 4 || d.k_bits < std::max(4, min_k_bits)) return QFX_OK;
-  if (d.n_bits <= 8 && d.k_bits <= 8) return QFX_OK;
+  const bool pair_shape = d.n_bits <= 8 && d.k_bits <= 8;  // what tc_pair.cu takes
+  if (pair_shape && !din_takes_pair_tail(d, ctx->sm_count / 2)) return QFX_OK;
   {
     std::vector<int> idx(d.k_bits);
     for (int i = 0; i < d.k_bits; ++i) idx[i] = i;
