@@ -133,6 +133,8 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1)
       // ---------------- B producer: B'_mid then B'_hi of every k block
       int slot = 0;
       uint32_t phase = 0;
+      // (programmatic dependent launch: B' comes from the split kernel launched before)
+      asm volatile("griddepcontrol.wait;" ::: "memory");
       for (int w = blockIdx.x; w < g.tiles * g.ksplit; w += gridDim.x) {
         const int t = w % g.tiles, kb0 = (w / g.tiles) * g.kblocks;
         int mt, nt;
@@ -640,10 +642,27 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
     attr.mark(ctx->device);
   }
   const int grid = std::min(g.tiles * g.ksplit, ctx->sm_count);
-  switch (pick_store_mode(g, C)) {
-    case 1: tc_fused_bf16x3<1><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
-    case 2: tc_fused_bf16x3<2><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
-    default: tc_fused_bf16x3<0><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  {
+    // programmatic dependent of the split kernel (see tc_pair.cu); QFLEX_PDL=0: plain launch
+    static const bool pdl = [] {
+      const char* e = getenv("QFLEX_PDL");
+      return e == nullptr || atoi(e) != 0;
+    }();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(FUSED_THREADS);
+    cfg.dynamicSmemBytes = (size_t)smem_bytes;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attrs[1];
+    attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = pdl ? 1 : 0;
+    switch (pick_store_mode(g, C)) {
+      case 1: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_fused_bf16x3<1>, mA, mBh, mBm, g)); break;
+      case 2: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_fused_bf16x3<2>, mA, mBh, mBm, g)); break;
+      default: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_fused_bf16x3<0>, mA, mBh, mBm, g));
+    }
   }
   QFX_CUDA(cudaGetLastError());
   if (ksplit > 1) {

@@ -237,6 +237,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       int slot = 0;
       uint32_t phase = 0;
       const int half_rows = bn >> 1;
+      // B' is written by the split kernel launched just before this one; with a
+      // programmatic dependent launch this kernel may have started before that one
+      // finished (returns at once otherwise)
+      asm volatile("griddepcontrol.wait;" ::: "memory");
       auto load_b = [&](int kb, int nt) {
 #pragma unroll
         for (int part = 0; part < 2; ++part) {
@@ -972,10 +976,28 @@ static int launch_pair(qfx_ctx* ctx, const qfx_contract_desc& din, const float2*
     QFX_CUDA(cudaMemsetAsync(prof_buf, 0, 8 * sizeof(long long), ctx->stream));
     g.part = reinterpret_cast<float2*>(prof_buf);
   }
-  switch (pick_store_mode(g, C)) {
-    case 1: tc_pair_bf16x3<1><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
-    case 2: tc_pair_bf16x3<2><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
-    default: tc_pair_bf16x3<0><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  {
+    // launched as a programmatic dependent of the split kernel: the prologue and the
+    // first A loads overlap the split's tail and the launch latency (QFLEX_PDL=0: plain)
+    static const bool pdl = [] {
+      const char* e = getenv("QFLEX_PDL");
+      return e == nullptr || atoi(e) != 0;
+    }();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(FUSED_THREADS);
+    cfg.dynamicSmemBytes = (size_t)smem_bytes;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attrs[1];
+    attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = pdl ? 1 : 0;
+    switch (pick_store_mode(g, C)) {
+      case 1: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_pair_bf16x3<1>, mA, mBh, mBm, g)); break;
+      case 2: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_pair_bf16x3<2>, mA, mBh, mBm, g)); break;
+      default: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_pair_bf16x3<0>, mA, mBh, mBm, g));
+    }
   }
   QFX_CUDA(cudaGetLastError());
   if ((g.dbg & 256) && (g.lag || g.dual)) {

@@ -189,6 +189,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       int slot = 0;
       uint32_t phase = 0;
       const int half_rows = bn >> 1;
+      // (programmatic dependent launch: B' comes from the split kernel launched before)
+      asm volatile("griddepcontrol.wait;" ::: "memory");
       for (int w = pair0; w < g.tiles; w += pair_step) {
         int mt, nt;
         decode_item(g, w, &mt, &nt);
@@ -622,10 +624,27 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
     attr.mark(ctx->device);
   }
   const int grid = 2 * std::min(g.tiles, n_pairs);
-  switch (pick_store_mode(g, C)) {
-    case 1: tc_pairlong_bf16x3<1><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
-    case 2: tc_pairlong_bf16x3<2><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g); break;
-    default: tc_pairlong_bf16x3<0><<<grid, FUSED_THREADS, smem_bytes, ctx->stream>>>(mA, mBh, mBm, g);
+  {
+    // programmatic dependent of the split kernel (see tc_pair.cu); QFLEX_PDL=0: plain launch
+    static const bool pdl = [] {
+      const char* e = getenv("QFLEX_PDL");
+      return e == nullptr || atoi(e) != 0;
+    }();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(FUSED_THREADS);
+    cfg.dynamicSmemBytes = (size_t)smem_bytes;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attrs[1];
+    attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = pdl ? 1 : 0;
+    switch (pick_store_mode(g, C)) {
+      case 1: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_pairlong_bf16x3<1>, mA, mBh, mBm, g)); break;
+      case 2: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_pairlong_bf16x3<2>, mA, mBh, mBm, g)); break;
+      default: QFX_CUDA(cudaLaunchKernelEx(&cfg, tc_pairlong_bf16x3<0>, mA, mBh, mBm, g));
+    }
   }
   QFX_CUDA(cudaGetLastError());
   ctx->stats.launches_gemm_tc++;

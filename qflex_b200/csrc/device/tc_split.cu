@@ -51,6 +51,10 @@ __device__ __forceinline__ uint32_t pack(__nv_bfloat16 lo, __nv_bfloat16 hi) {
 // MODE 0: operand A (row = m, natural [M][K]); MODE 1: operand B (expanded rows)
 template <int MODE>
 __global__ void __launch_bounds__(kThreads) split_gather(const __grid_constant__ SplitArgs g) {
+  // Programmatic dependent launch: the contraction kernel that follows may start its
+  // prologue (barrier init, TMEM allocation, first A loads) now; it waits
+  // (griddepcontrol.wait) before it reads what this kernel writes.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   __shared__ float2 tile[1 << kTileBits];
   __shared__ unsigned src_off[1 << kTileBits];
   __shared__ unsigned dst_off[1 << kTileBits];
