@@ -82,6 +82,8 @@ int qfx_launch_contract_tc_pair(qfx_ctx* ctx, const qfx_contract_desc& d, const 
                                 const float2* B, float2* C, bool* done);
 int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& d, const float2* A,
                                     const float2* B, float2* C, bool* done);
+int qfx_launch_tc_splitk_finish(qfx_ctx* ctx, const float2* part, float2* C,
+                                const qfx_contract_desc& d, int ksplit, int c_is_natural);
 // permute.cu
 int qfx_launch_permute(qfx_ctx* ctx, uint64_t src_off, uint64_t dst_off,
                        int n_bits, const int8_t* dst_pos);

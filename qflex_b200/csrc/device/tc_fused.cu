@@ -491,6 +491,28 @@ __global__ void tc_splitk_finish(const __grid_constant__ FinishArgs g) {
 
 }  // namespace
 
+// C = sum of the ksplit [M][N] slabs at `part` (also used by tc_pairlong.cu)
+int qfx_launch_tc_splitk_finish(qfx_ctx* ctx, const float2* part, float2* C,
+                                const qfx_contract_desc& d, int ksplit, int c_is_natural) {
+  FinishArgs f{};
+  f.part = part;
+  f.C = C;
+  f.m_bits = d.m_bits;
+  f.n_bits = d.n_bits;
+  f.ksplit = ksplit;
+  f.natural = c_is_natural;
+  memcpy(f.c_m, d.c_m, QFX_MAX_BITS);
+  memcpy(f.c_n, d.c_n, QFX_MAX_BITS);
+  const unsigned long long pairs = 1ull << (d.m_bits + d.n_bits - 1);
+  const unsigned fb = (unsigned)std::min<unsigned long long>((pairs + 255) / 256,
+                                                             16ull * ctx->sm_count);
+  tc_splitk_finish<<<fb, 256, 0, ctx->stream>>>(f);
+  QFX_CUDA(cudaGetLastError());
+  ctx->stats.launches_reduce++;
+  ctx->stats.launches_total++;
+  return QFX_OK;
+}
+
 // Roles already swapped (m_bits >= n_bits).  Returns QFX_OK and sets *done = true
 // when the fused kernel was launched; *done = false means "not applicable, use the
 // pre-split path" (not an error).
@@ -666,22 +688,8 @@ int qfx_launch_contract_tc_fused(qfx_ctx* ctx, const qfx_contract_desc& din, con
   }
   QFX_CUDA(cudaGetLastError());
   if (ksplit > 1) {
-    FinishArgs f{};
-    f.part = g.part;
-    f.C = C;
-    f.m_bits = d.m_bits;
-    f.n_bits = d.n_bits;
-    f.ksplit = ksplit;
-    f.natural = c_is_natural;
-    memcpy(f.c_m, d.c_m, QFX_MAX_BITS);
-    memcpy(f.c_n, d.c_n, QFX_MAX_BITS);
-    const unsigned long long pairs = (M * N) / 2;
-    const unsigned fb = (unsigned)std::min<unsigned long long>((pairs + 255) / 256,
-                                                               16ull * ctx->sm_count);
-    tc_splitk_finish<<<fb, 256, 0, ctx->stream>>>(f);
-    QFX_CUDA(cudaGetLastError());
-    ctx->stats.launches_reduce++;
-    ctx->stats.launches_total++;
+    rc = qfx_launch_tc_splitk_finish(ctx, g.part, C, d, ksplit, c_is_natural);
+    if (rc) return rc;
   }
   ctx->stats.launches_gemm_tc++;
   ctx->stats.launches_gemm_tc_fused++;

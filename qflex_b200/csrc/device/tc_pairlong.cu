@@ -160,15 +160,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       const int k_sh = lane < g.n_k_hi ? g.a_k_hi[lane] - 1 : -1;
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = pair0; w < g.tiles; w += pair_step) {
+      for (int w = pair0; w < g.tiles * g.ksplit; w += pair_step) {
+        const int kb0 = (w / g.tiles) * g.kblocks;  // split-K: this item's share of K
         int mt_, nt_;
-        decode_item(g, w, &mt_, &nt_);
+        decode_item(g, w % g.tiles, &mt_, &nt_);
         const unsigned mt = 2u * (unsigned)mt_ + rank;
         const unsigned row_base =
             __reduce_or_sync(0xffffffffu, (m_sh >= 0 && ((mt >> lane) & 1u)) ? (1u << m_sh) : 0u);
         for (int kb = 0; kb < g.kblocks; ++kb) {
           const unsigned off16 =
-              row_base | __reduce_or_sync(0xffffffffu, (k_sh >= 0 && (((unsigned)kb >> lane) & 1u))
+              row_base | __reduce_or_sync(0xffffffffu, (k_sh >= 0 && (((unsigned)(kb0 + kb) >> lane) & 1u))
                                                            ? (1u << k_sh)
                                                            : 0u);
           if (lane == 0) {
@@ -191,10 +192,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       const int half_rows = bn >> 1;
       // (programmatic dependent launch: B' comes from the split kernel launched before)
       asm volatile("griddepcontrol.wait;" ::: "memory");
-      for (int w = pair0; w < g.tiles; w += pair_step) {
+      for (int w = pair0; w < g.tiles * g.ksplit; w += pair_step) {
+        const int kb0 = (w / g.tiles) * g.kblocks;
         int mt, nt;
-        decode_item(g, w, &mt, &nt);
-        for (int kb = 0; kb < g.kblocks; ++kb) {
+        decode_item(g, w % g.tiles, &mt, &nt);
+        for (int kb = kb0; kb < kb0 + g.kblocks; ++kb) {
 #pragma unroll
           for (int part = 0; part < 2; ++part) {
             mbar_wait_spin(b_empty(slot), phase ^ 1u);
@@ -217,7 +219,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
       int cs = 0, bs = 0, acc = 0;
       uint32_t cph = 0, bph = 0, acc_phase = 0;
       const int nkk = (g.dbg & 4) ? 0 : g.nkk;
-      for (int w = pair0; w < g.tiles; w += pair_step) {
+      for (int w = pair0; w < g.tiles * g.ksplit; w += pair_step) {
         for (int ch = 0; ch < g.nchunks; ++ch) {
           mbar_wait_cluster(tempty_bar(acc), acc_phase ^ 1u);
           const uint32_t d_tmem = tmem_base + (uint32_t)(acc * bn);
@@ -283,7 +285,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
     const uint32_t flip = (vec && ((ctid >> 2) & 1u)) ? ok1 : 0u;
     int as = 0, cs = 0;
     uint32_t aph = 0, cph = 0;
-    for (int w = pair0; w < g.tiles; w += pair_step) {
+    for (int w = pair0; w < g.tiles * g.ksplit; w += pair_step) {
       for (int kb = 0; kb < g.kblocks; ++kb) {
         mbar_wait_spin(a_full(as), aph);
         mbar_wait_spin(c_empty(cs), cph ^ 1u);
@@ -362,10 +364,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
 #pragma unroll
       for (int i = 0; i < 7; ++i) m_local_b |= (unsigned)((ts.rowb >> i) & 1) << g.row_perm[i];
     }
-    for (int w = pair0; w < g.tiles; w += pair_step) {
+    for (int w = pair0; w < g.tiles * g.ksplit; w += pair_step) {
       int mt_, nt;
-      decode_item(g, w, &mt_, &nt);
+      decode_item(g, w % g.tiles, &mt_, &nt);
       const unsigned long long mtile = 2ull * (unsigned long long)mt_ + rank;
+      // split-K: this item's partial sums go to its own [M][N] slab (added in a fixed
+      // order by tc_splitk_finish, which also applies C's layout)
+      float2* const Cout =
+          g.ksplit > 1 ? g.part + ((unsigned long long)(w / g.tiles) << (g.m_bits + g.n_bits)) : g.C;
       float sum[8][16];
       for (int ch = 0; ch < g.nchunks; ++ch) {
         mbar_wait_spin(tfull_bar(acc), acc_phase);
@@ -417,13 +423,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
               co[g4] = ts.coj;
               for (int q = 2; q < g.n_bits; ++q) co[g4] |= ((n >> q) & 1ull) << g.c_n[q];
             }
-            tstore_piece(sum[p], g.C + rb + co[0], g.C + rb + co[1], ts.xm0, ts.xm1, lane);
+            tstore_piece(sum[p], Cout + rb + co[0], Cout + rb + co[1], ts.xm0, ts.xm1, lane);
           }
         }
         continue;
       }
       if (STORE == 1) {
-        float* tile_c = reinterpret_cast<float*>(g.C + mtile * BM * N);
+        float* tile_c = reinterpret_cast<float*>(Cout + mtile * BM * N);
         const int col0 = nt * bn + half * half_cols + 8 * (lane & 3);  // float column
 #pragma unroll
         for (int pp = 0; pp < 4; ++pp) {
@@ -444,7 +450,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
           const unsigned long long n0 =
               ((unsigned long long)nt * bn + half * half_cols + p * 16) >> 1;
           if (g.c_natural) {
-            float* dst = reinterpret_cast<float*>(g.C + row_off + n0);
+            float* dst = reinterpret_cast<float*>(Cout + row_off + n0);
             stg256(dst, &sum[p][0]);
             stg256(dst + 8, &sum[p][8]);
           } else {
@@ -453,7 +459,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(FUSED_THREADS, 1)
               const unsigned long long n = n0 + j;
               unsigned long long co = 0;
               for (int q = 0; q < g.n_bits; ++q) co |= ((n >> q) & 1ull) << g.c_n[q];
-              g.C[row_off + co] = make_float2(sum[p][2 * j], sum[p][2 * j + 1]);
+              Cout[row_off + co] = make_float2(sum[p][2 * j], sum[p][2 * j + 1]);
             }
           }
         }
@@ -530,7 +536,20 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
   g.bn = (int)std::min<uint64_t>(2 * N, MAX_BN);
   g.tiles_n = (int)((2 * N) / g.bn);
   g.tiles = (int)((M / (2 * BM)) * g.tiles_n);
-  if (g.tiles < 2 * n_pairs) return QFX_OK;
+  // few work items and a long K (the final merges, 2^12 x 256 x 2^16 = 32 items for 74
+  // pairs): split K over the items as tc_fused.cu does; partial [M][N] slabs, summed by
+  // tc_splitk_finish in a fixed order
+  const int kblocks_all = (int)std::max<uint64_t>(1, (2 * K) / BK);
+  int ksplit = 1;
+  if (g.tiles < 2 * n_pairs) {
+    static const bool splitk_on = [] {
+      const char* e = getenv("QFLEX_TC_PAIRLONG_SPLITK");
+      return e == nullptr || atoi(e) != 0;
+    }();
+    if (!splitk_on || kblocks_all < 64) return QFX_OK;
+    while (g.tiles * ksplit * 2 <= 8 * n_pairs && kblocks_all / (ksplit * 2) >= 8) ksplit *= 2;
+    if (g.tiles * ksplit < 2 * n_pairs) return QFX_OK;
+  }
   g.kb_bits = std::min(5, (int)d.k_bits);
   g.tile_bits = 7 + g.kb_bits;
   uint64_t span = 0;
@@ -541,10 +560,10 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
   if (!make_map_a(&mA, A, d, g.kb_bits, span, &g)) return QFX_OK;
 
   g.C = C;
-  g.ksplit = 1;
+  g.ksplit = ksplit;
   g.m_bits = d.m_bits;
   g.n_bits = d.n_bits;
-  g.kblocks = (int)std::max<uint64_t>(1, (2 * K) / BK);
+  g.kblocks = kblocks_all / ksplit;
   g.nkk = (int)std::min<uint64_t>(4, (2 * K) / 16);
   g.chunk = ctx->tc_chunk > 0 ? ctx->tc_chunk : 4;
   g.nchunks = (g.kblocks + g.chunk - 1) / g.chunk;
@@ -571,6 +590,8 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
   for (int i = 0; i < d.m_bits; ++i)
     if (d.c_m[i] != d.n_bits + i) g.c_natural = 0;
   if ((reinterpret_cast<uintptr_t>(C) & 31) != 0) g.c_natural = 0;
+  const int c_is_natural = g.c_natural;
+  if (ksplit > 1) g.c_natural = 1;  // the slabs are [M][N]; C's layout is applied by the finish
   memcpy(g.c_m, d.c_m, QFX_MAX_BITS);
   memcpy(g.c_n, d.c_n, QFX_MAX_BITS);
   g.n_m_hi = d.m_bits - 7;
@@ -599,11 +620,13 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
   const int smem_bytes = total();
   if (const char* e = getenv("QFLEX_FUSED_DBG")) g.dbg = atoi(e);
 
-  // workspace: B' hi/mid (2N x 2K bf16 each)
+  // workspace: B' hi/mid (2N x 2K bf16 each), then the split-K slabs
   const size_t b_bytes = (size_t)N * K * 8;
-  int rc = qfx_ensure_ws(ctx, 2 * b_bytes + 4096);
+  const size_t part_bytes = ksplit > 1 ? (size_t)ksplit * M * N * 8 : 0;
+  int rc = qfx_ensure_ws(ctx, 2 * b_bytes + 4096 + part_bytes);
   if (rc) return rc;
   uint8_t* ws = reinterpret_cast<uint8_t*>(ctx->ws);
+  g.part = reinterpret_cast<float2*>(ws + ((2 * b_bytes + 4095) & ~(size_t)4095));
   uint32_t* b_hi = reinterpret_cast<uint32_t*>(ws);
   uint32_t* b_mid = reinterpret_cast<uint32_t*>(ws + b_bytes);
   rc = qfx_launch_split(ctx, B, 1, d.b_n, d.n_bits, d.b_k, d.k_bits, b_hi, b_mid);
@@ -623,7 +646,7 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
                                   SMEM_LIMIT));
     attr.mark(ctx->device);
   }
-  const int grid = 2 * std::min(g.tiles, n_pairs);
+  const int grid = 2 * std::min(g.tiles * g.ksplit, n_pairs);
   {
     // programmatic dependent of the split kernel (see tc_pair.cu); QFLEX_PDL=0: plain launch
     static const bool pdl = [] {
@@ -647,6 +670,10 @@ int qfx_launch_contract_tc_pairlong(qfx_ctx* ctx, const qfx_contract_desc& din, 
     }
   }
   QFX_CUDA(cudaGetLastError());
+  if (ksplit > 1) {
+    rc = qfx_launch_tc_splitk_finish(ctx, g.part, C, d, ksplit, c_is_natural);
+    if (rc) return rc;
+  }
   ctx->stats.launches_gemm_tc++;
   ctx->stats.launches_gemm_tc_fused++;
   ctx->stats.launches_gemm_tc_pair++;

@@ -224,6 +224,26 @@ def test_pair_kernel_long_k_wide_n(ctx, m, n, k, groups, c_layout):
     assert ctx.stats()["launches_gemm_tc_pair"] == before + 1, used
 
 
+@pytest.mark.parametrize("m,n,k,c_layout", [(12, 8, 14, "natural"), (11, 8, 15, "scattered"),
+                                            (12, 7, 14, "transposed")])
+def test_pair_kernel_long_k_split_k(ctx, m, n, k, c_layout):
+    """Few 256-row work items and a long K (the headline's 2^12 x 256 x 2^16 merges): K is
+    split over the pair kernel's work items, slabs summed by tc_splitk_finish."""
+    rng = np.random.default_rng(62000 + 100 * m + 10 * n + k)
+    t = _natural(m, n, k)
+    if c_layout == "scattered":
+        pc = [int(x) for x in rng.permutation(m + n)]
+        t["c_m"], t["c_n"] = pc[:m], pc[m:]
+    elif c_layout == "transposed":
+        t["c_m"], t["c_n"] = list(range(m)), list(range(m, m + n))
+    before = ctx.stats()
+    err, used = _run(ctx, t, rng)
+    after = ctx.stats()
+    assert err < TOL_TC
+    assert after["launches_gemm_tc_pair"] == before["launches_gemm_tc_pair"] + 1, used
+    assert after["launches_reduce"] == before["launches_reduce"] + 1  # the slab sum
+
+
 # ---- split-K in tc_fused.cu: few output tiles, long K (the final merges)
 @pytest.mark.parametrize("m,n,k,scatter", [(10, 8, 12, False), (9, 6, 13, True), (8, 8, 14, False),
                                            (12, 8, 12, True)])
